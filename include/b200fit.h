@@ -1,0 +1,152 @@
+/*
+ * b200fit.h -- C ABI of libb200fit.so, the B200 (sm_100a) fit engine that sits
+ * under the pyspark.ml-shaped Python surface in orange3-spark_b200/b200fit/.
+ *
+ * The reference (Gjerman/Orange3-Spark) has NO native / FFI interface: its hot
+ * path is `pyspark.ml` objects reached over py4j.  Each entry point below
+ * therefore cites the reference call site whose (JVM-side) work it replaces,
+ * and the MLlib operation restated in SURVEY.md Appendix A.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative B2F_E* code otherwise;
+ *     b2f_last_error() returns a thread-local message for the last failure;
+ *   - all pointers are DEVICE pointers unless the name ends in _host;
+ *   - the caller owns every buffer (the library never allocates device memory)
+ *     and passes the CUDA stream as an opaque pointer (cudaStream_t; NULL = the
+ *     legacy default stream);
+ *   - calls are asynchronous on `stream`; nothing here synchronises the device;
+ *   - feature matrices are row-major fp32 `X[n, ld]`, ld >= d, ld % 4 == 0 and X
+ *     16-byte aligned (rows are legal float4 / TMA rows).
+ */
+#ifndef B200FIT_H_
+#define B200FIT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2F_OK 0
+#define B2F_EINVAL (-1)   /* bad argument (message says which) */
+#define B2F_ECUDA (-2)    /* CUDA runtime / driver error */
+#define B2F_EUNSUPPORTED (-3)
+
+/* column dtypes accepted by b2f_pack_columns */
+#define B2F_F32 0
+#define B2F_F64 1
+#define B2F_I32 2
+#define B2F_I64 3
+#define B2F_U8 4 /* also bool */
+
+/* b2f_kmeans_step algorithms */
+#define B2F_KM_AUTO 0
+#define B2F_KM_GENERIC 1 /* CUDA-core fp32, any k / d */
+#define B2F_KM_TC3 2     /* tcgen05 3xTF32 (fp32-accurate) contraction, d % 32 == 0, k % 128 == 0 */
+#define B2F_KM_TC1 3     /* tcgen05 1xTF32 contraction (filter pass; labels need refine) */
+
+typedef void* b2f_stream_t;
+
+/* ---- library ------------------------------------------------------------ */
+int b2f_version(void);
+const char* b2f_last_error(void);
+
+/* ---- synthetic inputs (Philox4x32-10 keyed on (seed, global row, column)) ----
+ * No reference counterpart: the reference ships no data generator; these produce the
+ * BASELINE.json config shapes on device so 100M x 128 never crosses PCIe.          */
+/* X[r, c] = centre[comp(row)][c] * 1 + z(row, c);  centre[j][c] = center_scale * z'(j, c);
+ * comp(row) = philox(row) mod n_components; optional per-column scale multiplies the result. */
+int b2f_synth_mixture(float* X, int64_t n, int64_t row0, int d, int64_t ld, uint64_t seed,
+                      int n_components, float center_scale, const float* col_scale, b2f_stream_t stream);
+/* X[r, c] = col_scale[c] * z(row, c);  margins m_k = X[r,:] . w_true[k,:] + b_true[k];
+ * n_classes == 2: y = 1 if u < sigmoid(m_0) else 0 (w_true is [1,d]);
+ * n_classes  > 2: y ~ Categorical(softmax(m)) by inverse CDF on u.  y is written as fp32 class ids. */
+int b2f_synth_logistic(float* X, float* y, int64_t n, int64_t row0, int d, int64_t ld, uint64_t seed,
+                       const float* col_scale, const float* w_true, const float* b_true, int n_classes,
+                       b2f_stream_t stream);
+
+/* ---- K1 loader: Dataset Builder -> VectorAssembler ------------------------
+ * replaces VectorAssembler(inputCols, outputCol='features').transform(df)
+ *   reference: orangecontrib/spark/widgets/ml/spark_ml_dataset.py:575-576 (A.1)
+ * col_ptrs_dev[d]  : device array of device pointers, one per ordered input column
+ * col_dtypes_dev[d]: device array of B2F_* dtype codes
+ * X[n, ld]         : fp32 row-major output (padding columns d..ld-1 are zeroed)
+ * bad_flag         : device int32, set to 1 if any value is NaN/Inf (NULL to skip) */
+int b2f_pack_columns(const void* const* col_ptrs_dev, const int32_t* col_dtypes_dev, int d, int64_t n,
+                     float* X, int64_t ld, int32_t* bad_flag, b2f_stream_t stream);
+
+/* column statistics for StandardScaler.fit / the LogisticRegression summarizer (A.3 pass 0, A.6)
+ *   reference: reached from fit() orangecontrib/spark/base/spark_ml_estimator.py:22
+ * out[0:d] += sum w (x - shift), out[d:2d] += sum w (x - shift)^2, out[2d] += sum w, out[2d+1] += sum w^2
+ * (fp64, accumulated with atomics: zero `out` first; `w` and `shift` may be NULL).       */
+int b2f_colstats(const float* X, int64_t n, int d, int64_t ld, const float* w, const float* shift,
+                 double* out, b2f_stream_t stream);
+/* label histogram: hist[c] += sum of w over rows with y == c, c < n_bins (fp64, zero first) */
+int b2f_label_hist(const float* y, const float* w, int64_t n, int n_bins, double* hist, int32_t* bad_flag,
+                   b2f_stream_t stream);
+
+/* ---- K2 KMeans (Lloyd) ----------------------------------------------------
+ * replaces the JVM work behind KMeans.fit
+ *   reference: orangecontrib/spark/base/spark_ml_estimator.py:22 with module = clustering
+ *   (orangecontrib/spark/widgets/ml/spark_ml_clustering.py:14); MLlib semantics: SURVEY.md A.2.
+ *
+ * Device state owned by the caller:
+ *   centers   double[k*d]                      master copy of the centres
+ *   prep      b2f_kmeans_prep_bytes(k,d) bytes  kernel-ready centre operands (opaque)
+ *   acc       b2f_kmeans_acc_bytes(k,d) bytes   accumulators; its HEAD is the all-reduce
+ *             payload double[k*d + k + 2] = [sums | counts | cost | n_rows]; the tail is
+ *             scratch (fp32 replicas, per-CTA partials).                                     */
+size_t b2f_kmeans_prep_bytes(int k, int d);
+size_t b2f_kmeans_acc_bytes(int k, int d);
+/* number of doubles in the all-reduce payload at the head of `acc` */
+int64_t b2f_kmeans_payload_len(int k, int d);
+int b2f_kmeans_prepare(const double* centers, int k, int d, void* prep, b2f_stream_t stream);
+int b2f_kmeans_acc_zero(void* acc, int k, int d, b2f_stream_t stream);
+/* one assignment + accumulate pass over this rank's rows (findClosest + axpy into sums):
+ * labels (int32[n]) may be NULL; w (row weights) may be NULL; algo is a B2F_KM_* code.       */
+int b2f_kmeans_step(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep, int k,
+                    void* acc, int32_t* labels, int algo, b2f_stream_t stream);
+/* folds scratch replicas / partials into the fp64 payload at the head of acc */
+int b2f_kmeans_fold(void* acc, int k, int d, b2f_stream_t stream);
+/* centre update from the (all-reduced) payload: centres with count > 0 move to sums/count,
+ * empty clusters keep their centre; status[0] = 1 if every moved centre moved <= tol else 0,
+ * status[1] = max squared move (as double bits in status_f64[0]); cost copied to status_f64[1]. */
+int b2f_kmeans_finalize(const double* payload, int k, int d, double tol, double* centers, int32_t* status,
+                        double* status_f64, b2f_stream_t stream);
+/* KMeansModel.transform: labels (int32[n]) and/or squared distance to the closest centre
+ * (float[n], used by computeCost and the k-means|| initialiser); no accumulation.
+ *   reference: orangecontrib/spark/widgets/ml/spark_ml_model.py:53                            */
+int b2f_kmeans_predict(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, int32_t* labels,
+                       float* dist2, int algo, b2f_stream_t stream);
+
+/* ---- K3 / K4 LogisticRegression loss + gradient passes --------------------
+ * replaces the treeAggregate of LogisticAggregator inside RDDLossFunction.calculate
+ *   reference: orangecontrib/spark/base/spark_ml_estimator.py:22 with module = classification
+ *   (orangecontrib/spark/widgets/ml/spark_ml_classification.py:15); semantics: SURVEY.md A.3.
+ *
+ * beta    double[K*d]  ORIGINAL-space weights (= standardized coefficient * 1/sigma_j), K = 1 binary
+ * icpt    double[K]    intercepts
+ * out     double[K*d + K + 2], ACCUMULATED (zero first; this is the all-reduce payload):
+ *           out[k*d + j] += sum_i w_i (p_ik - 1[y_i = k]) x_ij     (raw, not yet scaled by 1/sigma, 1/W)
+ *           out[K*d + k] += sum_i w_i (p_ik - 1[y_i = k])
+ *           out[K*d + K] += sum_i w_i loss_i ;  out[K*d + K + 1] += sum_i w_i
+ * scratch  b2f_lr_scratch_bytes(d, K) bytes of caller-owned device memory                       */
+size_t b2f_lr_scratch_bytes(int d, int n_classes);
+int b2f_lr_binary_lossgrad(const float* X, const float* y, const float* w, int64_t n, int d, int64_t ld,
+                           const double* beta, const double* icpt, double* out, void* scratch,
+                           b2f_stream_t stream);
+int b2f_lr_multinomial_lossgrad(const float* X, const float* y, const float* w, int64_t n, int d, int64_t ld,
+                                int n_classes, const double* beta, const double* icpt, double* out,
+                                void* scratch, b2f_stream_t stream);
+/* LogisticRegressionModel.transform (A.3 prediction): raw[n,Kc], prob[n,Kc], pred[n] (any may be NULL);
+ * Kc = 2 for binary (n_classes == 2, beta is [1,d]) else n_classes.
+ *   reference: orangecontrib/spark/widgets/ml/spark_ml_model.py:53                              */
+int b2f_lr_predict(const float* X, int64_t n, int d, int64_t ld, int n_classes, const double* beta,
+                   const double* icpt, double threshold, float* raw, float* prob, float* pred,
+                   b2f_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200FIT_H_ */

@@ -1,0 +1,112 @@
+// Shared helpers for libb200fit.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "b200fit.h"
+
+#ifndef __CUDA_ARCH__
+#define B2F_HOST 1
+#endif
+
+void b2f_set_error(const char* fmt, ...);
+
+#define B2F_REQUIRE(cond, ...)        \
+  do {                                \
+    if (!(cond)) {                    \
+      b2f_set_error(__VA_ARGS__);     \
+      return B2F_EINVAL;              \
+    }                                 \
+  } while (0)
+
+#define B2F_CUDA(call)                                                                  \
+  do {                                                                                  \
+    cudaError_t _e = (call);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      b2f_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+      return B2F_ECUDA;                                                                 \
+    }                                                                                   \
+  } while (0)
+
+#define B2F_LAUNCH_CHECK() B2F_CUDA(cudaGetLastError())
+
+static inline cudaStream_t b2f_cs(b2f_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// number of SMs of the current device (cached per device)
+int b2f_sm_count();
+
+static inline size_t b2f_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ---- kmeans buffer layouts (shared by kmeans_generic.cu / kmeans_tc.cu) ----
+// prep:  [ C32  float[k*d]   fp32 centres (rounded from the fp64 master)
+//          CH   float[k*d]   -2*c rounded to TF32 (low 13 mantissa bits zero)
+//          CL   float[k*d]   -2*c - CH, rounded to TF32
+//          CN   float[k]     ||c||^2 (fp32, from fp64)
+//          C64  double[k*d]  copy of the fp64 master (refine / exact paths) ]
+struct KmPrepLayout {
+  size_t off_c32, off_ch, off_cl, off_cn, off_c64, bytes;
+};
+static inline KmPrepLayout km_prep_layout(int k, int d) {
+  KmPrepLayout L;
+  size_t kd = (size_t)k * d;
+  size_t o = 0;
+  L.off_c32 = o; o = b2f_align_up(o + kd * 4, 1024);
+  L.off_ch = o;  o = b2f_align_up(o + kd * 4, 1024);
+  L.off_cl = o;  o = b2f_align_up(o + kd * 4, 1024);
+  L.off_cn = o;  o = b2f_align_up(o + (size_t)k * 4, 1024);
+  L.off_c64 = o; o = b2f_align_up(o + kd * 8, 1024);
+  L.bytes = o;
+  return L;
+}
+
+// acc:   [ payload double[k*d + k + 2] = sums | counts | cost | nrows
+//          rep     float[KM_REPLICAS * k * d]   fp32 replicas written with red.global.add
+//          cnt32   unsigned long long[k]        integer counts (unweighted fast path)        ]
+#define KM_REPLICAS 4
+struct KmAccLayout {
+  size_t off_payload, off_rep, off_cnt, bytes;
+  size_t payload_len;
+};
+static inline KmAccLayout km_acc_layout(int k, int d) {
+  KmAccLayout L;
+  size_t kd = (size_t)k * d;
+  L.payload_len = kd + k + 2;
+  size_t o = 0;
+  L.off_payload = o; o = b2f_align_up(o + L.payload_len * 8, 1024);
+  L.off_rep = o;     o = b2f_align_up(o + (size_t)KM_REPLICAS * kd * 4, 1024);
+  L.off_cnt = o;     o = b2f_align_up(o + (size_t)k * 8, 1024);
+  L.bytes = o;
+  return L;
+}
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// round-to-nearest fp32 -> tf32 (result is an fp32 bit pattern with the low 13 bits zero)
+__device__ __forceinline__ float to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float4 ldg_stream(const float4* p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+#endif
+
+// implemented in kmeans_tc.cu
+int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
+               int passes, bool accumulate, cudaStream_t stream);
+bool km_tc_supported(int k, int d, int64_t ld);

@@ -1,0 +1,346 @@
+// K2 KMeans: centre preparation, the CUDA-core (any k / d) assignment + accumulate kernel, fold,
+// finalize and predict, and the dispatch into the tcgen05 kernel (kmeans_tc.cu).
+// Replaces the JVM work behind KMeans.fit / KMeansModel.transform
+//   reference: orangecontrib/spark/base/spark_ml_estimator.py:22 (module = clustering,
+//   orangecontrib/spark/widgets/ml/spark_ml_clustering.py:14) and
+//   orangecontrib/spark/widgets/ml/spark_ml_model.py:53;  MLlib semantics: SURVEY.md A.2.
+#include "common.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// prepare: fp64 master centres -> kernel operands
+// ---------------------------------------------------------------------------------------------
+__global__ void km_prepare_kernel(const double* __restrict__ C, int k, int d, float* __restrict__ c32,
+                                  float* __restrict__ ch, float* __restrict__ cl, float* __restrict__ cn,
+                                  double* __restrict__ c64) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int j = warp; j < k; j += nwarps) {
+    double nn = 0.0;
+    for (int c = lane; c < d; c += 32) {
+      const size_t i = (size_t)j * d + c;
+      const double v = C[i];
+      nn += v * v;
+      c32[i] = (float)v;
+      c64[i] = v;
+      const double m2 = -2.0 * v;
+      const float hi = to_tf32((float)m2);
+      ch[i] = hi;
+      cl[i] = to_tf32((float)(m2 - (double)hi));
+    }
+    nn = warp_sum(nn);
+    if (lane == 0) cn[j] = (float)nn;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// generic step: one thread per row, centres streamed through shared memory in tiles.
+// Distances use the direct form sum (x - c)^2 in fp32 (no cancellation), ascending centre order
+// with strict '<' so ties keep the lowest index (findClosest semantics).
+// ---------------------------------------------------------------------------------------------
+#define KG_THREADS 256
+#define KG_TILE_FLOATS 8192   // centre tile in shared memory (32 KB)
+#define KG_TABLE_FLOATS 8192  // per-CTA accumulation table(s) (32 KB)
+
+template <bool ACC>
+__global__ void __launch_bounds__(KG_THREADS) km_generic_kernel(const float* __restrict__ X, int64_t n, int d,
+                                                                int64_t ld, const float* __restrict__ w,
+                                                                const float* __restrict__ C32, int k,
+                                                                double* __restrict__ payload, float* __restrict__ rep,
+                                                                int32_t* __restrict__ labels,
+                                                                float* __restrict__ dist2, int tile_k,
+                                                                int table_reps) {
+  extern __shared__ __align__(16) float smem[];
+  const int ds = (d + 3) & ~3;          // padded centre row in smem
+  float* ctile = smem;                  // [tile_k][ds]
+  float* table = smem + KG_TILE_FLOATS; // [table_reps][k][d+1] when table_reps > 0
+  const int tstride = k * (d + 1);
+  if (ACC && table_reps > 0) {
+    for (int i = threadIdx.x; i < table_reps * tstride; i += KG_THREADS) table[i] = 0.f;
+  }
+  double cost = 0.0, wsum = 0.0;
+  const int64_t nblocks = (n + KG_THREADS - 1) / KG_THREADS;
+  for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+    const int64_t r = blk * KG_THREADS + threadIdx.x;
+    const bool live = r < n;
+    const float* xr = X + (live ? r : 0) * ld;
+    float best = INFINITY;
+    int bi = 0;
+    for (int j0 = 0; j0 < k; j0 += tile_k) {
+      const int tk = min(tile_k, k - j0);
+      __syncthreads();
+      for (int i = threadIdx.x; i < tk * ds; i += KG_THREADS) {
+        const int jj = i / ds, c = i - jj * ds;
+        ctile[i] = (c < d) ? C32[(size_t)(j0 + jj) * d + c] : 0.f;
+      }
+      __syncthreads();
+      if (live) {
+        for (int jj = 0; jj < tk; jj += 4) {
+          float4 a0 = make_float4(0, 0, 0, 0), a1 = a0, a2 = a0, a3 = a0;
+          const float* c0 = ctile + (size_t)jj * ds;
+          const int j1 = min(jj + 1, tk - 1), j2 = min(jj + 2, tk - 1), j3 = min(jj + 3, tk - 1);
+          const float* c1 = ctile + (size_t)j1 * ds;
+          const float* c2 = ctile + (size_t)j2 * ds;
+          const float* c3 = ctile + (size_t)j3 * ds;
+          for (int c = 0; c < ds; c += 4) {
+            float4 x = *reinterpret_cast<const float4*>(xr + c);
+            if (c + 3 >= d) {  // mask padding columns (caller's padding need not be zero)
+              if (c + 1 >= d) x.y = 0.f;
+              if (c + 2 >= d) x.z = 0.f;
+              x.w = 0.f;
+            }
+            float4 v, t;
+            v = *reinterpret_cast<const float4*>(c0 + c);
+            t.x = x.x - v.x; t.y = x.y - v.y; t.z = x.z - v.z; t.w = x.w - v.w;
+            a0.x = fmaf(t.x, t.x, a0.x); a0.y = fmaf(t.y, t.y, a0.y); a0.z = fmaf(t.z, t.z, a0.z); a0.w = fmaf(t.w, t.w, a0.w);
+            v = *reinterpret_cast<const float4*>(c1 + c);
+            t.x = x.x - v.x; t.y = x.y - v.y; t.z = x.z - v.z; t.w = x.w - v.w;
+            a1.x = fmaf(t.x, t.x, a1.x); a1.y = fmaf(t.y, t.y, a1.y); a1.z = fmaf(t.z, t.z, a1.z); a1.w = fmaf(t.w, t.w, a1.w);
+            v = *reinterpret_cast<const float4*>(c2 + c);
+            t.x = x.x - v.x; t.y = x.y - v.y; t.z = x.z - v.z; t.w = x.w - v.w;
+            a2.x = fmaf(t.x, t.x, a2.x); a2.y = fmaf(t.y, t.y, a2.y); a2.z = fmaf(t.z, t.z, a2.z); a2.w = fmaf(t.w, t.w, a2.w);
+            v = *reinterpret_cast<const float4*>(c3 + c);
+            t.x = x.x - v.x; t.y = x.y - v.y; t.z = x.z - v.z; t.w = x.w - v.w;
+            a3.x = fmaf(t.x, t.x, a3.x); a3.y = fmaf(t.y, t.y, a3.y); a3.z = fmaf(t.z, t.z, a3.z); a3.w = fmaf(t.w, t.w, a3.w);
+          }
+          const float d0 = (a0.x + a0.y) + (a0.z + a0.w), d1 = (a1.x + a1.y) + (a1.z + a1.w);
+          const float d2 = (a2.x + a2.y) + (a2.z + a2.w), d3 = (a3.x + a3.y) + (a3.z + a3.w);
+          if (d0 < best) { best = d0; bi = j0 + jj; }
+          if (jj + 1 < tk && d1 < best) { best = d1; bi = j0 + jj + 1; }
+          if (jj + 2 < tk && d2 < best) { best = d2; bi = j0 + jj + 2; }
+          if (jj + 3 < tk && d3 < best) { best = d3; bi = j0 + jj + 3; }
+        }
+      }
+    }
+    if (live) {
+      if (labels) labels[r] = bi;
+      if (dist2) dist2[r] = best;
+      if (ACC) {
+        const float wi = w ? w[r] : 1.f;
+        cost += (double)wi * (double)best;
+        wsum += (double)wi;
+        if (table_reps > 0) {
+          float* t = table + (size_t)((threadIdx.x >> 5) % table_reps) * tstride + (size_t)bi * (d + 1);
+          for (int c = 0; c < d; ++c) atomicAdd(t + c, wi * xr[c]);
+          atomicAdd(t + d, wi);
+        } else {
+          float* t = rep + ((size_t)(blockIdx.x % KM_REPLICAS) * k + bi) * d;
+          for (int c = 0; c < d; ++c) atomicAdd(t + c, wi * xr[c]);
+          atomicAdd(payload + (size_t)k * d + bi, (double)wi);
+        }
+      }
+    }
+  }
+  if (ACC) {
+    __syncthreads();
+    if (table_reps > 0) {
+      for (int i = threadIdx.x; i < tstride; i += KG_THREADS) {
+        double s = 0.0;
+        for (int rp = 0; rp < table_reps; ++rp) s += (double)table[(size_t)rp * tstride + i];
+        if (s != 0.0) {
+          const int j = i / (d + 1), c = i - j * (d + 1);
+          if (c < d) atomicAdd(payload + (size_t)j * d + c, s);
+          else atomicAdd(payload + (size_t)k * d + j, s);
+        }
+      }
+    }
+    cost = warp_sum(cost);
+    wsum = warp_sum(wsum);
+    __shared__ double red[2][KG_THREADS / 32];
+    if ((threadIdx.x & 31) == 0) {
+      red[0][threadIdx.x >> 5] = cost;
+      red[1][threadIdx.x >> 5] = wsum;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double c = 0, s = 0;
+      for (int i = 0; i < KG_THREADS / 32; ++i) {
+        c += red[0][i];
+        s += red[1][i];
+      }
+      atomicAdd(payload + (size_t)k * d + k, c);
+      atomicAdd(payload + (size_t)k * d + k + 1, s);
+    }
+  }
+}
+
+static int km_generic_launch(const float* X, int64_t n, int d, int64_t ld, const float* w, const float* C32, int k,
+                             double* payload, float* rep, int32_t* labels, float* dist2, bool acc,
+                             cudaStream_t st) {
+  const int ds = (d + 3) & ~3;
+  B2F_REQUIRE(ds * 4 <= KG_TILE_FLOATS, "b2f_kmeans: generic kernel supports d <= %d", KG_TILE_FLOATS / 4);
+  int tile_k = KG_TILE_FLOATS / ds;
+  tile_k = (tile_k / 4) * 4;
+  if (tile_k > k) tile_k = (k + 3) / 4 * 4;
+  int table_reps = 0;
+  const size_t tstride = (size_t)k * (d + 1);
+  if (acc && tstride <= KG_TABLE_FLOATS) {
+    table_reps = (int)(KG_TABLE_FLOATS / tstride);
+    if (table_reps > KG_THREADS / 32) table_reps = KG_THREADS / 32;
+  }
+  size_t smem = (size_t)KG_TILE_FLOATS * 4 + (size_t)table_reps * tstride * 4;
+  int64_t nblocks = (n + KG_THREADS - 1) / KG_THREADS;
+  int64_t cap = (int64_t)b2f_sm_count() * 3;
+  int grid = (int)(nblocks < cap ? nblocks : cap);
+  if (grid < 1) grid = 1;
+  if (acc) {
+    B2F_CUDA(cudaFuncSetAttribute(km_generic_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    km_generic_kernel<true><<<grid, KG_THREADS, smem, st>>>(X, n, d, ld, w, C32, k, payload, rep, labels, dist2,
+                                                            tile_k, table_reps);
+  } else {
+    B2F_CUDA(cudaFuncSetAttribute(km_generic_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    km_generic_kernel<false><<<grid, KG_THREADS, smem, st>>>(X, n, d, ld, w, C32, k, payload, rep, labels, dist2,
+                                                             tile_k, 0);
+  }
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// fold / finalize
+// ---------------------------------------------------------------------------------------------
+__global__ void km_fold_kernel(double* __restrict__ payload, float* __restrict__ rep,
+                               unsigned long long* __restrict__ cnt, int k, int d) {
+  const size_t kd = (size_t)k * d;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < kd; i += (size_t)gridDim.x * blockDim.x) {
+    double s = 0.0;
+#pragma unroll
+    for (int rp = 0; rp < KM_REPLICAS; ++rp) {
+      s += (double)rep[rp * kd + i];
+      rep[rp * kd + i] = 0.f;
+    }
+    payload[i] += s;
+  }
+  for (size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x; j < (size_t)k; j += (size_t)gridDim.x * blockDim.x) {
+    payload[kd + j] += (double)cnt[j];
+    cnt[j] = 0ull;
+  }
+}
+
+__global__ void km_finalize_init_kernel(const double* __restrict__ payload, int k, int d, int32_t* status,
+                                        double* status_f64) {
+  status[0] = 1;
+  status[1] = 0;
+  status_f64[0] = 0.0;
+  status_f64[1] = payload[(size_t)k * d + k];
+}
+
+__global__ void km_finalize_kernel(const double* __restrict__ payload, int k, int d, double tol2,
+                                   double* __restrict__ C, int32_t* status, double* status_f64) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int j = warp; j < k; j += nwarps) {
+    const double cnt = payload[(size_t)k * d + j];
+    if (!(cnt > 0.0)) continue;  // empty cluster keeps its centre
+    double moved = 0.0;
+    for (int c = lane; c < d; c += 32) {
+      const size_t i = (size_t)j * d + c;
+      const double nc = payload[i] / cnt;
+      const double df = nc - C[i];
+      moved += df * df;
+      C[i] = nc;
+    }
+    moved = warp_sum(moved);
+    if (lane == 0) {
+      if (moved > tol2) atomicExch(status, 0);
+      atomicMax(reinterpret_cast<unsigned long long*>(status_f64), (unsigned long long)__double_as_longlong(moved));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+extern "C" size_t b2f_kmeans_prep_bytes(int k, int d) { return (k > 0 && d > 0) ? km_prep_layout(k, d).bytes : 0; }
+extern "C" size_t b2f_kmeans_acc_bytes(int k, int d) { return (k > 0 && d > 0) ? km_acc_layout(k, d).bytes : 0; }
+extern "C" int64_t b2f_kmeans_payload_len(int k, int d) {
+  return (k > 0 && d > 0) ? (int64_t)km_acc_layout(k, d).payload_len : 0;
+}
+
+extern "C" int b2f_kmeans_prepare(const double* centers, int k, int d, void* prep, b2f_stream_t stream) {
+  B2F_REQUIRE(centers && prep && k > 0 && d > 0, "b2f_kmeans_prepare: bad arguments");
+  KmPrepLayout L = km_prep_layout(k, d);
+  char* p = static_cast<char*>(prep);
+  int grid = (k + 7) / 8;
+  km_prepare_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(
+      centers, k, d, reinterpret_cast<float*>(p + L.off_c32), reinterpret_cast<float*>(p + L.off_ch),
+      reinterpret_cast<float*>(p + L.off_cl), reinterpret_cast<float*>(p + L.off_cn),
+      reinterpret_cast<double*>(p + L.off_c64));
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+extern "C" int b2f_kmeans_acc_zero(void* acc, int k, int d, b2f_stream_t stream) {
+  B2F_REQUIRE(acc && k > 0 && d > 0, "b2f_kmeans_acc_zero: bad arguments");
+  B2F_CUDA(cudaMemsetAsync(acc, 0, km_acc_layout(k, d).bytes, b2f_cs(stream)));
+  return B2F_OK;
+}
+
+static int km_pick_algo(int algo, int k, int d, int64_t ld, const float* w) {
+  if (algo == B2F_KM_AUTO) return (!w && km_tc_supported(k, d, ld)) ? B2F_KM_TC3 : B2F_KM_GENERIC;
+  return algo;
+}
+
+extern "C" int b2f_kmeans_step(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep, int k,
+                               void* acc, int32_t* labels, int algo, b2f_stream_t stream) {
+  B2F_REQUIRE(X && prep && acc, "b2f_kmeans_step: null pointer");
+  B2F_REQUIRE(n >= 0 && d > 0 && k > 0 && ld >= d && ld % 4 == 0, "b2f_kmeans_step: need ld >= d, ld %% 4 == 0");
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_kmeans_step: X must be 16-byte aligned");
+  if (n == 0) return B2F_OK;
+  KmPrepLayout P = km_prep_layout(k, d);
+  KmAccLayout A = km_acc_layout(k, d);
+  const char* pp = static_cast<const char*>(prep);
+  char* ap = static_cast<char*>(acc);
+  algo = km_pick_algo(algo, k, d, ld, w);
+  if (algo == B2F_KM_TC3 || algo == B2F_KM_TC1) {
+    B2F_REQUIRE(!w, "b2f_kmeans_step: the tensor-core path does not take row weights");
+    B2F_REQUIRE(km_tc_supported(k, d, ld), "b2f_kmeans_step: tensor-core path needs d %% 32 == 0, d <= 256, k %% 128 == 0");
+    return km_tc_step(X, n, d, ld, prep, k, acc, labels, algo == B2F_KM_TC3 ? 3 : 1, true, b2f_cs(stream));
+  }
+  B2F_REQUIRE(algo == B2F_KM_GENERIC, "b2f_kmeans_step: unknown algo %d", algo);
+  return km_generic_launch(X, n, d, ld, w, reinterpret_cast<const float*>(pp + P.off_c32), k,
+                           reinterpret_cast<double*>(ap + A.off_payload), reinterpret_cast<float*>(ap + A.off_rep),
+                           labels, nullptr, true, b2f_cs(stream));
+}
+
+extern "C" int b2f_kmeans_fold(void* acc, int k, int d, b2f_stream_t stream) {
+  B2F_REQUIRE(acc && k > 0 && d > 0, "b2f_kmeans_fold: bad arguments");
+  KmAccLayout A = km_acc_layout(k, d);
+  char* ap = static_cast<char*>(acc);
+  size_t kd = (size_t)k * d;
+  int grid = (int)((kd + 255) / 256);
+  if (grid > b2f_sm_count() * 8) grid = b2f_sm_count() * 8;
+  km_fold_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(reinterpret_cast<double*>(ap + A.off_payload),
+                                                   reinterpret_cast<float*>(ap + A.off_rep),
+                                                   reinterpret_cast<unsigned long long*>(ap + A.off_cnt), k, d);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+extern "C" int b2f_kmeans_finalize(const double* payload, int k, int d, double tol, double* centers, int32_t* status,
+                                   double* status_f64, b2f_stream_t stream) {
+  B2F_REQUIRE(payload && centers && status && status_f64 && k > 0 && d > 0, "b2f_kmeans_finalize: bad arguments");
+  km_finalize_init_kernel<<<1, 1, 0, b2f_cs(stream)>>>(payload, k, d, status, status_f64);
+  int grid = (k + 7) / 8;
+  km_finalize_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(payload, k, d, tol * tol, centers, status, status_f64);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+extern "C" int b2f_kmeans_predict(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k,
+                                  int32_t* labels, float* dist2, int algo, b2f_stream_t stream) {
+  B2F_REQUIRE(X && prep && (labels || dist2), "b2f_kmeans_predict: null pointer");
+  B2F_REQUIRE(n >= 0 && d > 0 && k > 0 && ld >= d && ld % 4 == 0, "b2f_kmeans_predict: need ld >= d, ld %% 4 == 0");
+  if (n == 0) return B2F_OK;
+  KmPrepLayout P = km_prep_layout(k, d);
+  const char* pp = static_cast<const char*>(prep);
+  algo = km_pick_algo(algo, k, d, ld, nullptr);
+  if (dist2) algo = B2F_KM_GENERIC;  // exact distances come from the direct-form kernel
+  if (algo == B2F_KM_TC3 || algo == B2F_KM_TC1) {
+    B2F_REQUIRE(km_tc_supported(k, d, ld), "b2f_kmeans_predict: tensor-core path needs d %% 32 == 0, d <= 256, k %% 128 == 0");
+    return km_tc_step(X, n, d, ld, prep, k, nullptr, labels, algo == B2F_KM_TC3 ? 3 : 1, false, b2f_cs(stream));
+  }
+  return km_generic_launch(X, n, d, ld, nullptr, reinterpret_cast<const float*>(pp + P.off_c32), k, nullptr, nullptr,
+                           labels, dist2, false, b2f_cs(stream));
+}

@@ -1,0 +1,188 @@
+// K1 loader: ordered feature columns -> row-major fp32 tiles, plus column statistics.
+// Replaces VectorAssembler.transform (reference: orangecontrib/spark/widgets/ml/spark_ml_dataset.py:575-576)
+// and the Summarizer pass behind StandardScaler / LogisticRegression (SURVEY.md A.1, A.3 pass 0, A.6).
+#include "common.cuh"
+
+#define PK_ROWS 64
+#define PK_COLS 32
+
+__device__ __forceinline__ float load_as_f32(const void* p, int dtype, int64_t i) {
+  switch (dtype) {
+    case B2F_F32: return __ldg(reinterpret_cast<const float*>(p) + i);
+    case B2F_F64: return __double2float_rn(__ldg(reinterpret_cast<const double*>(p) + i));
+    case B2F_I32: return (float)(double)__ldg(reinterpret_cast<const int32_t*>(p) + i);
+    case B2F_I64: return (float)(double)__ldg(reinterpret_cast<const long long*>(p) + i);
+    default: return (float)__ldg(reinterpret_cast<const unsigned char*>(p) + i);
+  }
+}
+
+// CTA = 256 threads, tile = 64 rows x 32 columns.  Reads run along N inside each column (coalesced),
+// the tile is transposed through padded shared memory, and rows leave as 16-byte stores.
+__global__ void __launch_bounds__(256) pack_columns_kernel(const void* const* __restrict__ cols,
+                                                           const int32_t* __restrict__ dtypes, int d, int64_t n,
+                                                           float* __restrict__ X, int64_t ld, int32_t* bad_flag) {
+  __shared__ float tile[PK_ROWS][PK_COLS + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t row_tiles = (n + PK_ROWS - 1) / PK_ROWS;
+  const int col_tiles = (int)((ld + PK_COLS - 1) / PK_COLS);
+  const int64_t tiles = row_tiles * col_tiles;
+  bool bad = false;
+  for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const int64_t r0 = (t / col_tiles) * PK_ROWS;
+    const int c0 = (int)(t % col_tiles) * PK_COLS;
+#pragma unroll
+    for (int cc = 0; cc < PK_COLS / 8; ++cc) {
+      const int cl = warp + cc * 8, c = c0 + cl;
+      const void* p = nullptr;
+      int dt = 0;
+      if (c < d) {
+        p = cols[c];
+        dt = dtypes[c];
+      }
+#pragma unroll
+      for (int rr = 0; rr < PK_ROWS / 32; ++rr) {
+        const int rl = lane + rr * 32;
+        const int64_t r = r0 + rl;
+        float v = 0.f;
+        if (p && r < n) {
+          v = load_as_f32(p, dt, r);
+          bad |= !isfinite(v);
+        }
+        tile[rl][cl] = v;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int rr = 0; rr < PK_ROWS / 32; ++rr) {
+      const int rl = (threadIdx.x >> 3) + rr * 32;
+      const int c4 = (threadIdx.x & 7) * 4;
+      const int64_t r = r0 + rl;
+      if (r < n && c0 + c4 < ld) {
+        float4 o = make_float4(tile[rl][c4], tile[rl][c4 + 1], tile[rl][c4 + 2], tile[rl][c4 + 3]);
+        *reinterpret_cast<float4*>(X + r * ld + c0 + c4) = o;
+      }
+    }
+    __syncthreads();
+  }
+  if (bad_flag && bad) atomicExch(bad_flag, 1);
+}
+
+// grid.y = chunks of 256 columns; CTA = 256 threads = 64 float4 column groups x 4 row lanes.
+__global__ void __launch_bounds__(256) colstats_kernel(const float* __restrict__ X, int64_t n, int d, int64_t ld,
+                                                       const float* __restrict__ w, const float* __restrict__ shift,
+                                                       double* __restrict__ out) {
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  const int c = (blockIdx.y * 64 + tx) * 4;
+  const bool active = c < d;
+  float sh[4] = {0.f, 0.f, 0.f, 0.f};
+  if (active && shift)
+    for (int j = 0; j < 4; ++j)
+      if (c + j < d) sh[j] = shift[c + j];
+  double s1[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0}, sw = 0, sw2 = 0;
+  for (int64_t r = (int64_t)blockIdx.x * 4 + ty; r < n; r += (int64_t)gridDim.x * 4) {
+    const float wi = w ? w[r] : 1.f;
+    if (active) {
+      const float4 v = ldg_stream(reinterpret_cast<const float4*>(X + r * ld + c));
+      const float xs[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const double t = (double)xs[j] - (double)sh[j];
+        const double wt = (double)wi * t;
+        s1[j] += wt;
+        s2[j] += wt * t;
+      }
+    }
+    if (blockIdx.y == 0 && tx == 0) {
+      sw += (double)wi;
+      sw2 += (double)wi * (double)wi;
+    }
+  }
+  __shared__ double red[4][64][8];
+  __shared__ double redw[4][2];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    red[ty][tx][j] = s1[j];
+    red[ty][tx][4 + j] = s2[j];
+  }
+  if (tx == 0) {
+    redw[ty][0] = sw;
+    redw[ty][1] = sw2;
+  }
+  __syncthreads();
+  if (ty == 0 && active) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (c + j < d) {
+        atomicAdd(out + c + j, red[0][tx][j] + red[1][tx][j] + red[2][tx][j] + red[3][tx][j]);
+        atomicAdd(out + d + c + j, red[0][tx][4 + j] + red[1][tx][4 + j] + red[2][tx][4 + j] + red[3][tx][4 + j]);
+      }
+  }
+  if (blockIdx.y == 0 && threadIdx.x == 0) {
+    atomicAdd(out + 2 * d, redw[0][0] + redw[1][0] + redw[2][0] + redw[3][0]);
+    atomicAdd(out + 2 * d + 1, redw[0][1] + redw[1][1] + redw[2][1] + redw[3][1]);
+  }
+}
+
+__global__ void __launch_bounds__(256) label_hist_kernel(const float* __restrict__ y, const float* __restrict__ w,
+                                                         int64_t n, int nbins, double* __restrict__ hist,
+                                                         int32_t* bad_flag) {
+  extern __shared__ double sh[];
+  for (int i = threadIdx.x; i < nbins; i += blockDim.x) sh[i] = 0.0;
+  __syncthreads();
+  bool bad = false;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = y[i];
+    const int c = (int)v;
+    if (!(v >= 0.f) || (float)c != v || c >= nbins) {
+      bad = true;
+      continue;
+    }
+    atomicAdd(&sh[c], w ? (double)w[i] : 1.0);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < nbins; i += blockDim.x)
+    if (sh[i] != 0.0) atomicAdd(hist + i, sh[i]);
+  if (bad_flag && bad) atomicExch(bad_flag, 1);
+}
+
+extern "C" int b2f_pack_columns(const void* const* col_ptrs_dev, const int32_t* col_dtypes_dev, int d, int64_t n,
+                                float* X, int64_t ld, int32_t* bad_flag, b2f_stream_t stream) {
+  B2F_REQUIRE(col_ptrs_dev && col_dtypes_dev && X, "b2f_pack_columns: null pointer");
+  B2F_REQUIRE(d > 0 && n >= 0 && ld >= d && ld % 4 == 0, "b2f_pack_columns: need d > 0, ld >= d, ld %% 4 == 0");
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_pack_columns: X must be 16-byte aligned");
+  if (n == 0) return B2F_OK;
+  int64_t tiles = ((n + PK_ROWS - 1) / PK_ROWS) * ((ld + PK_COLS - 1) / PK_COLS);
+  int64_t cap = (int64_t)b2f_sm_count() * 8;
+  int grid = (int)(tiles < cap ? tiles : cap);
+  pack_columns_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(col_ptrs_dev, col_dtypes_dev, d, n, X, ld, bad_flag);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+extern "C" int b2f_colstats(const float* X, int64_t n, int d, int64_t ld, const float* w, const float* shift,
+                            double* out, b2f_stream_t stream) {
+  B2F_REQUIRE(X && out, "b2f_colstats: null pointer");
+  B2F_REQUIRE(d > 0 && n >= 0 && ld >= d && ld % 4 == 0, "b2f_colstats: need d > 0, ld >= d, ld %% 4 == 0");
+  if (n == 0) return B2F_OK;
+  dim3 grid;
+  grid.y = (d + 255) / 256;
+  int64_t want = (n + 3) / 4;
+  int64_t cap = (int64_t)b2f_sm_count() * 8 / grid.y + 1;
+  grid.x = (unsigned)(want < cap ? want : cap);
+  colstats_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(X, n, d, ld, w, shift, out);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+extern "C" int b2f_label_hist(const float* y, const float* w, int64_t n, int n_bins, double* hist, int32_t* bad_flag,
+                              b2f_stream_t stream) {
+  B2F_REQUIRE(y && hist, "b2f_label_hist: null pointer");
+  B2F_REQUIRE(n_bins > 0 && n_bins <= 4096 && n >= 0, "b2f_label_hist: n_bins must be in [1, 4096]");
+  if (n == 0) return B2F_OK;
+  int64_t want = (n + 255) / 256;
+  int64_t cap = (int64_t)b2f_sm_count() * 4;
+  int grid = (int)(want < cap ? want : cap);
+  label_hist_kernel<<<grid, 256, n_bins * sizeof(double), b2f_cs(stream)>>>(y, w, n, n_bins, hist, bad_flag);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
