@@ -1,0 +1,374 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json metric: KMeans Lloyd iterations/s on 100M x 128 fp32, k = 1024
+(configs[1]) plus LR loss+gradient passes/s on 50M x 256 (configs[2]), rows sharded over N B200s.
+
+  python bench.py --gpus N --steps K --warmup W          # this repo's CUDA path (one JSON line)
+  python bench.py --impl reference ...                   # CPU restatement on the host cores
+
+A "step" is one full Lloyd iteration: assignment + accumulation kernel, fold, all-reduce of
+[sums|counts|cost], centre update and operand re-preparation.  Inputs are synthetic
+(Philox, generated on device, seed 20240611) and far larger than L2 (51.2 GB vs 126 MB).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "orange3-spark_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+SEED = 20240611
+KM = dict(n=100_000_000, d=128, k=1024, comps=1024, center_scale=2.0)
+LR = dict(n=50_000_000, d=256)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows", type=int, default=0, help="DEV ONLY: override the row count (marks the line reduced)")
+    ap.add_argument("--lr-rows", type=int, default=0, help="DEV ONLY: override the LR row count")
+    ap.add_argument("--algo", type=int, default=0, help="B2F_KM_* code (0 = auto)")
+    ap.add_argument("--no-e2e", action="store_true", help="DEV ONLY: skip the host-buffer end-to-end leg")
+    ap.add_argument("--no-lr", action="store_true", help="DEV ONLY: skip the LR leg")
+    ap.add_argument("--no-cpu", action="store_true", help="DEV ONLY: skip the cpu_baseline leg")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(hbm=p["hbm_gbs"], tensor=p["bf16_tflops_sustained"], tensor_burst=p["bf16_tflops"], src="measured")
+    except Exception:
+        return dict(hbm=6650.0, tensor=1400.0, tensor_burst=1590.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([s.strip() for s in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.25)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for nm, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def reference_arm(args):
+    """CPU restatement (oracle, numpy/OpenBLAS on all host threads) of one Lloyd iteration on a
+    bounded sample of the same workload, extrapolated linearly in N (every unit is linear in N)."""
+    import numpy as np
+
+    import oracle
+
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    n_total = args.rows or KM["n"]
+    n_s = min(n_total, 400_000)
+    rng = np.random.default_rng(SEED)
+    mu = (rng.standard_normal((KM["comps"], KM["d"])) * KM["center_scale"]).astype(np.float32)
+    X = (mu[rng.integers(0, KM["comps"], n_s)] + rng.standard_normal((n_s, KM["d"]), dtype=np.float32))
+    C = X[rng.choice(n_s, KM["k"], replace=False)].astype(np.float64)
+    X64 = X.astype(np.float64)
+    for _ in range(args.warmup):
+        oracle.kmeans_step(X64, C)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        _, _, sums, counts = oracle.kmeans_step(X64, C)
+        C, _ = oracle.kmeans.kmeans_update(C, sums, counts, 0.0)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = 1.0 / (dt * n_total / n_s)
+    sample = ("%d of %d rows (same d, k, mixture; numpy RNG), one Lloyd iteration per step, linear extrapolation "
+              "in N; CPU restatement, not Spark" % (n_s, n_total))
+    line = {"impl": "reference", "metric": "kmeans_lloyd_iter_per_s", "value": value, "unit": "iter/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3 * n_total / n_s,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(n_total, args.gpus),
+            "cpu_baseline": {"value": value, "unit": "iter/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n_total, gpus):
+    return {"workload": "KMeans k=1024 maxIter=20 on synthetic %dx128 fp32, fixed initialModel (BASELINE configs[1])"
+                        % n_total, "rows": n_total, "d": KM["d"], "k": KM["k"], "parallelism": "rows/%d" % gpus,
+            "l2": "inputs (%.1f GB per GPU) far exceed the 126 MB L2; no flush needed"
+                  % (n_total * KM["d"] * 4 / gpus / 1e9)}
+
+
+def b200_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from b200fit import _native as N
+    from b200fit._kmeans_init import init_random
+    from b200fit.classification import CudaLogRegEngine
+    from b200fit.clustering import CudaLloydEngine, KMeans
+    from b200fit.dist import Comm, shard_bounds
+    from b200fit.feature import VectorAssembler
+    from b200fit.frame import ColumnarFrame, DeviceMatrix
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    comm = Comm()
+    L = N.lib()
+    pk = peaks()
+    n_total = args.rows or KM["n"]
+    d, k = KM["d"], KM["k"]
+    lo, hi = shard_bounds(n_total, rank, world)
+    n = hi - lo
+
+    def sync_all():
+        comm.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        comm.all_reduce_max(t)
+        return float(t.item())
+
+    # ---------------- KMeans: device-resident inputs ----------------
+    Xt = torch.empty((n, d), dtype=torch.float32, device=dev)
+    N.check(L.b2f_synth_mixture(N.ptr(Xt), n, lo, d, d, SEED, KM["comps"], KM["center_scale"], None, N.stream_ptr()),
+            "b2f_synth_mixture")
+    X = DeviceMatrix(Xt, d, lo)
+    C0 = init_random(X, n_total, k, SEED, comm)  # 1024 seeded distinct data rows
+    eng = CudaLloydEngine(X, k, algo=args.algo)
+    eng.set_centers(C0)
+
+    def iteration(ev=None):
+        if ev:
+            s = N.stream_ptr()
+            N.check(L.b2f_kmeans_acc_zero(N.ptr(eng.acc), k, d, s), "acc_zero")
+            ev[0].record()
+            N.check(L.b2f_kmeans_step(N.ptr(Xt), n, d, d, None, N.ptr(eng.prep), k, N.ptr(eng.acc), None, args.algo, s),
+                    "step")
+            ev[1].record()
+            N.check(L.b2f_kmeans_fold(N.ptr(eng.acc), k, d, s), "fold")
+            eng.launches += 2
+            payload = eng.payload
+        else:
+            payload = eng.step()
+        comm.all_reduce_sum(payload)
+        eng.finalize_async(payload, 0.0)
+
+    for _ in range(args.warmup):
+        iteration()
+    sync_all()
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = eng.launches
+    with ClockSampler(local) as clk:
+        sync_all()
+        t0.record()
+        for i in range(args.steps):
+            iteration(kev[i])
+        t1.record()
+        sync_all()
+    ms_step = max_over_ranks(t0.elapsed_time(t1)) / args.steps
+    kern_ms = sum(a.elapsed_time(b) for a, b in kev) / args.steps
+    launches = eng.launches - launches0
+    cost_after = float(eng.status_f64.cpu()[1].item())
+    value = 1e3 / ms_step
+    flops = 2.0 * n * k * d
+    achieved = flops / (kern_ms * 1e-3) / 1e12
+    line = {"metric": "kmeans_lloyd_iter_per_s", "value": value, "unit": "iter/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "tf32x3->f32 (sums/cost folded in f64)",
+            "data": "synthetic", "config": workload_config(n_total, world), "gpu_launches": launches,
+            "clocks": clk.summary(),
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["tensor"], "unit": "TFLOP/s",
+                         "frac": achieved / pk["tensor"], "traffic": None, "kernel": "b2f_kmeans_step",
+                         "kernel_ms": kern_ms, "peak_source": pk["src"] + " bf16 sustained (no TF32 figure measured)",
+                         "algorithmic_flops_per_launch": flops},
+            "check": {"cost_after_last_timed_iter": cost_after}}
+    if args.rows:
+        line["reduced"] = True
+
+    # ---------------- end to end through the public API with HOST buffers ----------------
+    if not args.no_e2e:
+        line["e2e"] = e2e_leg(args, torch, Xt, C0, n, d, k, comm, ColumnarFrame, VectorAssembler, KMeans,
+                              max_over_ranks, sync_all)
+    del eng, X, Xt
+    torch.cuda.empty_cache()
+
+    # ---------------- LR binary (configs[2]): one fused loss+gradient pass per step ----------------
+    if not args.no_lr:
+        line["lr"] = lr_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, DeviceMatrix, shard_bounds,
+                            max_over_ranks, sync_all)
+    if rank == 0 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(n_total)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def e2e_leg(args, torch, Xt, C0, n, d, k, comm, ColumnarFrame, VectorAssembler, KMeans, max_over_ranks, sync_all):
+    """Same metric through the reference-facing call chain with HOST columns in pinned memory:
+    VectorAssembler.transform (H2D + pack) -> KMeans(maxIter=M, initialModel).fit -> centres to host."""
+    import psutil
+
+    iters = 20
+    n_full = n
+    avail = psutil.virtual_memory().available
+    if n * d * 4 * 1.25 > avail:  # never drive the box out of host memory: shrink and SAY so
+        n = int(avail * 0.6 / (d * 4))
+    cols = {}
+    for j in range(d):
+        h = torch.empty(n, dtype=torch.float32, pin_memory=True)
+        h.copy_(Xt[:n, j])
+        cols["f%d" % j] = h
+    torch.cuda.synchronize()
+    df = ColumnarFrame(cols)
+    va = VectorAssembler(inputCols=["f%d" % j for j in range(d)], outputCol="features", handleInvalid="keep")
+    km = KMeans(k=k, maxIter=iters, tol=0.0, initialModel=C0)
+    km._algo = args.algo
+    sync_all()
+    t0 = time.perf_counter()
+    model = km.fit(va.transform(df))
+    centers = model.clusterCenters()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=Xt.device)
+    comm.all_reduce_max(t)
+    dt = float(t.item())
+    assert len(centers) == k and model.summary.numIter == iters
+    scale = n / float(n_full)  # 1.0 unless host RAM forced a smaller e2e sample
+    return {"value": iters / dt * scale, "unit": "iter/s", "rows_used": n, "rows_full": n_full,
+            "host_ram_limited": n != n_full, "h2d_bytes_per_step": n * d * 4 / iters,
+            "d2h_bytes_per_step": (k * d * 8 + 24 * iters) / iters, "iterations": iters, "seconds": dt,
+            "what": "VectorAssembler.transform(host pinned columns) + KMeans.fit(maxIter=20, tol=0) + clusterCenters(); "
+                    "the one H2D of X is amortised over the fit's 20 iterations"}
+
+
+def lr_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, DeviceMatrix, shard_bounds,
+           max_over_ranks, sync_all):
+    import numpy as np
+
+    n_total = args.lr_rows or (LR["n"] if not args.rows else max(args.rows // 2, 1))
+    d = LR["d"]
+    lo, hi = shard_bounds(n_total, rank, world)
+    n = hi - lo
+    rng = np.random.default_rng(SEED)
+    scale = np.exp(rng.uniform(np.log(0.5), np.log(2.0), size=d)).astype(np.float32)
+    w_true = (rng.standard_normal(d) / np.sqrt(d)).astype(np.float32)
+    Xt = torch.empty((n, d), dtype=torch.float32, device=dev)
+    y = torch.empty(n, dtype=torch.float32, device=dev)
+    N.check(L.b2f_synth_logistic(N.ptr(Xt), N.ptr(y), n, lo, d, d, SEED + 1, N.ptr(torch.from_numpy(scale).to(dev)),
+                                 N.ptr(torch.from_numpy(w_true).to(dev)),
+                                 N.ptr(torch.tensor([0.3], dtype=torch.float32, device=dev)), 2, N.stream_ptr()),
+            "b2f_synth_logistic")
+    eng = CudaLogRegEngine(DeviceMatrix(Xt, d, lo), y, None, 2)
+    beta = (rng.standard_normal(d) * 0.05 / scale)
+    eng.beta.copy_(torch.from_numpy(beta).to(dev))
+
+    def one_pass():
+        comm.all_reduce_sum(eng.lossgrad_device())
+
+    for _ in range(args.warmup):
+        one_pass()
+    sync_all()
+    steps = max(args.steps, 5)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(steps):
+        one_pass()
+    t1.record()
+    sync_all()
+    ms = max_over_ranks(t0.elapsed_time(t1)) / steps
+    p = eng.out.cpu().numpy()
+    bytes_pass = n * (4.0 * d + 4.0)
+    gbs = bytes_pass / (ms * 1e-3) / 1e9
+    return {"metric": "lr_binary_lossgrad_pass_per_s", "value": 1e3 / ms, "unit": "pass/s", "ms_per_step": ms,
+            "config": {"workload": "binary LogisticRegression loss+gradient pass on synthetic %dx256 fp32 "
+                                   "(BASELINE configs[2])" % n_total, "rows": n_total, "d": d},
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
+                         "traffic": None, "kernel": "lr_binary_kernel", "algorithmic_bytes_per_launch": bytes_pass,
+                         "peak_source": pk["src"]},
+            "check": {"loss": float(p[d + 1] / p[d + 2]), "weight_sum": float(p[d + 2])}}
+
+
+def cpu_baseline(n_total):
+    """Oracle ('port') timed on the host cores on a bounded sample (about 10-30 s of CPU work)."""
+    import numpy as np
+
+    import oracle
+
+    n_s = 400_000
+    rng = np.random.default_rng(SEED)
+    mu = (rng.standard_normal((KM["comps"], KM["d"])) * KM["center_scale"]).astype(np.float32)
+    X = (mu[rng.integers(0, KM["comps"], n_s)] + rng.standard_normal((n_s, KM["d"]), dtype=np.float32)).astype(np.float64)
+    C = X[rng.choice(n_s, KM["k"], replace=False)].copy()
+    oracle.kmeans_step(X[:50_000], C)
+    t0 = time.perf_counter()
+    reps = 3
+    for _ in range(reps):
+        oracle.kmeans_step(X, C)
+    dt = (time.perf_counter() - t0) / reps
+    return {"value": 1.0 / (dt * n_total / n_s), "unit": "iter/s", "cores": os.cpu_count() or 1, "kind": "port",
+            "sample": "%d of %d rows, %d Lloyd assignment+accumulate passes, linear extrapolation in N; numpy/OpenBLAS "
+                      "fp64 CPU restatement of MLlib (Spark local[N] unavailable on this box)" % (n_s, n_total, reps)}
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        reference_arm(a)
+    else:
+        b200_arm(a)

@@ -1,0 +1,48 @@
+"""Row-sharded data parallelism: one process per GPU, torch.distributed for plumbing.
+
+SURVEY.md 8(e): rows are partitioned contiguously (shard r of G owns rows
+[r*N/G, (r+1)*N/G)); centres / coefficients are replicated; the ONLY per-unit
+exchange is one sum-all-reduce of the fp64 payload ([sums|counts|cost|n] per Lloyd
+iteration, [grad|loss|weightSum] per LR pass).  This replaces Spark's
+broadcast + reduceByKey / treeAggregate behind fit()
+(reference call site: orangecontrib/spark/base/spark_ml_estimator.py:22).
+Every rank then runs the identical finalize / optimizer step: no root, no broadcast.
+"""
+
+
+def shard_bounds(n_total, rank, world):
+    """Rows [lo, hi) owned by `rank`."""
+    return (n_total * rank) // world, (n_total * (rank + 1)) // world
+
+
+class Comm:
+    """Thin wrapper so the fit loops do not care whether a process group exists."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+
+        self._dist = dist
+        self.active = dist.is_available() and dist.is_initialized()
+        self.group = group
+        self.rank = dist.get_rank(group) if self.active else 0
+        self.world = dist.get_world_size(group) if self.active else 1
+
+    def all_reduce_sum(self, t):
+        """In-place sum over ranks of a (device or host) tensor; no-op for world 1."""
+        if self.active and self.world > 1:
+            self._dist.all_reduce(t, op=self._dist.ReduceOp.SUM, group=self.group)
+        return t
+
+    def all_reduce_max(self, t):
+        if self.active and self.world > 1:
+            self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX, group=self.group)
+        return t
+
+    def broadcast(self, t, src=0):
+        if self.active and self.world > 1:
+            self._dist.broadcast(t, src=src, group=self.group)
+        return t
+
+    def barrier(self):
+        if self.active and self.world > 1:
+            self._dist.barrier(group=self.group)

@@ -28,7 +28,7 @@ __device__ __forceinline__ u32x4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
 }
 
 // 1 / sqrt(8 * (65536^2 - 1) / 12) rounded to fp32
-#define IH_SCALE 1.8688122e-05f
+#define IH_SCALE 0x1.3988e2p-16f
 
 __device__ __forceinline__ float ih_normal(u32x4 r) {
   int s = (int)(r.x & 0xffffu) + (int)(r.x >> 16) + (int)(r.y & 0xffffu) + (int)(r.y >> 16) +

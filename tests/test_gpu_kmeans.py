@@ -1,0 +1,228 @@
+"""GPU parity tests for the loader and KMeans path, called through the C ABI and compared with
+the CPU oracle on identical seeded inputs.  Tolerances (north_star): labels equal except rows
+whose oracle top-2 distance gap is < 1e-6 relative; centres / cost within 1e-5 relative."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+
+SEED = 20240611
+
+
+def _imports():
+    from b200fit import _native as N
+    import gpu_util as G
+
+    return N, G
+
+
+def test_synth_mixture_is_bit_identical_to_cpu_mirror():
+    N, G = _imports()
+    L = N.lib()
+    n, d, ld, row0 = 3001, 10, 12, 123456789012
+    X = torch.empty((n, ld), dtype=torch.float32, device=G.dev())
+    cs = np.linspace(0.5, 2.0, d).astype(np.float32)
+    cs_d = torch.from_numpy(cs).to(G.dev())
+    N.check(L.b2f_synth_mixture(N.ptr(X), n, row0, d, ld, SEED, 7, 2.0, N.ptr(cs_d), G.stream()), "synth")
+    got = X.cpu().numpy()
+    want = synth.mixture(n, row0, d, SEED, 7, 2.0, cs)
+    assert np.array_equal(got[:, :d], want)
+    assert (got[:, d:] == 0).all()
+
+
+@pytest.mark.parametrize("n", [0, 1, 63, 64, 1000, 4099])
+def test_pack_columns_matches_vector_assembler(n):
+    N, G = _imports()
+    from b200fit.feature import pack_columns
+
+    rng = np.random.default_rng(n)
+    cols = [rng.normal(size=n), rng.normal(size=n).astype(np.float32), rng.integers(-5, 5, size=n).astype(np.int32),
+            rng.integers(-2 ** 40, 2 ** 40, size=n), rng.uniform(size=n) < 0.5, rng.normal(size=n) * 1e3,
+            rng.integers(0, 255, size=n).astype(np.uint8)]
+    want = oracle.assemble(cols).astype(np.float32)  # fp64 concat rounded to fp32
+    X = pack_columns(cols)
+    assert X.d == 7 and X.ld == 8 and X.n == n
+    got = X.data.cpu().numpy()
+    assert np.array_equal(got[:, :7], want.reshape(n, 7))
+    assert (got[:, 7:] == 0).all()
+    # device-resident columns take the single-launch path
+    Xd = pack_columns([torch.from_numpy(np.ascontiguousarray(c)).to(G.dev()) for c in cols])
+    assert np.array_equal(Xd.data.cpu().numpy(), got)
+
+
+def test_pack_columns_chunked_host_pipeline_and_nan_policy():
+    N, G = _imports()
+    from b200fit.feature import pack_columns
+
+    rng = np.random.default_rng(5)
+    n = 10007
+    cols = [rng.normal(size=n) for _ in range(5)]
+    X = pack_columns(cols, chunk_rows=1024)
+    assert np.array_equal(X.data.cpu().numpy()[:, :5], oracle.assemble(cols).astype(np.float32))
+    cols[2][77] = np.nan
+    with pytest.raises(ValueError):
+        pack_columns(cols)
+    Xk = pack_columns(cols, handle_invalid="keep")
+    assert np.isnan(Xk.data[77, 2].item())
+    with pytest.raises(ValueError):
+        pack_columns([np.zeros(3), np.zeros(4)])
+
+
+def test_colstats_matches_summarizer():
+    N, G = _imports()
+    from b200fit.feature import column_stats, pack_columns
+
+    rng = np.random.default_rng(9)
+    n, d = 5003, 13
+    Xh = (rng.normal(size=(n, d)) * rng.uniform(0.1, 10, size=d) + rng.normal(size=d) * 50).astype(np.float32)
+    Xh[:, 4] = 3.25  # zero-variance column
+    w = rng.uniform(0.5, 2.0, size=n).astype(np.float32)
+    X = pack_columns([Xh])
+    mean, std, W = column_stats(X, torch.from_numpy(w).to(G.dev()))
+    rm, rs, rW = oracle.summarize(Xh.astype(np.float64), w.astype(np.float64))
+    np.testing.assert_allclose(mean, rm, rtol=1e-10, atol=1e-10)
+    np.testing.assert_allclose(std, rs, rtol=1e-9, atol=1e-9)
+    assert std[4] == 0.0 and W == pytest.approx(rW, rel=1e-12)
+    mean1, std1, W1 = column_stats(X)
+    rm1, rs1, _ = oracle.summarize(Xh.astype(np.float64))
+    np.testing.assert_allclose(std1, rs1, rtol=1e-9, atol=1e-9)
+    assert W1 == n
+
+
+def _mixture(n, d, k_true, seed=SEED):
+    return synth.mixture(n, 0, d, seed, k_true, 2.0)
+
+
+KM_SHAPES = [  # n, d, k
+    (1, 3, 1), (257, 1, 2), (1000, 3, 8), (5000, 16, 8), (4097, 17, 5), (3000, 64, 255), (2048, 128, 256),
+    (1500, 130, 33), (777, 512, 16),
+]
+
+
+@pytest.mark.parametrize("n,d,k", KM_SHAPES)
+def test_kmeans_generic_step_matches_oracle(n, d, k):
+    N, G = _imports()
+    Xh = _mixture(n, d, max(k, 2))
+    rng = np.random.default_rng(n + d + k)
+    C = Xh[rng.choice(n, size=min(k, n), replace=False)].astype(np.float64)
+    if C.shape[0] < k:
+        C = np.concatenate([C, rng.normal(size=(k - C.shape[0], d))])
+    X, _, ld = G.upload_matrix(Xh)
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_GENERIC)
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
+    ok = G.allowed_label_mismatch(ref_d, ref_second)
+    bad = (labels != ref_lab) & ~ok
+    assert not bad.any(), "%d label mismatches outside the 1e-6 gap band" % bad.sum()
+    _, rcost, rsums, rcounts = oracle.kmeans_step(Xh.astype(np.float64), C)
+    if (labels == ref_lab).all():
+        np.testing.assert_array_equal(counts, rcounts)
+        scale = np.abs(Xh).astype(np.float64).sum(axis=0).max() / max(k, 1) + 1.0
+        np.testing.assert_allclose(sums, rsums, rtol=1e-5, atol=1e-6 * scale)
+    assert cost == pytest.approx(rcost, rel=1e-5, abs=1e-9)
+    assert nrows == n and counts.sum() == n
+
+
+def test_kmeans_ties_go_to_lowest_index_and_weights():
+    N, G = _imports()
+    Xh = np.array([[0, 0], [1, 1], [9, 8], [8, 9], [4.5, 4.5]], dtype=np.float32)
+    C = np.array([[0.5, 0.5], [8.5, 8.5], [0.5, 0.5]])  # centre 2 duplicates centre 0
+    X, d, ld = G.upload_matrix(Xh)
+    labels, sums, counts, cost, _ = G.kmeans_step_raw(X, 5, d, ld, C, N.KM_GENERIC)
+    assert labels.tolist()[:4] == [0, 0, 1, 1] and counts[2] == 0
+    w = torch.tensor([1, 2, 3, 4, 0], dtype=torch.float32, device=G.dev())
+    _, sums_w, counts_w, cost_w, wsum = G.kmeans_step_raw(X, 5, d, ld, C, N.KM_GENERIC, w=w)
+    _, rc, rs, rn = oracle.kmeans_step(Xh.astype(np.float64), C, w=np.array([1, 2, 3, 4, 0.0]))
+    np.testing.assert_allclose(sums_w, rs, rtol=1e-6)
+    np.testing.assert_allclose(counts_w, rn)
+    assert cost_w == pytest.approx(rc, rel=1e-6) and wsum == 10
+
+
+@pytest.mark.parametrize("n,d,k,iters", [(20000, 16, 8, 20), (6000, 32, 64, 8), (5000, 128, 256, 4)])
+def test_kmeans_fit_per_iteration_parity(n, d, k, iters):
+    """Estimator.fit with a fixed initialModel: centres and cost after EVERY iteration vs oracle."""
+    N, G = _imports()
+    from b200fit.clustering import CudaLloydEngine
+    from b200fit.dist import Comm
+    from b200fit.feature import pack_columns
+
+    Xh = _mixture(n, d, k)
+    rng = np.random.default_rng(1)
+    C0 = Xh[rng.choice(n, size=k, replace=False)].astype(np.float64)
+    ref = oracle.kmeans_lloyd(Xh.astype(np.float64), C0, max_iter=iters, tol=0.0)
+    X = pack_columns([Xh])
+    eng = CudaLloydEngine(X, k, algo=N.KM_GENERIC)
+    eng.set_centers(C0)
+    comm = Comm()
+    for it in range(iters):
+        payload = eng.step()
+        comm.all_reduce_sum(payload)
+        conv, cost = eng.finalize(payload, 0.0)
+        C = eng.get_centers()
+        scale = np.abs(ref["centers_hist"][it]).max()
+        np.testing.assert_allclose(C, ref["centers_hist"][it], rtol=1e-5, atol=1e-5 * scale)
+        assert cost == pytest.approx(ref["cost_hist"][it], rel=1e-5)
+        np.testing.assert_array_equal(eng.get_counts(payload), ref["counts_hist"][it])
+
+
+def test_kmeans_empty_cluster_keeps_centre_and_convergence_flag():
+    N, G = _imports()
+    from b200fit.clustering import KMeans
+    from b200fit.frame import ColumnarFrame
+
+    rng = np.random.default_rng(3)
+    Xh = rng.normal(size=(500, 3)).astype(np.float32)
+    C0 = np.vstack([Xh[:3].astype(np.float64), [[100.0, 100.0, 100.0]]])
+    ref = oracle.kmeans_lloyd(Xh.astype(np.float64), C0, max_iter=50, tol=1e-4)
+    m = KMeans(k=4, maxIter=50, tol=1e-4, initialModel=C0).fit(ColumnarFrame({"features": Xh}))
+    C = np.array(m.clusterCenters())
+    np.testing.assert_array_equal(C[3], C0[3])
+    assert m.summary.numIter == ref["numIter"] and m.summary.converged
+    np.testing.assert_allclose(C, ref["centers"], rtol=1e-5, atol=1e-6)
+    assert m.summary.trainingCost == pytest.approx(ref["trainingCost"], rel=1e-5)
+    assert sum(m.summary.clusterSizes) == 500 and m.summary.clusterSizes[3] == 0
+
+
+def test_kmeans_widget_path_cfg1_shape():
+    """BASELINE config 1 path at reduced N: columns f0..f15 -> Dataset Builder (VectorAssembler) ->
+    KMeans widget 'Apply' with GUI text parameters -> Model Transformer."""
+    N, G = _imports()
+    import fake_widget as fw
+    import b200fit
+    from b200fit.frame import ColumnarFrame
+
+    n, d, k = 50000, 16, 8
+    Xh = synth.mixture(n, 0, d, SEED, 8, 3.0)
+    df = ColumnarFrame({"f%d" % j: Xh[:, j].astype(np.float64) for j in range(d)})
+    va = b200fit.feature.VectorAssembler(inputCols=["f%d" % j for j in range(d)], outputCol="features")
+    out_df = va.transform(df)
+    rng = np.random.default_rng(8)
+    C0 = Xh[rng.choice(n, size=k, replace=False)].astype(np.float64)
+    model = fw.press_apply(b200fit.clustering.KMeans, out_df, edits={"k": "8", "maxIter": "20", "tol": "1e-4"},
+                           objects={"initialModel": C0})
+    ref = oracle.kmeans_lloyd(Xh.astype(np.float64), C0, max_iter=20, tol=1e-4)
+    assert model.summary.numIter == ref["numIter"]
+    np.testing.assert_allclose(np.array(model.clusterCenters()), ref["centers"], rtol=1e-5, atol=1e-5)
+    pred = model.transform(out_df).col("prediction").cpu().numpy()
+    rl, rd, rs = oracle.kmeans_assign(Xh.astype(np.float64), ref["centers"], return_second=True)
+    assert not ((pred != rl) & ~G.allowed_label_mismatch(rd, rs)).any()
+    assert model.computeCost(out_df) == pytest.approx(float(rd.sum()), rel=1e-5)
+
+
+@pytest.mark.parametrize("mode", ["random", "k-means||"])
+def test_kmeans_init_modes_give_a_sane_clustering(mode):
+    N, G = _imports()
+    from b200fit.clustering import KMeans
+    from b200fit.frame import ColumnarFrame
+
+    Xh = synth.mixture(20000, 0, 8, SEED, 5, 6.0)
+    m = KMeans(k=5, initMode=mode, seed=7, maxIter=30).fit(ColumnarFrame({"features": Xh}))
+    C = np.array(m.clusterCenters())
+    assert C.shape == (5, 8) and np.isfinite(C).all()
+    if mode == "k-means||":  # well separated blobs: k-means|| must find all five
+        truth = synth.mixture_centers(8, SEED, 5, 6.0).astype(np.float64)
+        dmat = ((truth[:, None, :] - C[None, :, :]) ** 2).sum(-1)
+        assert (dmat.min(axis=1) < 0.1).all()

@@ -1,0 +1,179 @@
+"""GPU parity tests for the LogisticRegression path through the C ABI vs the CPU oracle.
+Tolerances (north_star): loss & gradient within 1e-5 relative at identical iterates;
+coefficients & objective history within 1e-5 relative per iteration under the optimizer."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _imports():
+    from b200fit import _native as N
+    import gpu_util as G
+
+    return N, G
+
+
+def _binary_data(n, d, seed, scale=True):
+    rng = np.random.default_rng(seed)
+    s = np.exp(rng.uniform(np.log(0.5), np.log(2.0), size=d)) if scale else np.ones(d)
+    X = (rng.normal(size=(n, d)) * s).astype(np.float32)
+    wt = rng.normal(size=d) / np.sqrt(d)
+    y = (rng.uniform(size=n) < 1 / (1 + np.exp(-(X @ wt + 0.3)))).astype(np.float32)
+    return X, y
+
+
+def _multi_data(n, d, K, seed):
+    rng = np.random.default_rng(seed)
+    X = (rng.normal(size=(n, d)) * np.exp(rng.uniform(np.log(0.5), np.log(2.0), size=d))).astype(np.float32)
+    Wt = rng.normal(size=(K, d)) / np.sqrt(d)
+    y = np.argmax(X @ Wt.T + rng.gumbel(size=(n, K)), axis=1).astype(np.float32)
+    return X, y
+
+
+def _grad_close(got, ref, rtol=1e-5):
+    scale = np.abs(ref).max() + 1e-30
+    np.testing.assert_allclose(got, ref, rtol=rtol, atol=rtol * scale)
+
+
+@pytest.mark.parametrize("n,d", [(1, 1), (5, 3), (1000, 16), (4099, 100), (3000, 256), (2000, 300), (1500, 640),
+                                 (900, 1024)])
+@pytest.mark.parametrize("weighted", [False, True])
+def test_lr_binary_lossgrad_matches_oracle(n, d, weighted):
+    N, G = _imports()
+    Xh, yh = _binary_data(n, d, n + d)
+    rng = np.random.default_rng(d)
+    wh = rng.uniform(0.5, 2.0, size=n).astype(np.float32) if weighted else None
+    X, _, ld = G.upload_matrix(Xh)
+    y = torch.from_numpy(yh).to(G.dev())
+    w = torch.from_numpy(wh).to(G.dev()) if weighted else None
+    for trial in range(3):
+        beta = rng.normal(size=d) * (0.0 if trial == 0 else 0.3 / np.sqrt(d)) * (trial ** 2)
+        b0 = float(rng.normal()) if trial else 0.0
+        loss, g, gb, W = G.lr_lossgrad_raw(X, y, w, n, d, ld, 2, beta, b0)
+        rl, rg, rgb = oracle.lr_binary_lossgrad(Xh, yh, wh, beta, b0, np.ones(d))
+        assert loss == pytest.approx(rl, rel=1e-5, abs=1e-9)
+        _grad_close(g[0], rg)
+        assert gb[0] == pytest.approx(rgb, rel=1e-5, abs=1e-5 * (np.abs(rg).max() + 1e-30) + 1e-9)
+        assert W == pytest.approx(n if wh is None else float(wh.astype(np.float64).sum()), rel=1e-12)
+
+
+@pytest.mark.parametrize("n,d,K", [(7, 3, 3), (1000, 16, 4), (3000, 100, 10), (2500, 512, 20), (1200, 257, 8),
+                                   (800, 700, 5), (600, 64, 32)])
+def test_lr_multinomial_lossgrad_matches_oracle(n, d, K):
+    N, G = _imports()
+    Xh, yh = _multi_data(n, d, K, n + d + K)
+    rng = np.random.default_rng(K)
+    wh = rng.uniform(0.5, 2.0, size=n).astype(np.float32)
+    X, _, ld = G.upload_matrix(Xh)
+    y = torch.from_numpy(yh).to(G.dev())
+    w = torch.from_numpy(wh).to(G.dev())
+    for trial in range(2):
+        B = rng.normal(size=(K, d)) * trial * 0.5 / np.sqrt(d)
+        b0 = rng.normal(size=K) * trial
+        for ww, wwh in ((None, None), (w, wh)):
+            loss, g, gb, W = G.lr_lossgrad_raw(X, y, ww, n, d, ld, K, B, b0)
+            rl, rg, rgb = oracle.lr_multinomial_lossgrad(Xh, yh, wwh, B, b0, np.ones(d))
+            assert loss == pytest.approx(rl, rel=1e-5)
+            _grad_close(g, rg, rtol=2e-5)
+            _grad_close(gb, rgb, rtol=2e-5)
+
+
+def _fit_both(Xh, yh, wh=None, **kw):
+    from b200fit.classification import LogisticRegression
+    from b200fit.frame import ColumnarFrame
+
+    cols = {"features": Xh, "label": yh.astype(np.float64)}
+    if wh is not None:
+        cols["wt"] = wh
+        kw["weightCol"] = "wt"
+    m = LogisticRegression(**kw).fit(ColumnarFrame(cols))
+    okw = dict(max_iter=kw.get("maxIter", 100), reg_param=kw.get("regParam", 0.0),
+               elastic_net=kw.get("elasticNetParam", 0.0), tol=kw.get("tol", 1e-6),
+               fit_intercept=kw.get("fitIntercept", True), standardization=kw.get("standardization", True),
+               family=kw.get("family", "auto"))
+    ref = oracle.lr_fit(Xh, yh.astype(np.int64), wh, return_states=True, **okw)
+    return m, ref
+
+
+def _check_trajectory(m, ref, rtol=1e-5):
+    h, rh = m.summary.objectiveHistory, ref["objectiveHistory"]
+    assert len(h) == len(rh) and m.summary.totalIterations == ref["totalIterations"]
+    np.testing.assert_allclose(h, rh, rtol=rtol)
+    for x, st in zip(m.summary.iterates, ref["states"]):
+        sc = np.abs(st["x"]).max() + 1e-12
+        np.testing.assert_allclose(x, st["x"], rtol=rtol, atol=rtol * sc)
+
+
+def test_lr_binary_fit_follows_oracle_trajectory():
+    Xh, yh = _binary_data(20000, 64, 11)
+    m, ref = _fit_both(Xh, yh, regParam=0.01, maxIter=15)
+    _check_trajectory(m, ref)
+    sc = np.abs(ref["coefficients"]).max()
+    np.testing.assert_allclose(m.coefficients, ref["coefficients"], rtol=1e-5, atol=1e-5 * sc)
+    assert m.intercept == pytest.approx(ref["intercept"], rel=1e-5, abs=1e-6)
+
+
+def test_lr_binary_fit_kat_weighted():
+    # pyspark doctest: coef (-1.0807265, -0.6462906), intercept 3.1127669
+    Xh = np.array([[0.0, 5.0], [1.0, 2.0], [2.0, 1.0], [3.0, 3.0]], dtype=np.float32)
+    yh = np.array([1, 0, 1, 0], dtype=np.float32)
+    m, ref = _fit_both(Xh, yh, np.array([1.0, 2.0, 3.0, 4.0], dtype=np.float32), regParam=0.01, tol=1e-12)
+    np.testing.assert_allclose(m.coefficients, [-1.08072651, -0.64629055], atol=5e-5)
+    assert m.intercept == pytest.approx(3.11276685, abs=1e-4)
+
+
+def test_lr_options_no_intercept_no_standardization_constant_column():
+    Xh, yh = _binary_data(5000, 12, 5)
+    Xh[:, 3] = 1.5  # constant column -> coefficient pinned to zero
+    for kw in (dict(fitIntercept=False, regParam=0.05, maxIter=10),
+               dict(standardization=False, regParam=0.05, maxIter=10)):
+        m, ref = _fit_both(Xh, yh, **kw)
+        _check_trajectory(m, ref)
+        assert m.coefficients[3] == 0.0
+
+
+def test_lr_multinomial_elastic_net_follows_oracle_trajectory():
+    """BASELINE config 4 shape at reduced N: 20 classes, elasticNetParam=0.5 => OWL-QN."""
+    Xh, yh = _multi_data(8000, 64, 20, 21)
+    m, ref = _fit_both(Xh, yh, regParam=0.01, elasticNetParam=0.5, family="multinomial", maxIter=12)
+    _check_trajectory(m, ref, rtol=2e-5)
+    assert m.coefficientMatrix.shape == (20, 64)
+    sc = np.abs(ref["coefficients"]).max()
+    np.testing.assert_allclose(m.coefficientMatrix, ref["coefficients"], rtol=2e-5, atol=2e-5 * sc)
+    np.testing.assert_allclose(m.interceptVector, ref["intercept"], rtol=2e-5, atol=2e-5)
+
+
+def test_lr_model_transform_matches_oracle_prediction():
+    from b200fit.classification import LogisticRegressionModel
+    from b200fit.frame import ColumnarFrame
+
+    rng = np.random.default_rng(2)
+    Xh = rng.normal(size=(3001, 37)).astype(np.float32)
+    for coef, icpt in ((rng.normal(size=37), 0.2), (rng.normal(size=(5, 37)), rng.normal(size=5))):
+        m = LogisticRegressionModel(coef, icpt, 2 if np.ndim(coef) == 1 else 5)
+        out = m.transform(ColumnarFrame({"features": Xh}))
+        raw, prob, pred = oracle.lr_predict(Xh, coef, icpt)
+        np.testing.assert_allclose(out.col("rawPrediction").cpu().numpy(), raw, rtol=1e-4, atol=1e-4)
+        np.testing.assert_allclose(out.col("probability").cpu().numpy(), prob, rtol=1e-4, atol=1e-5)
+        gp = out.col("prediction").cpu().numpy()
+        margin = np.sort(prob, axis=1)
+        sure = (margin[:, -1] - margin[:, -2]) > 1e-4
+        assert (gp[sure] == pred[sure]).all()
+
+
+def test_lr_rejects_bad_labels_and_unsupported_options():
+    from b200fit.classification import LogisticRegression
+    from b200fit.frame import ColumnarFrame
+
+    Xh = np.zeros((4, 2), dtype=np.float32)
+    with pytest.raises(ValueError):
+        LogisticRegression().fit(ColumnarFrame({"features": Xh, "label": np.array([0, 1, 0.5, 1])}))
+    with pytest.raises(ValueError):
+        LogisticRegression(family="binomial").fit(ColumnarFrame({"features": Xh, "label": np.array([0, 1, 2, 1])}))
+    with pytest.raises(NotImplementedError):
+        LogisticRegression(lowerBoundsOnIntercepts=[0.0]).fit(
+            ColumnarFrame({"features": Xh, "label": np.array([0, 1, 0, 1])}))

@@ -1,0 +1,152 @@
+"""CPU tests of the host side: parameter marshalling through the fake widget, the frame,
+the product's own L-BFGS / OWL-QN against the oracle's restatement, C-ABI symbol export."""
+import ctypes
+import inspect
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle
+from oracle.optim import LBFGS as OLBFGS
+from oracle.optim import OWLQN as OOWLQN
+
+import b200fit
+from b200fit import _native
+from b200fit.frame import ColumnarFrame
+from b200fit.optim import LBFGS, OWLQN
+
+import fake_widget as fw
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_cabi_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "b200fit.h")).read()
+    declared = set(re.findall(r"\b(b2f_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    lib = ctypes.CDLL(_native.LIB_PATH)  # load only; no compute without a GPU
+    for name in declared:
+        assert hasattr(lib, name), "missing export %s" % name
+    assert declared == set(_native.PROTOTYPES), "ctypes prototypes out of sync with the header"
+    lib.b2f_version.restype = ctypes.c_int
+    assert lib.b2f_version() >= 100
+
+
+def test_estimator_discovery_and_description():
+    est = fw.list_estimators(b200fit.clustering)
+    assert "KMeans" in est and "KMeansModel" not in est
+    est = fw.list_estimators(b200fit.classification)
+    assert "LogisticRegression" in est and "LogisticRegressionModel" not in est
+    assert "VectorAssembler" in fw.list_transformers(b200fit.feature)
+    assert "StandardScalerModel" not in fw.list_transformers(b200fit.feature)
+    name, doc, table = fw.describe(b200fit.clustering.KMeans)
+    assert name == "b200fit.clustering.KMeans" and doc
+    assert list(table)[:3] == ["featuresCol", "predictionCol", "k"]
+    assert table["k"][1] == 2 and table["tol"][1] == 1e-4 and table["initMode"][1] == "k-means||"
+    assert all(len(v) == 3 and v[2] for v in table.values()), "every ctor kwarg needs a Param doc"
+    _, _, t2 = fw.describe(b200fit.classification.LogisticRegression)
+    assert t2["maxIter"][1] == 100 and t2["regParam"][1] == 0.0 and t2["family"][1] == "auto"
+    assert all(len(v) == 3 for v in t2.values())
+    sig = inspect.signature(b200fit.clustering.KMeans)
+    assert all(p.default is not inspect.Parameter.empty for p in sig.parameters.values())
+
+
+def test_text_coercion_matches_gui_rules():
+    assert fw.text_to_value("None") is None and fw.text_to_value("") is None
+    assert fw.text_to_value("True") is True and fw.text_to_value("False") is False
+    assert fw.text_to_value("8") == 8 and isinstance(fw.text_to_value("8"), int)
+    assert fw.text_to_value("0.0") == 0.0 and isinstance(fw.text_to_value("0.0"), float)
+    assert fw.text_to_value("1e-4") == 1e-4
+    assert fw.text_to_value("k-means||") == "k-means||"
+
+
+def test_param_map_is_resolved_by_name_and_types():
+    km = b200fit.clustering.KMeans()
+    pm = {fw.ForeignParam(km, "k", ""): 8, fw.ForeignParam(km, "tol", ""): 0, fw.ForeignParam(km, "seed", ""): None,
+          fw.ForeignParam(km, "initMode", ""): "random"}
+    c = km.copy(pm)
+    assert c.getOrDefault("k") == 8 and c.getOrDefault("tol") == 0.0 and isinstance(c.getOrDefault("tol"), float)
+    assert c.getOrDefault("seed") == km.getOrDefault("seed")  # None -> stays at default
+    assert km.getOrDefault("k") == 2  # original untouched
+    with pytest.raises(ValueError):
+        km.copy({"nope": 1})
+    with pytest.raises(TypeError):
+        km.copy({"k": "many"})
+    lr = b200fit.classification.LogisticRegression(regParam=1)
+    assert lr.getRegParam() == 1.0 and lr.setMaxIter(5).getMaxIter() == 5
+
+
+def test_frame_behaves_like_the_dataframe_calls_the_widgets_make():
+    df = ColumnarFrame({"b": np.arange(3), "a": np.array([1.5, 2.5, 3.5]), "cls": np.array([0, 1, 1])})
+    assert sorted(df.columns) == ["a", "b", "cls"]
+    out = df.withColumn("label", df["cls"].cast("double"))
+    assert out.col("label").dtype == np.float64 and "label" not in df.columns
+    assert out.count() == 3 and out.cache() is out
+    with pytest.raises(ValueError):
+        ColumnarFrame({"a": np.zeros(3), "b": np.zeros(4)})
+
+
+def _toy_objective(seed, n=300, d=7, K=1, lam=0.03):
+    rng = np.random.default_rng(seed)
+    X = rng.normal(size=(n, d)) * rng.uniform(0.5, 2.0, size=d)
+    if K == 1:
+        y = (rng.uniform(size=n) < 1 / (1 + np.exp(-(X @ rng.normal(size=d))))).astype(float)
+    else:
+        y = np.argmax(X @ rng.normal(size=(d, K)) + rng.gumbel(size=(n, K)), axis=1)
+    inv = np.ones(d)
+
+    def f(x):
+        if K == 1:
+            loss, g, gb = oracle.lr_binary_lossgrad(X, y, None, x[:d], x[d], inv)
+            return loss + 0.5 * lam * x[:d] @ x[:d], np.concatenate([g + lam * x[:d], [gb]])
+        C = x[: K * d].reshape(K, d)
+        loss, G, gb = oracle.lr_multinomial_lossgrad(X, y, None, C, x[K * d:], inv)
+        return loss + 0.5 * lam * (C * C).sum(), np.concatenate([(G + lam * C).ravel(), gb])
+
+    return f, np.zeros(K * d + K)
+
+
+@pytest.mark.parametrize("seed,K", [(0, 1), (1, 1), (2, 3)])
+def test_product_lbfgs_follows_the_oracle_trajectory(seed, K):
+    f, x0 = _toy_objective(seed, K=K)
+    mine = LBFGS(50, 10, 1e-9).run(f, x0)
+    _, theirs = OLBFGS(50, 10, 1e-9).minimize(f, x0)
+    assert len(mine) == len(theirs)
+    for a, b in zip(mine, theirs):
+        np.testing.assert_allclose(a.x, b["x"], rtol=0, atol=1e-12)
+        assert a.adj_value == pytest.approx(b["adj_value"], abs=1e-13)
+    assert mine[-1].n_evals == theirs[-1]["evals"]
+
+
+@pytest.mark.parametrize("seed,K", [(3, 1), (4, 3)])
+def test_product_owlqn_follows_the_oracle_trajectory(seed, K):
+    f, x0 = _toy_objective(seed, K=K)
+    d = (len(x0) - K) // K
+    l1 = np.concatenate([np.full(K * d, 0.02), np.zeros(K)])
+    mine = OWLQN(60, 10, l1, 1e-9).run(f, x0)
+    _, theirs = OOWLQN(60, 10, l1, 1e-9).minimize(f, x0)
+    assert len(mine) == len(theirs)
+    for a, b in zip(mine, theirs):
+        np.testing.assert_allclose(a.x, b["x"], rtol=0, atol=1e-12)
+    assert (mine[-1].x[: K * d] == 0).any()
+    assert mine[-1].adj_value < mine[0].adj_value
+
+
+def test_product_has_no_path_into_the_oracle():
+    pkg = os.path.join(ROOT, "orange3-spark_b200", "b200fit")
+    for fn in os.listdir(pkg):
+        if fn.endswith(".py"):
+            src = open(os.path.join(pkg, fn)).read()
+            assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), fn
+
+
+def test_missing_gpu_fails_loudly():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(_native.B200FitError):
+        b200fit.clustering.KMeans(k=2, initialModel=np.zeros((2, 2))).fit(
+            ColumnarFrame({"features": np.zeros((4, 2), dtype=np.float32)}))
