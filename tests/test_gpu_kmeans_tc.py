@@ -1,0 +1,111 @@
+"""GPU parity tests for the tcgen05 / TMA / TMEM Lloyd kernel (B2F_KM_TC3, 3xTF32) through the
+C ABI: labels, sums, counts and cost vs the CPU oracle, per-iteration centres, and agreement
+with the CUDA-core kernel.  Same tolerances as test_gpu_kmeans.py."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+SEED = 20240611
+
+
+def _imports():
+    from b200fit import _native as N
+    import gpu_util as G
+
+    return N, G
+
+
+TC_SHAPES = [(128, 32, 128), (1, 32, 128), (1000, 64, 128), (5000, 128, 256), (4099, 128, 1024), (3000, 96, 384),
+             (20000, 128, 128)]
+
+
+@pytest.mark.parametrize("n,d,k", TC_SHAPES)
+def test_tc3_step_matches_oracle(n, d, k):
+    N, G = _imports()
+    Xh = synth.mixture(n, 0, d, SEED, k, 2.0)
+    rng = np.random.default_rng(n + d + k)
+    if n >= k:
+        C = Xh[rng.choice(n, size=k, replace=False)].astype(np.float64)
+    else:
+        C = synth.mixture_centers(d, SEED, k, 2.0).astype(np.float64)
+    X, _, ld = G.upload_matrix(Xh)
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TC3)
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
+    bad = (labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)
+    assert not bad.any(), "%d label mismatches outside the 1e-6 gap band" % bad.sum()
+    _, rcost, rsums, rcounts = oracle.kmeans_step(Xh.astype(np.float64), C)
+    assert nrows == n and counts.sum() == n
+    if (labels == ref_lab).all():
+        np.testing.assert_array_equal(counts, rcounts)
+        scale = np.abs(Xh).astype(np.float64).sum(axis=0).max() / k + 1.0
+        np.testing.assert_allclose(sums, rsums, rtol=1e-5, atol=1e-6 * scale)
+    # rows that coincide with their centre have distance ~0: absolute slack of fp32 cancellation
+    assert cost == pytest.approx(rcost, rel=1e-5, abs=1e-3 * n)
+
+
+def test_tc3_agrees_with_generic_kernel_and_predict():
+    N, G = _imports()
+    L = N.lib()
+    n, d, k = 30000, 128, 512
+    Xh = synth.mixture(n, 0, d, SEED + 1, k, 2.0)
+    C = synth.mixture_centers(d, SEED + 1, k, 2.0).astype(np.float64) + 0.05
+    X, _, ld = G.upload_matrix(Xh)
+    lt, st, ct, costt, _ = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TC3)
+    lg, sg, cg, costg, _ = G.kmeans_step_raw(X, n, d, ld, C, N.KM_GENERIC)
+    assert (lt == lg).mean() > 0.9999
+    assert costt == pytest.approx(costg, rel=1e-5)
+    cen, prep, acc = G.kmeans_state(C, k, d)
+    lab = torch.empty(n, dtype=torch.int32, device=G.dev())
+    N.check(L.b2f_kmeans_predict(N.ptr(X), n, d, ld, N.ptr(prep), k, N.ptr(lab), None, N.KM_TC3, G.stream()), "predict")
+    assert np.array_equal(lab.cpu().numpy(), lt)
+
+
+def test_tc3_fit_per_iteration_parity():
+    """BASELINE config 2 shape at reduced N (d = 128, k = 1024, fixed initialModel, tol = 0)."""
+    N, G = _imports()
+    from b200fit.clustering import CudaLloydEngine
+    from b200fit.dist import Comm
+    from b200fit.feature import pack_columns
+
+    n, d, k, iters = 60000, 128, 1024, 5
+    Xh = synth.mixture(n, 0, d, SEED, k, 2.0)
+    C0 = Xh[np.random.default_rng(2).choice(n, size=k, replace=False)].astype(np.float64)
+    ref = oracle.kmeans_lloyd(Xh.astype(np.float64), C0, max_iter=iters, tol=0.0)
+    eng = CudaLloydEngine(pack_columns([Xh]), k, algo=N.KM_AUTO)
+    eng.set_centers(C0)
+    comm = Comm()
+    for it in range(iters):
+        payload = eng.step()
+        comm.all_reduce_sum(payload)
+        _, cost = eng.finalize(payload, 0.0)
+        sc = np.abs(ref["centers_hist"][it]).max()
+        np.testing.assert_allclose(eng.get_centers(), ref["centers_hist"][it], rtol=1e-5, atol=1e-5 * sc)
+        assert cost == pytest.approx(ref["cost_hist"][it], rel=1e-5)
+        np.testing.assert_array_equal(eng.get_counts(payload), ref["counts_hist"][it])
+
+
+def test_tc1_filter_pass_is_sane():
+    N, G = _imports()
+    n, d, k = 8000, 128, 256
+    Xh = synth.mixture(n, 0, d, SEED, k, 2.0)
+    C = synth.mixture_centers(d, SEED, k, 2.0).astype(np.float64) + 0.02
+    X, _, ld = G.upload_matrix(Xh)
+    lt, _, counts, cost, _ = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TC1)
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
+    clear = (ref_second - ref_d) > 0.05 * ref_second
+    assert (lt[clear] == ref_lab[clear]).all() and counts.sum() == n
+    assert cost == pytest.approx(float(ref_d.sum()), rel=5e-3)
+
+
+def test_tc_rejects_unsupported_shapes():
+    N, G = _imports()
+    Xh = np.zeros((100, 48), dtype=np.float32)
+    X, _, ld = G.upload_matrix(Xh)
+    with pytest.raises(N.B200FitError):
+        G.kmeans_step_raw(X, 100, 48, ld, np.zeros((128, 48)), N.KM_TC3)
+    with pytest.raises(N.B200FitError):
+        G.kmeans_step_raw(X[:, :32].contiguous(), 100, 32, 32, np.zeros((100, 32)), N.KM_TC3)
