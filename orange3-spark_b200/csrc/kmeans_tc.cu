@@ -11,15 +11,18 @@
 // Replaces MLlib's findClosest + axpy loop behind KMeans.fit;
 //   reference call site: orangecontrib/spark/base/spark_ml_estimator.py:22.
 //
-// CTA = 256 threads, persistent (one CTA per SM), warp roles:
+// CTA = 384 threads, persistent (one CTA per SM), warp roles:
 //   warp 0  X producer   : TMA loads of the 128-row X tile (KC chunks of 128 rows x 32 floats)
 //   warp 1  MMA issuer   : one elected thread issues tcgen05.mma, commits to mbarriers
 //   warp 2  B producer   : TMA loads of centre operand stages (C_hi / C_lo chunk of 128 centres)
 //   warp 3  TMEM allocator
-//   warps 4-7 (128 thr)  : split X into hi/lo in place, then epilogue: tcgen05.ld, + ||c||^2,
-//                          running argmin (thread == row), labels, cost, and the row -> centroid
-//                          accumulation with 16-byte vector reductions into fp32 replicas.
+//   warps 4-7 (128 thr)  : epilogue: tcgen05.ld, + ||c||^2, running argmin (thread == row), labels
+//   warps 8-11 (128 thr) : split each landed X chunk into explicit TF32 hi / lo operands, then
+//                          the row -> centroid accumulation of the PREVIOUS tile (16-byte vector
+//                          reductions into fp32 replicas), cost and counts -- decoupled from the
+//                          argmin warps so neither stalls the tensor pipe.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -28,9 +31,10 @@ namespace {
 constexpr int TM = 128;            // rows per tile == UMMA M == TMEM lanes
 constexpr int TN = 128;            // centres per accumulator tile == UMMA N
 constexpr int CHUNK_BYTES = TM * 128;  // 128 rows x 32 floats, 128B swizzle atom rows
-constexpr int NTHREADS = 256;
+constexpr int NTHREADS = 384;
 constexpr int EPI_THREADS = 128;
-constexpr uint32_t TMEM_COLS = 256;  // two accumulator buffers of TN columns
+constexpr uint32_t TMEM_COLS = 512;  // [0,256) two accumulator buffers | [256,384) X_hi | [384,512) X_lo
+constexpr uint32_t TMEM_A_HI = 256, TMEM_A_LO = 384;
 
 // ---------------------------------------------------------------------------------------------
 // PTX wrappers
@@ -75,22 +79,43 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
       : "memory");
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
 }
-__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                            uint32_t accumulate) {
+// A operand from tensor memory (lanes = rows, columns = K), B from shared memory
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+      "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]),
+      "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]),
+      "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -108,23 +133,23 @@ __device__ __forceinline__ void red_add_v4(float* p, float4 v) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
                : "memory");
 }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-// K-major, 128B-swizzled operand tile whose 8-row groups are 1024 B apart (SM100 UMMA descriptor:
-// start>>4 | LBO(=1, unused for swizzled K-major)<<16 | SBO(1024>>4)<<32 | version 1<<46 | SWIZZLE_128B(2)<<61)
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
-  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
+// Shared-memory matrix descriptor (SM100 UMMA) for a K-major, 128B-swizzled operand tile whose 8-row
+// groups are 1024 B apart:  start>>4 | LBO(=1, unused for swizzled K-major)<<16 | SBO(1024>>4)<<32 |
+// version(1)<<46 | SWIZZLE_128B(2)<<61.  The MMA issuer builds it as desc_fixed | (address >> 4).
 // kind::tf32, fp32 accumulate, A and B K-major, M = 128, N = TN
 constexpr uint32_t IDESC_TF32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 
 struct Smem {
-  // dynamic shared memory, carved manually (1024-byte aligned): XH[KC] | XL[KC] (NPASS==3) | stages
-  uint64_t x_full, x_split, x_empty;
+  // lives behind the operand tiles in dynamic shared memory (see km_tc_kernel for the carve-up)
+  // per 32-column chunk of the X tile: staging (smem) full/empty, operand (TMEM) full/empty
+  uint64_t xs_full[4], xs_empty[4], xa_full[4], xa_empty[4];
   uint64_t b_full[8], b_empty[8];
   uint64_t t_full[2], t_empty[2];
+  uint64_t a_full[2], a_empty[2];  // epilogue -> accumulate hand-off (labels / scores of one row tile)
   uint32_t tmem_base;
-  float cn[2][TN];
+  int lab[2][TM];
+  float score[2][TM];
 };
 
 }  // namespace
@@ -136,12 +161,12 @@ __global__ void __launch_bounds__(NTHREADS, 1)
                  const float* __restrict__ cn, int k, int nstages, double* __restrict__ payload,
                  float* __restrict__ rep, unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels,
                  int accumulate) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];  // 128B swizzle atoms need 1024-byte alignment
+  uint8_t* base = smem_raw;
+  if (smem_u32(base) & 1023u) __trap();
   const int KC = d / 32;
-  uint8_t* xh = base;
-  uint8_t* xl = xh + (size_t)KC * CHUNK_BYTES;
-  uint8_t* stages = (NPASS == 3) ? xl + (size_t)KC * CHUNK_BYTES : xl;
+  uint8_t* xs = base;  // TMA staging of the raw fp32 X tile (KC chunks of 128 rows x 128 B, 128B swizzle)
+  uint8_t* stages = xs + (size_t)KC * CHUNK_BYTES;
   const int stage_bytes = (NPASS == 3 ? 2 : 1) * CHUNK_BYTES;
   Smem* sm = reinterpret_cast<Smem*>(stages + (size_t)nstages * stage_bytes);
 
@@ -150,16 +175,21 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   const int NT = k / TN;
 
   if (threadIdx.x == 0) {
-    mbar_init(&sm->x_full, 1);
-    mbar_init(&sm->x_split, EPI_THREADS);
-    mbar_init(&sm->x_empty, 1);
-    for (int s = 0; s < nstages; ++s) {
+    for (int c = 0; c < 4; ++c) {
+      mbar_init(&sm->xs_full[c], 1);
+      mbar_init(&sm->xs_empty[c], EPI_THREADS);
+      mbar_init(&sm->xa_full[c], EPI_THREADS);
+      mbar_init(&sm->xa_empty[c], 1);
+    }
+    for (int s = 0; s < 8; ++s) {
       mbar_init(&sm->b_full[s], 1);
       mbar_init(&sm->b_empty[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&sm->t_full[b], 1);
       mbar_init(&sm->t_empty[b], EPI_THREADS);
+      mbar_init(&sm->a_full[b], EPI_THREADS);
+      mbar_init(&sm->a_empty[b], EPI_THREADS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -175,162 +205,230 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   const uint32_t tmem_base = sm->tmem_base;
 
   if (warp == 0) {
-    // ===================== X producer =====================
+    // ===================== X producer: one TMA per 32-column chunk, chunk-granular reuse ==========
     if (lane == 0) {
       uint32_t it = 0;
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        mbar_wait(&sm->x_empty, (it & 1) ^ 1);  // all MMAs of the previous tile have read X
-        mbar_expect_tx(&sm->x_full, (uint32_t)(KC * CHUNK_BYTES));
-        for (int kc = 0; kc < KC; ++kc)
-          tma_load_2d(xh + (size_t)kc * CHUNK_BYTES, &map_x, kc * 32, (int)(tile * TM), &sm->x_full);
+        for (int kc = 0; kc < KC; ++kc) {
+          mbar_wait(&sm->xs_empty[kc], (it & 1) ^ 1);  // the split warps have read the previous tile's chunk
+          mbar_expect_tx(&sm->xs_full[kc], (uint32_t)CHUNK_BYTES);
+          tma_load_2d(xs + (size_t)kc * CHUNK_BYTES, &map_x, kc * 32, (int)(tile * TM), &sm->xs_full[kc]);
+        }
       }
     }
   } else if (warp == 2) {
     // ===================== B producer =====================
     if (lane == 0) {
-      uint32_t it = 0;
+      uint32_t s = 0, ph = 0;
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         for (int nt = 0; nt < NT; ++nt) {
-          for (int kc = 0; kc < KC; ++kc, ++it) {
-            const int s = it % nstages;
-            const uint32_t ph = (it / nstages) & 1;
+          for (int kc = 0; kc < KC; ++kc) {
             mbar_wait(&sm->b_empty[s], ph ^ 1);
             mbar_expect_tx(&sm->b_full[s], (uint32_t)stage_bytes);
             uint8_t* dst = stages + (size_t)s * stage_bytes;
             tma_load_2d(dst, &map_ch, kc * 32, nt * TN, &sm->b_full[s]);
             if (NPASS == 3) tma_load_2d(dst + CHUNK_BYTES, &map_cl, kc * 32, nt * TN, &sm->b_full[s]);
+            if (++s == (uint32_t)nstages) {
+              s = 0;
+              ph ^= 1;
+            }
           }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      uint32_t it = 0, bit = 0, acc_it = 0;
-      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        mbar_wait(&sm->x_split, it & 1);  // X tile landed and was split into hi / lo
-        tc_fence_after();
-        for (int nt = 0; nt < NT; ++nt, ++acc_it) {
-          const int buf = acc_it & 1;
-          mbar_wait(&sm->t_empty[buf], ((acc_it >> 1) & 1) ^ 1);  // epilogue drained this accumulator
+    // The whole warp stays converged (waits are executed by all lanes); one elected lane issues the
+    // tcgen05 instructions, so descriptors live in uniform registers and the issue loop stays short.
+    const uint64_t desc_fixed = (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+    const uint32_t st_a = smem_u32(stages) >> 4;
+    const uint32_t chunk16 = CHUNK_BYTES >> 4, stage16 = (uint32_t)stage_bytes >> 4;
+    uint32_t it = 0, acc_it = 0, stage = 0, bphase = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      for (int nt = 0; nt < NT; ++nt, ++acc_it) {
+        const uint32_t buf = acc_it & 1;
+        mbar_wait(&sm->t_empty[buf], ((acc_it >> 1) & 1) ^ 1);  // epilogue drained this accumulator
+        const uint32_t tmem_d = tmem_base + buf * TN;
+        for (int kc = 0; kc < KC; ++kc) {
+          if (nt == 0) mbar_wait(&sm->xa_full[kc], it & 1);  // X chunk split into hi / lo sits in TMEM
+          mbar_wait(&sm->b_full[stage], bphase);
           tc_fence_after();
-          const uint32_t tmem_d = tmem_base + (uint32_t)(buf * TN);
-          for (int kc = 0; kc < KC; ++kc, ++bit) {
-            const int s = bit % nstages;
-            mbar_wait(&sm->b_full[s], (bit / nstages) & 1);
-            tc_fence_after();
-            const uint32_t a_hi = smem_u32(xh + (size_t)kc * CHUNK_BYTES);
-            const uint32_t a_lo = smem_u32(xl + (size_t)kc * CHUNK_BYTES);
-            const uint32_t b_hi = smem_u32(stages + (size_t)s * stage_bytes);
-            const uint32_t b_lo = b_hi + CHUNK_BYTES;
+          if (elect_one()) {
+            const uint32_t a_hi = tmem_base + TMEM_A_HI + kc * 32;  // 32 TMEM columns per chunk
+            const uint32_t a_lo = tmem_base + TMEM_A_LO + kc * 32;
+            const uint64_t b_hi = desc_fixed | (uint64_t)(st_a + stage * stage16);
+            const uint64_t b_lo = b_hi + chunk16;
 #pragma unroll
-            for (int k8 = 0; k8 < 4; ++k8) {
-              const uint32_t off = k8 * 32;  // 8 tf32 = 32 bytes along K inside the swizzle atom
-              tc_mma_tf32(tmem_d, umma_desc_sw128(a_hi + off), umma_desc_sw128(b_hi + off), IDESC_TF32,
-                          (kc | k8) ? 1u : 0u);
+            for (int k8 = 0; k8 < 4; ++k8) {  // 8 tf32 = 32 bytes = 2 descriptor units along K
+              tc_mma_tf32_ts(tmem_d, a_hi + 8 * k8, b_hi + 2 * k8, IDESC_TF32, (kc | k8) ? 1u : 0u);
               if (NPASS == 3) {
-                tc_mma_tf32(tmem_d, umma_desc_sw128(a_hi + off), umma_desc_sw128(b_lo + off), IDESC_TF32, 1u);
-                tc_mma_tf32(tmem_d, umma_desc_sw128(a_lo + off), umma_desc_sw128(b_hi + off), IDESC_TF32, 1u);
+                tc_mma_tf32_ts(tmem_d, a_hi + 8 * k8, b_lo + 2 * k8, IDESC_TF32, 1u);
+                tc_mma_tf32_ts(tmem_d, a_lo + 8 * k8, b_hi + 2 * k8, IDESC_TF32, 1u);
               }
             }
-            tc_commit(&sm->b_empty[s]);  // stage may be refilled once these MMAs retire
+            tc_commit(&sm->b_empty[stage]);                      // stage may be refilled once these retire
+            if (nt == NT - 1) tc_commit(&sm->xa_empty[kc]);      // TMEM X chunk free for the next tile
+            if (kc == KC - 1) tc_commit(&sm->t_full[buf]);       // accumulator complete
           }
-          tc_commit(&sm->t_full[buf]);  // accumulator complete
+          __syncwarp();
+          if (++stage == (uint32_t)nstages) {
+            stage = 0;
+            bphase ^= 1;
+          }
         }
-        tc_commit(&sm->x_empty);  // X tile free for the next TMA
       }
     }
-  } else if (warp >= 4) {
-    // ===================== split + epilogue (128 threads, thread == row) =====================
-    const int et = threadIdx.x - 128;
+  } else if (warp >= 4 && warp < 8) {
+    // ===================== epilogue: running argmin, thread == row =====================
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const int row_in_tile = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-    double cost = 0.0;
-    unsigned long long nrows = 0;
     uint32_t it = 0, acc_it = 0;
-    float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      // ---- split x into explicit TF32 hi (in place) and lo
-      mbar_wait(&sm->x_full, it & 1);
-      {
-        float4* h4 = reinterpret_cast<float4*>(xh);
-        float4* l4 = reinterpret_cast<float4*>(xl);
-        const int nvec = KC * CHUNK_BYTES / 16;
-        for (int i = et; i < nvec; i += EPI_THREADS) {
-          const float4 v = h4[i];
-          float4 hi, lo;
-          hi.x = to_tf32(v.x); hi.y = to_tf32(v.y); hi.z = to_tf32(v.z); hi.w = to_tf32(v.w);
-          h4[i] = hi;
-          if (NPASS == 3) {
-            lo.x = to_tf32(v.x - hi.x); lo.y = to_tf32(v.y - hi.y); lo.z = to_tf32(v.z - hi.z); lo.w = to_tf32(v.w - hi.w);
-            l4[i] = lo;
-          }
-        }
-        fence_proxy_async();  // generic-proxy writes -> visible to the tensor core (async proxy)
-        mbar_arrive(&sm->x_split);
-      }
-      // ---- running argmin over all centre tiles
-      float b1 = INFINITY, b2 = INFINITY;
-      int i1 = 0;
+      // two independent chains (even / odd columns) keep the min/max dependency chains short
+      float b1a = INFINITY, b2a = INFINITY, b1b = INFINITY, b2b = INFINITY;
+      int i1a = 0, i1b = 1;
       for (int nt = 0; nt < NT; ++nt, ++acc_it) {
         const int buf = acc_it & 1;
-        sm->cn[buf][et] = cn[nt * TN + et];
-        epi_bar_sync();
         mbar_wait(&sm->t_full[buf], (acc_it >> 1) & 1);
         tc_fence_after();
         const uint32_t taddr = tmem_base + lane_addr + (uint32_t)(buf * TN);
+        uint32_t v[2][32];
+        tmem_ld32(taddr, v[0]);
 #pragma unroll
-        for (int c0 = 0; c0 < TN; c0 += 32) {
-          uint32_t v[32];
-          tmem_ld32(taddr + c0, v);
+        for (int c = 0; c < TN / 32; ++c) {
           tmem_ld_wait();
+          if (c + 1 < TN / 32) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+          const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + c * 32);  // warp-uniform, L1 hits
+          const int jbase = nt * TN + c * 32;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float s = __uint_as_float(v[j]) + sm->cn[buf][c0 + j];
-            const bool lt = s < b1;
-            b2 = fminf(b2, fmaxf(b1, s));
-            b1 = fminf(b1, s);
-            i1 = lt ? (nt * TN + c0 + j) : i1;
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 cv = __ldg(cn4 + j4);
+            const float s0 = __uint_as_float(v[c & 1][j4 * 4 + 0]) + cv.x;
+            const float s1 = __uint_as_float(v[c & 1][j4 * 4 + 1]) + cv.y;
+            const float s2 = __uint_as_float(v[c & 1][j4 * 4 + 2]) + cv.z;
+            const float s3 = __uint_as_float(v[c & 1][j4 * 4 + 3]) + cv.w;
+            const int j = jbase + j4 * 4;
+            i1a = (s0 < b1a) ? j : i1a;       b2a = fminf(b2a, fmaxf(b1a, s0)); b1a = fminf(b1a, s0);
+            i1b = (s1 < b1b) ? j + 1 : i1b;   b2b = fminf(b2b, fmaxf(b1b, s1)); b1b = fminf(b1b, s1);
+            i1a = (s2 < b1a) ? j + 2 : i1a;   b2a = fminf(b2a, fmaxf(b1a, s2)); b1a = fminf(b1a, s2);
+            i1b = (s3 < b1b) ? j + 3 : i1b;   b2b = fminf(b2b, fmaxf(b1b, s3)); b1b = fminf(b1b, s3);
           }
         }
         tc_fence_before();
         mbar_arrive(&sm->t_empty[buf]);
       }
-      // ---- labels, cost, centroid accumulation (rows re-read from L2, one warp per row)
+      // merge the chains: smaller score wins, equal scores keep the lower centre index
+      const bool a_wins = (b1a < b1b) || (b1a == b1b && i1a < i1b);
+      const float b1 = a_wins ? b1a : b1b;
+      const int i1 = a_wins ? i1a : i1b;
       const int64_t row = tile * TM + row_in_tile;
       if (labels && row < n) labels[row] = i1;
       if (accumulate) {
-        const int nch = (d + 127) / 128;
-        for (int r = 0; r < 32; ++r) {
-          const int64_t rr = tile * TM + q * 32 + r;
-          if (rr >= n) break;
-          const int lbl = __shfl_sync(0xffffffffu, i1, r);
-          const float sc = __shfl_sync(0xffffffffu, b1, r);
-          float xn = 0.f;
-          for (int ch = 0; ch < nch; ++ch) {
-            const int c = ch * 128 + lane * 4;
-            if (c < d) {
-              const float4 xv = *reinterpret_cast<const float4*>(X + rr * ld + c);
-              xn = fmaf(xv.x, xv.x, xn); xn = fmaf(xv.y, xv.y, xn); xn = fmaf(xv.z, xv.z, xn); xn = fmaf(xv.w, xv.w, xn);
-              red_add_v4(myrep + (size_t)lbl * d + c, xv);
+        const int ab = it & 1;
+        mbar_wait(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1);
+        sm->lab[ab][row_in_tile] = i1;
+        sm->score[ab][row_in_tile] = b1;
+        mbar_arrive(&sm->a_full[ab]);  // release semantics order the two stores before the arrive
+      }
+    }
+  } else if (warp >= 8) {
+    // ===================== split X into TF32 hi / lo; accumulate finished row tiles =====================
+    const int w4 = warp - 8;
+    double cost = 0.0;
+    unsigned long long nrows = 0;
+    float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
+    const int nch = (d + 127) / 128;
+    uint32_t it = 0;
+    int64_t prev_tile = -1;
+    for (int64_t tile = blockIdx.x;; tile += gridDim.x, ++it) {
+      const bool have = tile < ntiles;
+      if (have) {
+        // thread == row: read the row's 32 floats of each chunk from the swizzled staging tile
+        // (16-byte piece p of row r sits at r*128 + ((p ^ (r & 7)) << 4)), split into explicit TF32
+        // hi / lo, and store them as the A operand in tensor memory (lane = row, column = k).
+        const int r = w4 * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
+        for (int kc = 0; kc < KC; ++kc) {
+          mbar_wait(&sm->xs_full[kc], it & 1);
+          const uint8_t* src = xs + (size_t)kc * CHUNK_BYTES + (size_t)r * 128;
+          uint32_t hi[32], lo[32];
+#pragma unroll
+          for (int p = 0; p < 8; ++p) {
+            const float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
+            const float h0 = to_tf32(v.x), h1 = to_tf32(v.y), h2 = to_tf32(v.z), h3 = to_tf32(v.w);
+            hi[p * 4 + 0] = __float_as_uint(h0); hi[p * 4 + 1] = __float_as_uint(h1);
+            hi[p * 4 + 2] = __float_as_uint(h2); hi[p * 4 + 3] = __float_as_uint(h3);
+            if (NPASS == 3) {
+              lo[p * 4 + 0] = __float_as_uint(to_tf32(v.x - h0)); lo[p * 4 + 1] = __float_as_uint(to_tf32(v.y - h1));
+              lo[p * 4 + 2] = __float_as_uint(to_tf32(v.z - h2)); lo[p * 4 + 3] = __float_as_uint(to_tf32(v.w - h3));
             }
           }
-          xn = warp_sum(xn);
-          if (lane == 0) {
-            cost += (double)fmaxf(xn + sc, 0.f);
-            atomicAdd(cnt + lbl, 1ull);
-            ++nrows;
+          mbar_arrive(&sm->xs_empty[kc]);                 // staging chunk may be refilled (next tile)
+          mbar_wait(&sm->xa_empty[kc], (it & 1) ^ 1);     // previous tile's MMAs are done with this TMEM chunk
+          tc_fence_after();
+          tmem_st32(tmem_base + lane_addr + TMEM_A_HI + kc * 32, hi);
+          if (NPASS == 3) tmem_st32(tmem_base + lane_addr + TMEM_A_LO + kc * 32, lo);
+          tmem_st_wait();
+          tc_fence_before();
+          mbar_arrive(&sm->xa_full[kc]);
+        }
+      }
+      if (accumulate && prev_tile >= 0) {
+        // rows of the previous tile: labels / scores come from the epilogue warps, the row values are
+        // re-read from global memory (L2 hits: the tile was just streamed in by TMA)
+        const uint32_t pit = it - 1;
+        const int ab = pit & 1;
+        mbar_wait(&sm->a_full[ab], (pit >> 1) & 1);
+        const int my_lab = sm->lab[ab][w4 * 32 + lane];
+        const float my_sc = sm->score[ab][w4 * 32 + lane];
+        mbar_arrive(&sm->a_empty[ab]);
+        const int64_t r0 = prev_tile * TM + w4 * 32;
+        for (int g = 0; g < 32; g += 8) {
+          float4 xv[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int64_t rr = r0 + g + u;
+            xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (rr < n && lane * 4 < d) xv[u] = *reinterpret_cast<const float4*>(X + rr * ld + lane * 4);
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int64_t rr = r0 + g + u;
+            const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
+            const float sc = __shfl_sync(0xffffffffu, my_sc, g + u);
+            if (rr < n) {  // warp-uniform
+              float xn = 0.f;
+              if (lane * 4 < d) {
+                xn = fmaf(xv[u].x, xv[u].x, xn); xn = fmaf(xv[u].y, xv[u].y, xn);
+                xn = fmaf(xv[u].z, xv[u].z, xn); xn = fmaf(xv[u].w, xv[u].w, xn);
+                red_add_v4(myrep + (size_t)lbl * d + lane * 4, xv[u]);
+              }
+              for (int ch = 1; ch < nch; ++ch) {  // d > 128 (single-pass variant only)
+                const int c = ch * 128 + lane * 4;
+                if (c < d) {
+                  const float4 x2 = *reinterpret_cast<const float4*>(X + rr * ld + c);
+                  xn = fmaf(x2.x, x2.x, xn); xn = fmaf(x2.y, x2.y, xn);
+                  xn = fmaf(x2.z, x2.z, xn); xn = fmaf(x2.w, x2.w, xn);
+                  red_add_v4(myrep + (size_t)lbl * d + c, x2);
+                }
+              }
+              xn = warp_sum(xn);
+              if (lane == 0) {
+                cost += (double)fmaxf(xn + sc, 0.f);
+                atomicAdd(cnt + lbl, 1ull);
+                ++nrows;
+              }
+            }
           }
         }
       }
+      if (!have) break;
+      prev_tile = tile;
     }
-    if (accumulate) {
-      // one double atomic per warp
-      if (lane == 0) {
-        atomicAdd(payload + (size_t)k * d + k, cost);
-        atomicAdd(payload + (size_t)k * d + k + 1, (double)nrows);
-      }
+    if (accumulate && lane == 0) {
+      atomicAdd(payload + (size_t)k * d + k, cost);
+      atomicAdd(payload + (size_t)k * d + k + 1, (double)nrows);
     }
   }
   // ---- teardown
@@ -386,9 +484,9 @@ static const int kSmemLimit = 227 * 1024;
 
 static int km_tc_stages(int d, int passes) {
   const int KC = d / 32;
-  const int xbytes = (passes == 3 ? 2 : 1) * KC * CHUNK_BYTES;
+  const int xbytes = KC * CHUNK_BYTES;  // fp32 staging only: the hi / lo operands live in tensor memory
   const int stage = (passes == 3 ? 2 : 1) * CHUNK_BYTES;
-  const int left = kSmemLimit - 1024 /*align*/ - (int)sizeof(Smem) - 64 - xbytes;
+  const int left = kSmemLimit - (int)sizeof(Smem) - 64 - xbytes;
   int s = left / stage;
   if (s > 8) s = 8;
   return s;
@@ -428,10 +526,11 @@ int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, i
     cnt = reinterpret_cast<unsigned long long*>(ap + A.off_cnt);
   }
   const int KC = d / 32;
-  const size_t smem = 1024 + (size_t)(passes == 3 ? 2 : 1) * KC * CHUNK_BYTES +
+  const size_t smem = (size_t)KC * CHUNK_BYTES +
                       (size_t)nstages * (passes == 3 ? 2 : 1) * CHUNK_BYTES + sizeof(Smem) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
+  if (const char* g = getenv("B2F_TC_GRID")) grid = atoi(g) > 0 ? atoi(g) : grid;  // dev knob
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
   if (passes == 3) {
     B2F_CUDA(cudaFuncSetAttribute(km_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
