@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
                  const __grid_constant__ CUtensorMap map_cl, const float* __restrict__ X, int64_t n, int d, int64_t ld,
                  const float* __restrict__ cn, int k, int nstages, double* __restrict__ payload,
                  float* __restrict__ rep, unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels,
-                 int accumulate) {
+                 int accumulate, int dbg) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];  // 128B swizzle atoms need 1024-byte alignment
   uint8_t* base = smem_raw;
   if (smem_u32(base) & 1023u) __trap();
@@ -223,6 +223,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         for (int nt = 0; nt < NT; ++nt) {
           for (int kc = 0; kc < KC; ++kc) {
+            if ((dbg & 1) && ph) continue;
             mbar_wait(&sm->b_empty[s], ph ^ 1);
             mbar_expect_tx(&sm->b_full[s], (uint32_t)stage_bytes);
             uint8_t* dst = stages + (size_t)s * stage_bytes;
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         const uint32_t tmem_d = tmem_base + buf * TN;
         for (int kc = 0; kc < KC; ++kc) {
           if (nt == 0) mbar_wait(&sm->xa_full[kc], it & 1);  // X chunk split into hi / lo sits in TMEM
-          mbar_wait(&sm->b_full[stage], bphase);
+          if (!(dbg & 1) || bphase == 0) mbar_wait(&sm->b_full[stage], bphase);
           tc_fence_after();
           if (elect_one()) {
             const uint32_t a_hi = tmem_base + TMEM_A_HI + kc * 32;  // 32 TMEM columns per chunk
@@ -301,6 +302,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
           if (c + 1 < TN / 32) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
           const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + c * 32);  // warp-uniform, L1 hits
           const int jbase = nt * TN + c * 32;
+          if (dbg & 2) continue;
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
             const float4 cv = __ldg(cn4 + j4);
@@ -532,14 +534,15 @@ int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, i
   int grid = b2f_sm_count();
   if (const char* g = getenv("B2F_TC_GRID")) grid = atoi(g) > 0 ? atoi(g) : grid;  // dev knob
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
+  const int dbg = getenv("B2F_TC_DBG") ? atoi(getenv("B2F_TC_DBG")) : 0;  // dev knob, results invalid when set
   if (passes == 3) {
     B2F_CUDA(cudaFuncSetAttribute(km_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     km_tc_kernel<3><<<grid, NTHREADS, smem, stream>>>(mx, mh, ml, X, n, d, ld, cn, k, nstages, payload, rep, cnt,
-                                                      labels, accumulate ? 1 : 0);
+                                                      labels, accumulate ? 1 : 0, dbg);
   } else {
     B2F_CUDA(cudaFuncSetAttribute(km_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     km_tc_kernel<1><<<grid, NTHREADS, smem, stream>>>(mx, mh, ml, X, n, d, ld, cn, k, nstages, payload, rep, cnt,
-                                                      labels, accumulate ? 1 : 0);
+                                                      labels, accumulate ? 1 : 0, dbg);
   }
   B2F_LAUNCH_CHECK();
   return B2F_OK;

@@ -16,6 +16,7 @@ ap.add_argument("--d", type=int, default=128)
 ap.add_argument("--k", type=int, default=1024)
 ap.add_argument("--algo", type=int, default=2)
 ap.add_argument("--reps", type=int, default=5)
+ap.add_argument("--predict", action="store_true", help="labels only (no accumulation)")
 a = ap.parse_args()
 L = N.lib()
 dev = torch.device("cuda", 0)
@@ -26,13 +27,18 @@ C = X[idx].double().contiguous()
 prep = torch.empty(L.b2f_kmeans_prep_bytes(a.k, a.d), dtype=torch.uint8, device=dev)
 acc = torch.empty(L.b2f_kmeans_acc_bytes(a.k, a.d), dtype=torch.uint8, device=dev)
 N.check(L.b2f_kmeans_prepare(N.ptr(C), a.k, a.d, N.ptr(prep), N.stream_ptr()), "prep")
+lab = torch.empty(a.n, dtype=torch.int32, device=dev)
 ts = []
 for i in range(a.reps + 2):
     N.check(L.b2f_kmeans_acc_zero(N.ptr(acc), a.k, a.d, N.stream_ptr()), "zero")
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    N.check(L.b2f_kmeans_step(N.ptr(X), a.n, a.d, a.d, None, N.ptr(prep), a.k, N.ptr(acc), None, a.algo,
-                              N.stream_ptr()), "step")
+    if a.predict:
+        N.check(L.b2f_kmeans_predict(N.ptr(X), a.n, a.d, a.d, N.ptr(prep), a.k, N.ptr(lab), None, a.algo,
+                                     N.stream_ptr()), "predict")
+    else:
+        N.check(L.b2f_kmeans_step(N.ptr(X), a.n, a.d, a.d, None, N.ptr(prep), a.k, N.ptr(acc), None, a.algo,
+                                  N.stream_ptr()), "step")
     e1.record()
     torch.cuda.synchronize()
     if i >= 2:
