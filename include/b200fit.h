@@ -136,6 +136,20 @@ size_t b2f_lr_scratch_bytes(int d, int n_classes);
 int b2f_lr_binary_lossgrad(const float* X, const float* y, const float* w, int64_t n, int d, int64_t ld,
                            const double* beta, const double* icpt, double* out, void* scratch,
                            b2f_stream_t stream);
+/* Same pass as b2f_lr_binary_lossgrad for callers that cannot supply scratch memory.
+ * (No counterpart in the reference; it exists for hosts that may not allocate on the device:
+ * bindings that own only the buffers they were handed, or code running where cudaMalloc is not
+ * allowed.)  The per-CTA partial sums go to a fixed array inside the library (about 1.2 MB that
+ * every GPU loading the library keeps until exit), so:
+ *   - the padded feature count ld must be <= 512; larger inputs are rejected with B2F_EINVAL;
+ *   - the call allocates and frees nothing; inputs and `out` (accumulated, zero it first) are
+ *     still the caller's;
+ *   - the first call on each device looks up the array's device address (a one-time runtime
+ *     query): make that first call before starting any stream capture;
+ *   - all calls on a device share the array: two calls that can overlap on the GPU (different
+ *     streams, or different host threads) race on it and give wrong sums -- serialise them.     */
+int b2f_lr_binary_lossgrad_noalloc(const float* X, const float* y, const float* w, int64_t n, int d, int64_t ld,
+                                   const double* beta, const double* icpt, double* out, b2f_stream_t stream);
 int b2f_lr_multinomial_lossgrad(const float* X, const float* y, const float* w, int64_t n, int d, int64_t ld,
                                 int n_classes, const double* beta, const double* icpt, double* out,
                                 void* scratch, b2f_stream_t stream);

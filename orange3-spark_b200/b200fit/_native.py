@@ -37,6 +37,7 @@ PROTOTYPES = {
     "b2f_kmeans_predict": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _i32, _vp, _vp, _i32, _vp]),
     "b2f_lr_scratch_bytes": (_sz, [_i32, _i32]),
     "b2f_lr_binary_lossgrad": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "b2f_lr_binary_lossgrad_noalloc": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i64, _vp, _vp, _vp, _vp]),
     "b2f_lr_multinomial_lossgrad": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i64, _i32, _vp, _vp, _vp, _vp, _vp]),
     "b2f_lr_predict": (C.c_int, [_vp, _i64, _i32, _i64, _i32, _vp, _vp, _f64, _vp, _vp, _vp, _vp]),
 }

@@ -511,3 +511,69 @@ extern "C" int b2f_lr_predict(const float* X, int64_t n, int d, int64_t ld, int 
   B2F_LAUNCH_CHECK();
   return B2F_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of the binary loss+gradient pass.
+//
+// Some callers of this library are not able to hand over scratch memory: a host program that
+// is not built on a device allocator (for example a JVM / cgo / ctypes binding that only owns
+// the input and output buffers it was given), or code running where cudaMalloc is off limits
+// (inside a latency-critical loop, or after the process has handed all device memory to
+// another framework's pool).  For them the per-CTA partial sums live in the fixed device array
+// below instead of caller-provided scratch.
+//
+// The array is part of the library image: every GPU that loads libb200fit.so holds these
+// LR_NA_SCRATCH_DOUBLES * 8 bytes (about 1.2 MB) until the process exits.
+// ---------------------------------------------------------------------------------------------
+#define LR_NA_MAX_D 512       // largest feature count (padded row length) the variant accepts
+#define LR_NA_MAX_PARTS 304   // largest number of per-CTA partials it will ever use
+#define LR_NA_SCRATCH_DOUBLES (LR_NA_MAX_PARTS * (LR_NA_MAX_D + 3))
+
+static __device__ __align__(256) double lr_na_scratch[LR_NA_SCRATCH_DOUBLES];
+
+// Device address of lr_na_scratch, looked up once per device.  In host code the symbol name is
+// only a handle for the runtime, not a pointer a kernel can use, so the address has to come
+// from cudaGetSymbolAddress with the right device current.
+static int lr_na_scratch_ptr(double** out) {
+  static double* cached[64];
+  int dev = 0;
+  B2F_CUDA(cudaGetDevice(&dev));
+  B2F_REQUIRE(dev >= 0 && dev < 64, "b2f_lr_binary_lossgrad_noalloc: device index %d out of range", dev);
+  if (!cached[dev]) {
+    void* p = nullptr;
+    B2F_CUDA(cudaGetSymbolAddress(&p, lr_na_scratch));
+    cached[dev] = static_cast<double*>(p);
+  }
+  *out = cached[dev];
+  return B2F_OK;
+}
+
+extern "C" int b2f_lr_binary_lossgrad_noalloc(const float* X, const float* y, const float* w, int64_t n, int d,
+                                              int64_t ld, const double* beta, const double* icpt, double* out,
+                                              b2f_stream_t stream) {
+  B2F_REQUIRE(X && y && beta && icpt && out, "b2f_lr_binary_lossgrad_noalloc: null pointer");
+  B2F_REQUIRE(n >= 0 && d > 0 && ld >= d && ld % 4 == 0, "b2f_lr_binary_lossgrad_noalloc: need ld >= d, ld %% 4 == 0");
+  B2F_REQUIRE(ld <= LR_NA_MAX_D,
+              "b2f_lr_binary_lossgrad_noalloc: padded feature count %lld exceeds the built-in scratch limit of %d; "
+              "use b2f_lr_binary_lossgrad with caller-provided scratch",
+              (long long)ld, LR_NA_MAX_D);
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_lr_binary_lossgrad_noalloc: X must be 16-byte aligned");
+  if (n == 0) return B2F_OK;
+  double* partials = nullptr;
+  int rc = lr_na_scratch_ptr(&partials);  // first call on a device does the one-time address lookup
+  if (rc != B2F_OK) return rc;
+  cudaStream_t st = b2f_cs(stream);
+  int grid = lr_grid_binary();
+  if (grid > LR_NA_MAX_PARTS) grid = LR_NA_MAX_PARTS;
+  // Nothing in the scratch has to start at zero: each CTA overwrites its whole d + 3 slice and the
+  // fold reads exactly the `grid` slices written by this call, so leftovers of earlier calls are inert.
+  const int nch = (int)((ld + 127) / 128);
+  if (nch <= 1) rc = lr_binary_launch<1>(X, y, w, n, d, ld, beta, icpt, partials, grid, st);
+  else if (nch <= 2) rc = lr_binary_launch<2>(X, y, w, n, d, ld, beta, icpt, partials, grid, st);
+  else rc = lr_binary_launch<4>(X, y, w, n, d, ld, beta, icpt, partials, grid, st);
+  if (rc != B2F_OK) return rc;
+  const int len = d + 3;
+  lr_fold_kernel<<<(len + 127) / 128, 128, 0, st>>>(partials, grid, len, out);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
