@@ -45,6 +45,8 @@ extern "C" {
 #define B2F_KM_GENERIC 1 /* CUDA-core fp32, any k / d */
 #define B2F_KM_TC3 2     /* tcgen05 3xTF32 (fp32-accurate) contraction, d % 32 == 0, k % 128 == 0 */
 #define B2F_KM_TC1 3     /* tcgen05 1xTF32 contraction (filter pass; labels need refine) */
+#define B2F_KM_TCB 4     /* tcgen05 bf16x3 filter pass + 3xTF32 re-check of uncertain rows; d in {64,128},
+                            k % 128 == 0; only through b2f_kmeans_step_ws (needs labels + workspace)    */
 
 typedef void* b2f_stream_t;
 
@@ -107,6 +109,15 @@ int b2f_kmeans_acc_zero(void* acc, int k, int d, b2f_stream_t stream);
  * labels (int32[n]) may be NULL; w (row weights) may be NULL; algo is a B2F_KM_* code.       */
 int b2f_kmeans_step(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep, int k,
                     void* acc, int32_t* labels, int algo, b2f_stream_t stream);
+/* Same pass with a caller-provided workspace (b2f_kmeans_ws_bytes(n, k, d) bytes, 256-byte aligned),
+ * which enables B2F_KM_TCB: rows whose label the bf16x3 pass cannot certify are listed in the
+ * workspace, gathered and re-assigned by the 3xTF32 kernel.  The list holds n/16 rows; if more rows are
+ * uncertain the excess is DROPPED and the payload's row count (last entry) comes out below n -- the
+ * caller must then redo the pass with B2F_KM_TC3.  B2F_KM_AUTO picks TCB when the shape allows it and
+ * labels / ws are given, else behaves like b2f_kmeans_step.  Same reference call site as above.        */
+size_t b2f_kmeans_ws_bytes(int64_t n, int k, int d);
+int b2f_kmeans_step_ws(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep, int k,
+                       void* acc, int32_t* labels, void* ws, size_t ws_bytes, int algo, b2f_stream_t stream);
 /* folds scratch replicas / partials into the fp64 payload at the head of acc */
 int b2f_kmeans_fold(void* acc, int k, int d, b2f_stream_t stream);
 /* centre update from the (all-reduced) payload: centres with count > 0 move to sums/count,

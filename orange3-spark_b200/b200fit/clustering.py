@@ -42,6 +42,16 @@ class CudaLloydEngine:
         self.status = torch.zeros(2, dtype=torch.int32, device=dev)
         self.status_f64 = torch.zeros(2, dtype=torch.float64, device=dev)
         self.launches = 0
+        self.fallbacks = 0
+        # bf16x3 filter pass + 3xTF32 re-check (B2F_KM_TCB) needs a labels buffer and a workspace
+        self.use_ws = (algo in (N.KM_AUTO, N.KM_TCB) and w is None and self.d in (64, 128) and self.k % 128 == 0
+                       and X.ld % 4 == 0 and X.n > 0)
+        if algo == N.KM_TCB and not self.use_ws:
+            raise ValueError("B2F_KM_TCB needs d in {64, 128}, k % 128 == 0 and no row weights")
+        if self.use_ws:
+            self.ws_bytes = int(self.L.b2f_kmeans_ws_bytes(X.n, self.k, self.d))
+            self.ws = torch.zeros(self.ws_bytes, dtype=torch.uint8, device=dev)
+            self.labels_buf = torch.empty(X.n, dtype=torch.int32, device=dev)
 
     def set_centers(self, C):
         torch = _torch()
@@ -56,16 +66,31 @@ class CudaLloydEngine:
                 "b2f_kmeans_prepare")
         self.launches += 1
 
-    def step(self, labels=None):
-        """Zero accumulators, assign + accumulate this shard, fold -> fp64 payload (device)."""
+    def step(self, labels=None, exact=False):
+        """Zero accumulators, assign + accumulate this shard, fold -> fp64 payload (device).
+        exact=True forces the 3xTF32 kernel (used when the re-check list of the bf16x3 pass overflowed)."""
         s = N.stream_ptr()
         X = self.X
         N.check(self.L.b2f_kmeans_acc_zero(N.ptr(self.acc), self.k, self.d, s), "b2f_kmeans_acc_zero")
-        N.check(self.L.b2f_kmeans_step(N.ptr(X.data), X.n, X.d, X.ld, N.ptr(self.w), N.ptr(self.prep), self.k,
-                                       N.ptr(self.acc), N.ptr(labels), self.algo, s), "b2f_kmeans_step")
+        if self.use_ws and not exact:
+            lab = labels if labels is not None else self.labels_buf
+            N.check(self.L.b2f_kmeans_step_ws(N.ptr(X.data), X.n, X.d, X.ld, None, N.ptr(self.prep), self.k,
+                                              N.ptr(self.acc), N.ptr(lab), N.ptr(self.ws), self.ws_bytes, self.algo,
+                                              s), "b2f_kmeans_step_ws")
+            self.launches += 4  # filter kernel, gather, 3xTF32 re-check, scatter
+        else:
+            algo = N.KM_TC3 if (exact or self.algo == N.KM_TCB) else self.algo
+            N.check(self.L.b2f_kmeans_step(N.ptr(X.data), X.n, X.d, X.ld, N.ptr(self.w), N.ptr(self.prep), self.k,
+                                           N.ptr(self.acc), N.ptr(labels), algo, s), "b2f_kmeans_step")
+            self.launches += 1
         N.check(self.L.b2f_kmeans_fold(N.ptr(self.acc), self.k, self.d, s), "b2f_kmeans_fold")
-        self.launches += 3
+        self.launches += 1
         return self.payload
+
+    def rows_counted(self, payload):
+        """Rows that were accumulated (last payload entry); below the row total means the re-check list
+        of the bf16x3 pass overflowed and the pass must be redone with exact=True."""
+        return float(payload[self.k * self.d + self.k + 1].item())
 
     def finalize_async(self, payload, tol):
         s = N.stream_ptr()
@@ -94,9 +119,22 @@ def lloyd(engine, comm, max_iter, tol):
     model holds the updated centres; trainingCost is the cost of the LAST assignment step."""
     it, converged, costs = 0, False, []
     payload = None
+    n_total = None
     while it < max_iter and not converged:
         payload = engine.step()
         comm.all_reduce_sum(payload)
+        if getattr(engine, "use_ws", False):
+            rows = engine.rows_counted(payload)
+            if n_total is None:
+                import torch
+
+                t = torch.tensor([float(engine.X.n)], dtype=torch.float64, device=payload.device)
+                comm.all_reduce_sum(t)
+                n_total = float(t.item())
+            if rows != n_total:  # some rank dropped uncertain rows: redo this pass with the 3xTF32 kernel
+                engine.fallbacks += 1
+                payload = engine.step(exact=True)
+                comm.all_reduce_sum(payload)
         converged, cost = engine.finalize(payload, tol)
         costs.append(cost)
         it += 1

@@ -43,9 +43,12 @@ static inline size_t b2f_align_up(size_t x, size_t a) { return (x + a - 1) / a *
 //          CH   float[k*d]   -2*c rounded to TF32 (low 13 mantissa bits zero)
 //          CL   float[k*d]   -2*c - CH, rounded to TF32
 //          CN   float[k]     ||c||^2 (fp32, from fp64)
-//          C64  double[k*d]  copy of the fp64 master (refine / exact paths) ]
+//          C64  double[k*d]  copy of the fp64 master (refine / exact paths)
+//          CB1  bf16[k*d]    -2*c rounded to bf16          (operands of the bf16x3 kernel)
+//          CB2  bf16[k*d]    -2*c - CB1, rounded to bf16
+//          MISC float[64]    [0] = max_j ||c_j|| (as float bits, written with atomicMax) ]
 struct KmPrepLayout {
-  size_t off_c32, off_ch, off_cl, off_cn, off_c64, bytes;
+  size_t off_c32, off_ch, off_cl, off_cn, off_c64, off_cb1, off_cb2, off_misc, bytes;
 };
 static inline KmPrepLayout km_prep_layout(int k, int d) {
   KmPrepLayout L;
@@ -56,6 +59,9 @@ static inline KmPrepLayout km_prep_layout(int k, int d) {
   L.off_cl = o;  o = b2f_align_up(o + kd * 4, 1024);
   L.off_cn = o;  o = b2f_align_up(o + (size_t)k * 4, 1024);
   L.off_c64 = o; o = b2f_align_up(o + kd * 8, 1024);
+  L.off_cb1 = o; o = b2f_align_up(o + kd * 2, 1024);
+  L.off_cb2 = o; o = b2f_align_up(o + kd * 2, 1024);
+  L.off_misc = o; o = b2f_align_up(o + 256, 1024);
   L.bytes = o;
   return L;
 }
@@ -107,6 +113,13 @@ __device__ __forceinline__ float4 ldg_stream(const float4* p) {
 #endif
 
 // implemented in kmeans_tc.cu
+// n_dev (optional, device): the kernel processes min(n, *n_dev) rows (row count known only on the device)
 int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
-               int passes, bool accumulate, cudaStream_t stream);
+               int passes, bool accumulate, const int* n_dev, cudaStream_t stream);
 bool km_tc_supported(int k, int d, int64_t ld);
+
+// implemented in kmeans_tcb.cu (bf16x3 filter pass + 3xTF32 re-check of ambiguous rows)
+bool km_tcb_supported(int k, int d, int64_t ld);
+size_t km_tcb_ws_bytes(int64_t n, int k, int d);
+int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
+                void* ws, size_t ws_bytes, bool accumulate, cudaStream_t stream);

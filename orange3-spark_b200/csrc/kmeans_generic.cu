@@ -4,6 +4,8 @@
 //   reference: orangecontrib/spark/base/spark_ml_estimator.py:22 (module = clustering,
 //   orangecontrib/spark/widgets/ml/spark_ml_clustering.py:14) and
 //   orangecontrib/spark/widgets/ml/spark_ml_model.py:53;  MLlib semantics: SURVEY.md A.2.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 // ---------------------------------------------------------------------------------------------
@@ -11,7 +13,8 @@
 // ---------------------------------------------------------------------------------------------
 __global__ void km_prepare_kernel(const double* __restrict__ C, int k, int d, float* __restrict__ c32,
                                   float* __restrict__ ch, float* __restrict__ cl, float* __restrict__ cn,
-                                  double* __restrict__ c64) {
+                                  double* __restrict__ c64, __nv_bfloat16* __restrict__ cb1,
+                                  __nv_bfloat16* __restrict__ cb2, unsigned int* __restrict__ misc) {
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -27,9 +30,16 @@ __global__ void km_prepare_kernel(const double* __restrict__ C, int k, int d, fl
       const float hi = to_tf32((float)m2);
       ch[i] = hi;
       cl[i] = to_tf32((float)(m2 - (double)hi));
+      const __nv_bfloat16 b1 = __float2bfloat16_rn((float)m2);
+      cb1[i] = b1;
+      cb2[i] = __float2bfloat16_rn((float)(m2 - (double)__bfloat162float(b1)));
     }
     nn = warp_sum(nn);
-    if (lane == 0) cn[j] = (float)nn;
+    if (lane == 0) {
+      cn[j] = (float)nn;
+      // max_j ||c_j|| rounded up: non-negative floats order like their bit patterns
+      atomicMax(misc, __float_as_uint(__fsqrt_ru((float)nn * 1.0000002f)));
+    }
   }
 }
 
@@ -263,10 +273,12 @@ extern "C" int b2f_kmeans_prepare(const double* centers, int k, int d, void* pre
   KmPrepLayout L = km_prep_layout(k, d);
   char* p = static_cast<char*>(prep);
   int grid = (k + 7) / 8;
+  B2F_CUDA(cudaMemsetAsync(p + L.off_misc, 0, 256, b2f_cs(stream)));
   km_prepare_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(
       centers, k, d, reinterpret_cast<float*>(p + L.off_c32), reinterpret_cast<float*>(p + L.off_ch),
       reinterpret_cast<float*>(p + L.off_cl), reinterpret_cast<float*>(p + L.off_cn),
-      reinterpret_cast<double*>(p + L.off_c64));
+      reinterpret_cast<double*>(p + L.off_c64), reinterpret_cast<__nv_bfloat16*>(p + L.off_cb1),
+      reinterpret_cast<__nv_bfloat16*>(p + L.off_cb2), reinterpret_cast<unsigned int*>(p + L.off_misc));
   B2F_LAUNCH_CHECK();
   return B2F_OK;
 }
@@ -296,12 +308,30 @@ extern "C" int b2f_kmeans_step(const float* X, int64_t n, int d, int64_t ld, con
   if (algo == B2F_KM_TC3 || algo == B2F_KM_TC1) {
     B2F_REQUIRE(!w, "b2f_kmeans_step: the tensor-core path does not take row weights");
     B2F_REQUIRE(km_tc_supported(k, d, ld), "b2f_kmeans_step: tensor-core path needs d %% 32 == 0, d <= 256, k %% 128 == 0");
-    return km_tc_step(X, n, d, ld, prep, k, acc, labels, algo == B2F_KM_TC3 ? 3 : 1, true, b2f_cs(stream));
+    return km_tc_step(X, n, d, ld, prep, k, acc, labels, algo == B2F_KM_TC3 ? 3 : 1, true, nullptr, b2f_cs(stream));
   }
   B2F_REQUIRE(algo == B2F_KM_GENERIC, "b2f_kmeans_step: unknown algo %d", algo);
   return km_generic_launch(X, n, d, ld, w, reinterpret_cast<const float*>(pp + P.off_c32), k,
                            reinterpret_cast<double*>(ap + A.off_payload), reinterpret_cast<float*>(ap + A.off_rep),
                            labels, nullptr, true, b2f_cs(stream));
+}
+
+extern "C" size_t b2f_kmeans_ws_bytes(int64_t n, int k, int d) {
+  return (n >= 0 && k > 0 && d > 0) ? km_tcb_ws_bytes(n, k, d) : 0;
+}
+
+extern "C" int b2f_kmeans_step_ws(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep,
+                                  int k, void* acc, int32_t* labels, void* ws, size_t ws_bytes, int algo,
+                                  b2f_stream_t stream) {
+  B2F_REQUIRE(X && prep && acc, "b2f_kmeans_step_ws: null pointer");
+  B2F_REQUIRE(n >= 0 && d > 0 && k > 0 && ld >= d && ld % 4 == 0, "b2f_kmeans_step_ws: need ld >= d, ld %% 4 == 0");
+  if (algo == B2F_KM_AUTO && !w && labels && ws && km_tcb_supported(k, d, ld)) algo = B2F_KM_TCB;
+  if (algo != B2F_KM_TCB) return b2f_kmeans_step(X, n, d, ld, w, prep, k, acc, labels, algo, stream);
+  B2F_REQUIRE(!w, "b2f_kmeans_step_ws: the tensor-core path does not take row weights");
+  B2F_REQUIRE(km_tcb_supported(k, d, ld), "b2f_kmeans_step_ws: B2F_KM_TCB needs d in {64, 128} and k %% 128 == 0");
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_kmeans_step_ws: X must be 16-byte aligned");
+  if (n == 0) return B2F_OK;
+  return km_tcb_step(X, n, d, ld, prep, k, acc, labels, ws, ws_bytes, true, b2f_cs(stream));
 }
 
 extern "C" int b2f_kmeans_fold(void* acc, int k, int d, b2f_stream_t stream) {
@@ -339,7 +369,7 @@ extern "C" int b2f_kmeans_predict(const float* X, int64_t n, int d, int64_t ld, 
   if (dist2) algo = B2F_KM_GENERIC;  // exact distances come from the direct-form kernel
   if (algo == B2F_KM_TC3 || algo == B2F_KM_TC1) {
     B2F_REQUIRE(km_tc_supported(k, d, ld), "b2f_kmeans_predict: tensor-core path needs d %% 32 == 0, d <= 256, k %% 128 == 0");
-    return km_tc_step(X, n, d, ld, prep, k, nullptr, labels, algo == B2F_KM_TC3 ? 3 : 1, false, b2f_cs(stream));
+    return km_tc_step(X, n, d, ld, prep, k, nullptr, labels, algo == B2F_KM_TC3 ? 3 : 1, false, nullptr, b2f_cs(stream));
   }
   return km_generic_launch(X, n, d, ld, nullptr, reinterpret_cast<const float*>(pp + P.off_c32), k, nullptr, nullptr,
                            labels, dist2, false, b2f_cs(stream));

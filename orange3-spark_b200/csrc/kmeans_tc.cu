@@ -11,134 +11,20 @@
 // Replaces MLlib's findClosest + axpy loop behind KMeans.fit;
 //   reference call site: orangecontrib/spark/base/spark_ml_estimator.py:22.
 //
-// CTA = 384 threads, persistent (one CTA per SM), warp roles:
+// CTA = 512 threads, persistent (one CTA per SM), warp roles:
 //   warp 0  X producer   : TMA loads of the 128-row X tile (KC chunks of 128 rows x 32 floats)
 //   warp 1  MMA issuer   : one elected thread issues tcgen05.mma, commits to mbarriers
 //   warp 2  B producer   : TMA loads of centre operand stages (C_hi / C_lo chunk of 128 centres)
 //   warp 3  TMEM allocator
 //   warps 4-7 (128 thr)  : epilogue: tcgen05.ld, + ||c||^2, running argmin (thread == row), labels
-//   warps 8-11 (128 thr) : split each landed X chunk into explicit TF32 hi / lo operands, then
-//                          the row -> centroid accumulation of the PREVIOUS tile (16-byte vector
-//                          reductions into fp32 replicas), cost and counts -- decoupled from the
-//                          argmin warps so neither stalls the tensor pipe.
-#include <cuda.h>
-#include <stdlib.h>
-
-#include "common.cuh"
+//   warps 8-11 (128 thr) : split each landed X chunk into explicit TF32 hi / lo operands (tcgen05.st
+//                          into tensor memory: the MMA takes A from TMEM)
+//   warps 12-15 (128 thr): row -> centroid accumulation of finished tiles (16-byte vector reductions
+//                          into fp32 replicas), cost and counts -- decoupled from the argmin and
+//                          split warps so nothing stalls the tensor pipe.
+#include "tc_common.cuh"
 
 namespace {
-
-constexpr int TM = 128;            // rows per tile == UMMA M == TMEM lanes
-constexpr int TN = 128;            // centres per accumulator tile == UMMA N
-constexpr int CHUNK_BYTES = TM * 128;  // 128 rows x 32 floats, 128B swizzle atom rows
-constexpr int NTHREADS = 384;
-constexpr int EPI_THREADS = 128;
-constexpr uint32_t TMEM_COLS = 512;  // [0,256) two accumulator buffers | [256,384) X_hi | [384,512) X_lo
-constexpr uint32_t TMEM_A_HI = 256, TMEM_A_LO = 384;
-
-// ---------------------------------------------------------------------------------------------
-// PTX wrappers
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-// Bounded wait: a protocol bug must trap, never hang the GPU.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000ll) {
-      printf("b200fit km_tc: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-      __trap();
-    }
-  }
-}
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
-          smem_u32(dst)),
-      "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
-      : "memory");
-}
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile(
-      "{\n\t.reg .pred P;\n\t"
-      "elect.sync _|P, 0xffffffff;\n\t"
-      "selp.u32 %0, 1, 0, P;\n\t}"
-      : "=r"(pred));
-  return pred != 0;
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-               : "memory");
-}
-// A operand from tensor memory (lanes = rows, columns = K), B from shared memory
-__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
-                                               uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
-      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
-      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
-      "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]),
-      "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]),
-      "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
-      : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void red_add_v4(float* p, float4 v) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-               : "memory");
-}
-
-// Shared-memory matrix descriptor (SM100 UMMA) for a K-major, 128B-swizzled operand tile whose 8-row
-// groups are 1024 B apart:  start>>4 | LBO(=1, unused for swizzled K-major)<<16 | SBO(1024>>4)<<32 |
-// version(1)<<46 | SWIZZLE_128B(2)<<61.  The MMA issuer builds it as desc_fixed | (address >> 4).
-// kind::tf32, fp32 accumulate, A and B K-major, M = 128, N = TN
-constexpr uint32_t IDESC_TF32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 
 struct Smem {
   // lives behind the operand tiles in dynamic shared memory (see km_tc_kernel for the carve-up)
@@ -160,7 +46,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
                  const __grid_constant__ CUtensorMap map_cl, const float* __restrict__ X, int64_t n, int d, int64_t ld,
                  const float* __restrict__ cn, int k, int nstages, double* __restrict__ payload,
                  float* __restrict__ rep, unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels,
-                 int accumulate, int dbg) {
+                 int accumulate, int dbg, const int* __restrict__ n_dev) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];  // 128B swizzle atoms need 1024-byte alignment
   uint8_t* base = smem_raw;
   if (smem_u32(base) & 1023u) __trap();
@@ -171,6 +57,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   Smem* sm = reinterpret_cast<Smem*>(stages + (size_t)nstages * stage_bytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (n_dev) n = min(n, (int64_t)max(*n_dev, 0));  // row count produced on the device (re-check pass)
   const int64_t ntiles = (n + TM - 1) / TM;
   const int NT = k / TN;
 
@@ -245,37 +132,53 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     const uint32_t st_a = smem_u32(stages) >> 4;
     const uint32_t chunk16 = CHUNK_BYTES >> 4, stage16 = (uint32_t)stage_bytes >> 4;
     uint32_t it = 0, acc_it = 0, stage = 0, bphase = 0;
+    const int KB = (KC % 2 == 0) ? 2 : 1;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       for (int nt = 0; nt < NT; ++nt, ++acc_it) {
         const uint32_t buf = acc_it & 1;
         mbar_wait(&sm->t_empty[buf], ((acc_it >> 1) & 1) ^ 1);  // epilogue drained this accumulator
         const uint32_t tmem_d = tmem_base + buf * TN;
-        for (int kc = 0; kc < KC; ++kc) {
-          if (nt == 0) mbar_wait(&sm->xa_full[kc], it & 1);  // X chunk split into hi / lo sits in TMEM
-          if (!(dbg & 1) || bphase == 0) mbar_wait(&sm->b_full[stage], bphase);
-          tc_fence_after();
-          if (elect_one()) {
-            const uint32_t a_hi = tmem_base + TMEM_A_HI + kc * 32;  // 32 TMEM columns per chunk
-            const uint32_t a_lo = tmem_base + TMEM_A_LO + kc * 32;
-            const uint64_t b_hi = desc_fixed | (uint64_t)(st_a + stage * stage16);
-            const uint64_t b_lo = b_hi + chunk16;
+        // Issue in batches of KB chunks: the tensor queue is only a few instructions deep, so the fixed
+        // cost of one wait / elect / commit round must be amortised over a long run of MMAs.
+        for (int kc0 = 0; kc0 < KC; kc0 += KB) {
+          uint32_t st_idx[2];
 #pragma unroll
-            for (int k8 = 0; k8 < 4; ++k8) {  // 8 tf32 = 32 bytes = 2 descriptor units along K
-              tc_mma_tf32_ts(tmem_d, a_hi + 8 * k8, b_hi + 2 * k8, IDESC_TF32, (kc | k8) ? 1u : 0u);
-              if (NPASS == 3) {
-                tc_mma_tf32_ts(tmem_d, a_hi + 8 * k8, b_lo + 2 * k8, IDESC_TF32, 1u);
-                tc_mma_tf32_ts(tmem_d, a_lo + 8 * k8, b_hi + 2 * k8, IDESC_TF32, 1u);
+          for (int j = 0; j < 2; ++j) {
+            if (j < KB) {
+              if (nt == 0) mbar_wait(&sm->xa_full[kc0 + j], it & 1);  // X chunk (hi / lo) sits in TMEM
+              if (!(dbg & 1) || bphase == 0) mbar_wait(&sm->b_full[stage], bphase);
+              st_idx[j] = stage;
+              if (++stage == (uint32_t)nstages) {
+                stage = 0;
+                bphase ^= 1;
               }
             }
-            tc_commit(&sm->b_empty[stage]);                      // stage may be refilled once these retire
-            if (nt == NT - 1) tc_commit(&sm->xa_empty[kc]);      // TMEM X chunk free for the next tile
-            if (kc == KC - 1) tc_commit(&sm->t_full[buf]);       // accumulator complete
+          }
+          tc_fence_after();
+          if (elect_one()) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              if (j < KB) {
+                const int kc = kc0 + j;
+                const uint32_t a_hi = tmem_base + TMEM_A_HI + kc * 32;  // 32 TMEM columns per chunk
+                const uint32_t a_lo = tmem_base + TMEM_A_LO + kc * 32;
+                const uint64_t b_hi = desc_fixed | (uint64_t)(st_a + st_idx[j] * stage16);
+                const uint64_t b_lo = b_hi + chunk16;
+#pragma unroll
+                for (int k8 = 0; k8 < 4; ++k8) {  // 8 tf32 = 32 bytes = 2 descriptor units along K
+                  tc_mma_tf32_ts(tmem_d, a_hi + 8 * k8, b_hi + 2 * k8, IDESC_TF32, (kc | k8) ? 1u : 0u);
+                  if (NPASS == 3) {
+                    tc_mma_tf32_ts(tmem_d, a_hi + 8 * k8, b_lo + 2 * k8, IDESC_TF32, 1u);
+                    tc_mma_tf32_ts(tmem_d, a_lo + 8 * k8, b_hi + 2 * k8, IDESC_TF32, 1u);
+                  }
+                }
+                tc_commit(&sm->b_empty[st_idx[j]]);                  // stage may be refilled once these retire
+                if (nt == NT - 1) tc_commit(&sm->xa_empty[kc]);      // TMEM X chunk free for the next tile
+              }
+            }
+            if (kc0 + KB >= KC) tc_commit(&sm->t_full[buf]);        // accumulator complete
           }
           __syncwarp();
-          if (++stage == (uint32_t)nstages) {
-            stage = 0;
-            bphase ^= 1;
-          }
         }
       }
     }
@@ -334,67 +237,69 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         mbar_arrive(&sm->a_full[ab]);  // release semantics order the two stores before the arrive
       }
     }
-  } else if (warp >= 8) {
-    // ===================== split X into TF32 hi / lo; accumulate finished row tiles =====================
+  } else if (warp >= 8 && warp < 12) {
+    // ===================== split X into explicit TF32 hi / lo operands in tensor memory =====================
     const int w4 = warp - 8;
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      // thread == row: read the row's 32 floats of each chunk from the swizzled staging tile
+      // (16-byte piece p of row r sits at r*128 + ((p ^ (r & 7)) << 4)), split into explicit TF32
+      // hi / lo, and store them as the A operand in tensor memory (lane = row, column = k).
+      const int r = w4 * 32 + lane;
+      const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
+      for (int kc = 0; kc < KC; ++kc) {
+        mbar_wait(&sm->xs_full[kc], it & 1);
+        const uint8_t* src = xs + (size_t)kc * CHUNK_BYTES + (size_t)r * 128;
+        uint32_t hi[32], lo[32];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          const float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
+          const float h0 = to_tf32(v.x), h1 = to_tf32(v.y), h2 = to_tf32(v.z), h3 = to_tf32(v.w);
+          hi[p * 4 + 0] = __float_as_uint(h0); hi[p * 4 + 1] = __float_as_uint(h1);
+          hi[p * 4 + 2] = __float_as_uint(h2); hi[p * 4 + 3] = __float_as_uint(h3);
+          if (NPASS == 3) {
+            lo[p * 4 + 0] = __float_as_uint(to_tf32(v.x - h0)); lo[p * 4 + 1] = __float_as_uint(to_tf32(v.y - h1));
+            lo[p * 4 + 2] = __float_as_uint(to_tf32(v.z - h2)); lo[p * 4 + 3] = __float_as_uint(to_tf32(v.w - h3));
+          }
+        }
+        mbar_arrive(&sm->xs_empty[kc]);                 // staging chunk may be refilled (next tile)
+        mbar_wait(&sm->xa_empty[kc], (it & 1) ^ 1);     // previous tile's MMAs are done with this TMEM chunk
+        tc_fence_after();
+        tmem_st32(tmem_base + lane_addr + TMEM_A_HI + kc * 32, hi);
+        if (NPASS == 3) tmem_st32(tmem_base + lane_addr + TMEM_A_LO + kc * 32, lo);
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(&sm->xa_full[kc]);
+      }
+    }
+  } else if (warp >= 12) {
+    // ===================== accumulate finished row tiles (own warps: never delays the split) ==========
+    const int w4 = warp - 12;
     double cost = 0.0;
     unsigned long long nrows = 0;
     float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
     const int nch = (d + 127) / 128;
     uint32_t it = 0;
-    int64_t prev_tile = -1;
-    for (int64_t tile = blockIdx.x;; tile += gridDim.x, ++it) {
-      const bool have = tile < ntiles;
-      if (have) {
-        // thread == row: read the row's 32 floats of each chunk from the swizzled staging tile
-        // (16-byte piece p of row r sits at r*128 + ((p ^ (r & 7)) << 4)), split into explicit TF32
-        // hi / lo, and store them as the A operand in tensor memory (lane = row, column = k).
-        const int r = w4 * 32 + lane;
-        const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
-        for (int kc = 0; kc < KC; ++kc) {
-          mbar_wait(&sm->xs_full[kc], it & 1);
-          const uint8_t* src = xs + (size_t)kc * CHUNK_BYTES + (size_t)r * 128;
-          uint32_t hi[32], lo[32];
-#pragma unroll
-          for (int p = 0; p < 8; ++p) {
-            const float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
-            const float h0 = to_tf32(v.x), h1 = to_tf32(v.y), h2 = to_tf32(v.z), h3 = to_tf32(v.w);
-            hi[p * 4 + 0] = __float_as_uint(h0); hi[p * 4 + 1] = __float_as_uint(h1);
-            hi[p * 4 + 2] = __float_as_uint(h2); hi[p * 4 + 3] = __float_as_uint(h3);
-            if (NPASS == 3) {
-              lo[p * 4 + 0] = __float_as_uint(to_tf32(v.x - h0)); lo[p * 4 + 1] = __float_as_uint(to_tf32(v.y - h1));
-              lo[p * 4 + 2] = __float_as_uint(to_tf32(v.z - h2)); lo[p * 4 + 3] = __float_as_uint(to_tf32(v.w - h3));
-            }
-          }
-          mbar_arrive(&sm->xs_empty[kc]);                 // staging chunk may be refilled (next tile)
-          mbar_wait(&sm->xa_empty[kc], (it & 1) ^ 1);     // previous tile's MMAs are done with this TMEM chunk
-          tc_fence_after();
-          tmem_st32(tmem_base + lane_addr + TMEM_A_HI + kc * 32, hi);
-          if (NPASS == 3) tmem_st32(tmem_base + lane_addr + TMEM_A_LO + kc * 32, lo);
-          tmem_st_wait();
-          tc_fence_before();
-          mbar_arrive(&sm->xa_full[kc]);
-        }
-      }
-      if (accumulate && prev_tile >= 0) {
+    if (accumulate) {
+      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         // rows of the previous tile: labels / scores come from the epilogue warps, the row values are
         // re-read from global memory (L2 hits: the tile was just streamed in by TMA)
-        const uint32_t pit = it - 1;
+        const uint32_t pit = it;
         const int ab = pit & 1;
         mbar_wait(&sm->a_full[ab], (pit >> 1) & 1);
         const int my_lab = sm->lab[ab][w4 * 32 + lane];
         const float my_sc = sm->score[ab][w4 * 32 + lane];
         mbar_arrive(&sm->a_empty[ab]);
-        const int64_t r0 = prev_tile * TM + w4 * 32;
+        const int64_t r0 = tile * TM + w4 * 32;
         for (int g = 0; g < 32; g += 8) {
           float4 xv[8];
-#pragma unroll
+  #pragma unroll
           for (int u = 0; u < 8; ++u) {
             const int64_t rr = r0 + g + u;
             xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (rr < n && lane * 4 < d) xv[u] = *reinterpret_cast<const float4*>(X + rr * ld + lane * 4);
           }
-#pragma unroll
+  #pragma unroll
           for (int u = 0; u < 8; ++u) {
             const int64_t rr = r0 + g + u;
             const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
@@ -425,8 +330,6 @@ __global__ void __launch_bounds__(NTHREADS, 1)
           }
         }
       }
-      if (!have) break;
-      prev_tile = tile;
     }
     if (accumulate && lane == 0) {
       atomicAdd(payload + (size_t)k * d + k, cost);
@@ -444,44 +347,6 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-        qres == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  }
-  return fn;
-}
-
-// 2-D fp32 row-major [rows, cols] (row pitch `pitch` floats), box = 32 floats x 128 rows, 128B swizzle
-static int make_map(CUtensorMap* m, const float* base, uint64_t rows, uint64_t cols, uint64_t pitch) {
-  EncodeTiledFn enc = get_encode_fn();
-  if (!enc) {
-    b2f_set_error("cuTensorMapEncodeTiled is not available from this driver");
-    return B2F_ECUDA;
-  }
-  cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {pitch * sizeof(float)};
-  cuuint32_t box[2] = {32, (cuuint32_t)TM};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    b2f_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%llu cols=%llu pitch=%llu)", (int)r,
-                  (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)pitch);
-    return B2F_ECUDA;
-  }
-  return B2F_OK;
-}
-
 static const int kSmemLimit = 227 * 1024;
 
 static int km_tc_stages(int d, int passes) {
@@ -502,7 +367,7 @@ bool km_tc_supported(int k, int d, int64_t ld) {
 }
 
 int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
-               int passes, bool accumulate, cudaStream_t stream) {
+               int passes, bool accumulate, const int* n_dev, cudaStream_t stream) {
   B2F_REQUIRE(passes == 1 || passes == 3, "km_tc_step: passes must be 1 or 3");
   B2F_REQUIRE(n < (1ll << 31) * (int64_t)TM, "km_tc_step: too many rows for one launch");
   const int nstages = km_tc_stages(d, passes);
@@ -514,9 +379,9 @@ int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, i
   const float* cn = reinterpret_cast<const float*>(pp + P.off_cn);
   CUtensorMap mx, mh, ml;
   int rc;
-  if ((rc = make_map(&mx, X, (uint64_t)n, (uint64_t)d, (uint64_t)ld)) != B2F_OK) return rc;
-  if ((rc = make_map(&mh, ch, (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
-  if ((rc = make_map(&ml, cl, (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
+  if ((rc = make_map_f32(&mx, X, (uint64_t)n, (uint64_t)d, (uint64_t)ld)) != B2F_OK) return rc;
+  if ((rc = make_map_f32(&mh, ch, (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
+  if ((rc = make_map_f32(&ml, cl, (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
   double* payload = nullptr;
   float* rep = nullptr;
   unsigned long long* cnt = nullptr;
@@ -538,11 +403,11 @@ int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, i
   if (passes == 3) {
     B2F_CUDA(cudaFuncSetAttribute(km_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     km_tc_kernel<3><<<grid, NTHREADS, smem, stream>>>(mx, mh, ml, X, n, d, ld, cn, k, nstages, payload, rep, cnt,
-                                                      labels, accumulate ? 1 : 0, dbg);
+                                                      labels, accumulate ? 1 : 0, dbg, n_dev);
   } else {
     B2F_CUDA(cudaFuncSetAttribute(km_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     km_tc_kernel<1><<<grid, NTHREADS, smem, stream>>>(mx, mh, ml, X, n, d, ld, cn, k, nstages, payload, rep, cnt,
-                                                      labels, accumulate ? 1 : 0, dbg);
+                                                      labels, accumulate ? 1 : 0, dbg, n_dev);
   }
   B2F_LAUNCH_CHECK();
   return B2F_OK;

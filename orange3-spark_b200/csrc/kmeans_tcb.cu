@@ -1,0 +1,493 @@
+// K2 fused Lloyd kernel, bf16x3 filter pass + exact re-check (sm_100a only).
+//
+// The 3xTF32 kernel (kmeans_tc.cu) is limited by the tensor pipe under the board power cap.  This
+// variant halves the tensor work: x = x1 + x2 (+ r), c' = -2c = c1 + c2 (+ r), all bf16, and
+//     score ~= x1.c1 + x1.c2 + x2.c1 + ||c||^2        (three kind::f16 MMAs, fp32 accumulation)
+// whose error is bounded per row by  tau = kappa * ||x|| * max_j ||c_j||  (dropped terms <= 3 u^2 per
+// operand pair with u = 2^-8, plus accumulation slack).  A row whose best and second-best scores are
+// more than 2 tau apart has a CERTAIN label; every other row is appended to a list, gathered into a
+// compact matrix and re-assigned by the 3xTF32 kernel, which also does its accumulation.  So labels,
+// sums and counts equal the 3xTF32 path's; only the cost of certain rows carries the bf16x3 error
+// (zero-mean, ~1e-4 relative per row).
+//
+// Replaces MLlib's findClosest + axpy loop behind KMeans.fit;
+//   reference call site: orangecontrib/spark/base/spark_ml_estimator.py:22.
+//
+// CTA = 512 threads, persistent, one per SM:
+//   warp 0  X producer (TMA, fp32 staging chunks of 128 rows x 32 floats)
+//   warp 1  MMA issuer (one batch of 12*KA tcgen05.mma per centre tile, A operand from tensor memory)
+//   warp 2  B producer (TMA, stage = 128 centres x 64 k of c1 and of c2, bf16, 128B swizzle)
+//   warp 3  TMEM allocator
+//   warps 4-7   epilogue: tcgen05.ld, + ||c||^2, running best / second best, certainty test
+//   warps 8-11  split: fp32 row -> x1, x2 bf16 pairs -> tcgen05.st into tensor memory; row norms
+//   warps 12-15 accumulate certain rows (16-byte vector reductions), cost, counts
+#include <cuda_bf16.h>
+
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr uint32_t TB_TMEM_COLS = 512;  // [0,256) two accumulators | [256,320) x1 | [320,384) x2 (bf16 pairs)
+constexpr uint32_t TB_A1 = 256, TB_A2 = 320;
+constexpr int TB_THREADS = 512;
+constexpr int TB_STAGE_BYTES = 2 * CHUNK_BYTES;  // c1 atom + c2 atom (128 centres x 64 bf16 each)
+// kind::f16, bf16 inputs, fp32 accumulate, A and B K-major, M = 128, N = TN
+constexpr uint32_t IDESC_BF16 =
+    (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+
+struct SmemB {
+  uint64_t xs_full[4], xs_empty[4];  // fp32 staging, per 32-float chunk
+  uint64_t xa_full[2], xa_empty[2];  // TMEM operand, per 64-k atom
+  uint64_t b_full[8], b_empty[8];
+  uint64_t t_full[2], t_empty[2];
+  uint64_t a_full[2], a_empty[2];    // epilogue -> accumulate hand-off
+  uint64_t n_full[2];                // split -> epilogue: squared row norms of a tile
+  uint32_t tmem_base;
+  int lab[2][TM];                    // certain label, or -1 for a row sent to the re-check list
+  float score[2][TM];
+  float xnorm2[2][TM];
+};
+
+struct TcbWs {  // header of the caller-provided workspace
+  int count;    // rows appended to the re-check list (may exceed cap: the excess is dropped)
+  int used;     // min(count, cap), written by the gather kernel
+  int pad[62];
+};
+
+__device__ __forceinline__ void tc_mma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(IDESC_BF16), "r"(accumulate)
+      : "memory");
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(TB_THREADS, 1)
+    km_tcb_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c1,
+                  const __grid_constant__ CUtensorMap map_c2, const float* __restrict__ X, int64_t n, int d,
+                  int64_t ld, const float* __restrict__ cn, const float* __restrict__ cmax_ptr, float kappa2, int k,
+                  int nstages, double* __restrict__ payload, float* __restrict__ rep,
+                  unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels, int accumulate,
+                  TcbWs* __restrict__ ws, int32_t* __restrict__ amb_idx, int cap) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  if (smem_u32(smem_raw) & 1023u) __trap();
+  const int KC = d / 32;  // fp32 staging chunks
+  const int KA = d / 64;  // 64-k atoms of the bf16 operands
+  uint8_t* xs = smem_raw;
+  uint8_t* stages = xs + (size_t)KC * CHUNK_BYTES;
+  SmemB* sm = reinterpret_cast<SmemB*>(stages + (size_t)nstages * TB_STAGE_BYTES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t ntiles = (n + TM - 1) / TM;
+  const int NT = k / TN;
+
+  if (threadIdx.x == 0) {
+    for (int c = 0; c < 4; ++c) {
+      mbar_init(&sm->xs_full[c], 1);
+      mbar_init(&sm->xs_empty[c], EPI_THREADS);
+    }
+    for (int c = 0; c < 2; ++c) {
+      mbar_init(&sm->xa_full[c], EPI_THREADS);
+      mbar_init(&sm->xa_empty[c], 1);
+      mbar_init(&sm->t_full[c], 1);
+      mbar_init(&sm->t_empty[c], EPI_THREADS);
+      mbar_init(&sm->a_full[c], EPI_THREADS);
+      mbar_init(&sm->a_empty[c], EPI_THREADS);
+      mbar_init(&sm->n_full[c], EPI_THREADS);
+    }
+    for (int s = 0; s < 8; ++s) {
+      mbar_init(&sm->b_full[s], 1);
+      mbar_init(&sm->b_empty[s], 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 3) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm->tmem_base)),
+                 "r"(TB_TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sm->tmem_base;
+
+  if (warp == 0) {
+    // ===================== X producer =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        for (int kc = 0; kc < KC; ++kc) {
+          mbar_wait(&sm->xs_empty[kc], (it & 1) ^ 1);
+          mbar_expect_tx(&sm->xs_full[kc], (uint32_t)CHUNK_BYTES);
+          tma_load_2d(xs + (size_t)kc * CHUNK_BYTES, &map_x, kc * 32, (int)(tile * TM), &sm->xs_full[kc]);
+        }
+      }
+    }
+  } else if (warp == 2) {
+    // ===================== B producer =====================
+    if (lane == 0) {
+      uint32_t s = 0, ph = 0;
+      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (int nt = 0; nt < NT; ++nt) {
+          for (int a = 0; a < KA; ++a) {
+            mbar_wait(&sm->b_empty[s], ph ^ 1);
+            mbar_expect_tx(&sm->b_full[s], (uint32_t)TB_STAGE_BYTES);
+            uint8_t* dst = stages + (size_t)s * TB_STAGE_BYTES;
+            tma_load_2d(dst, &map_c1, a * 64, nt * TN, &sm->b_full[s]);
+            tma_load_2d(dst + CHUNK_BYTES, &map_c2, a * 64, nt * TN, &sm->b_full[s]);
+            if (++s == (uint32_t)nstages) {
+              s = 0;
+              ph ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer: one batch (12 * KA instructions) per centre tile =====================
+    const uint64_t desc_fixed = (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+    const uint32_t st_a = smem_u32(stages) >> 4;
+    const uint32_t chunk16 = CHUNK_BYTES >> 4, stage16 = (uint32_t)TB_STAGE_BYTES >> 4;
+    uint32_t it = 0, acc_it = 0, stage = 0, bphase = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      for (int nt = 0; nt < NT; ++nt, ++acc_it) {
+        const uint32_t buf = acc_it & 1;
+        mbar_wait(&sm->t_empty[buf], ((acc_it >> 1) & 1) ^ 1);
+        const uint32_t tmem_d = tmem_base + buf * TN;
+        uint32_t st_idx[2];
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          if (a < KA) {
+            if (nt == 0) mbar_wait(&sm->xa_full[a], it & 1);
+            mbar_wait(&sm->b_full[stage], bphase);
+            st_idx[a] = stage;
+            if (++stage == (uint32_t)nstages) {
+              stage = 0;
+              bphase ^= 1;
+            }
+          }
+        }
+        tc_fence_after();
+        if (elect_one()) {
+#pragma unroll
+          for (int a = 0; a < 2; ++a) {
+            if (a < KA) {
+              const uint32_t a1 = tmem_base + TB_A1 + a * 32;  // 32 columns = 64 bf16 of k per atom
+              const uint32_t a2 = tmem_base + TB_A2 + a * 32;
+              const uint64_t b1 = desc_fixed | (uint64_t)(st_a + st_idx[a] * stage16);
+              const uint64_t b2 = b1 + chunk16;
+#pragma unroll
+              for (int s = 0; s < 4; ++s) {  // 16 bf16 of k = 32 bytes = 2 descriptor units, 8 TMEM columns
+                tc_mma_bf16_ts(tmem_d, a1 + 8 * s, b1 + 2 * s, (a | s) ? 1u : 0u);
+                tc_mma_bf16_ts(tmem_d, a1 + 8 * s, b2 + 2 * s, 1u);
+                tc_mma_bf16_ts(tmem_d, a2 + 8 * s, b1 + 2 * s, 1u);
+              }
+              tc_commit(&sm->b_empty[st_idx[a]]);
+              if (nt == NT - 1) tc_commit(&sm->xa_empty[a]);
+            }
+          }
+          tc_commit(&sm->t_full[buf]);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ===================== epilogue: best / second best per row, certainty test =====================
+    const int q = warp & 3;
+    const int row_in_tile = q * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    const float cmax = *cmax_ptr;
+    uint32_t it = 0, acc_it = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      float b1a = INFINITY, b2a = INFINITY, b1b = INFINITY, b2b = INFINITY;
+      int i1a = 0, i1b = 1;
+      for (int nt = 0; nt < NT; ++nt, ++acc_it) {
+        const int buf = acc_it & 1;
+        mbar_wait(&sm->t_full[buf], (acc_it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + lane_addr + (uint32_t)(buf * TN);
+        uint32_t v[2][32];
+        tmem_ld32(taddr, v[0]);
+#pragma unroll
+        for (int c = 0; c < TN / 32; ++c) {
+          tmem_ld_wait();
+          if (c + 1 < TN / 32) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+          const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + c * 32);
+          const int jbase = nt * TN + c * 32;
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 cv = __ldg(cn4 + j4);
+            const float s0 = __uint_as_float(v[c & 1][j4 * 4 + 0]) + cv.x;
+            const float s1 = __uint_as_float(v[c & 1][j4 * 4 + 1]) + cv.y;
+            const float s2 = __uint_as_float(v[c & 1][j4 * 4 + 2]) + cv.z;
+            const float s3 = __uint_as_float(v[c & 1][j4 * 4 + 3]) + cv.w;
+            const int j = jbase + j4 * 4;
+            i1a = (s0 < b1a) ? j : i1a;       b2a = fminf(b2a, fmaxf(b1a, s0)); b1a = fminf(b1a, s0);
+            i1b = (s1 < b1b) ? j + 1 : i1b;   b2b = fminf(b2b, fmaxf(b1b, s1)); b1b = fminf(b1b, s1);
+            i1a = (s2 < b1a) ? j + 2 : i1a;   b2a = fminf(b2a, fmaxf(b1a, s2)); b1a = fminf(b1a, s2);
+            i1b = (s3 < b1b) ? j + 3 : i1b;   b2b = fminf(b2b, fmaxf(b1b, s3)); b1b = fminf(b1b, s3);
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&sm->t_empty[buf]);
+      }
+      const bool a_wins = (b1a < b1b) || (b1a == b1b && i1a < i1b);
+      const float b1 = a_wins ? b1a : b1b;
+      const int i1 = a_wins ? i1a : i1b;
+      const float b2 = fminf(fmaxf(b1a, b1b), fminf(b2a, b2b));  // second smallest over both chains
+      const int nb = it & 1;
+      mbar_wait(&sm->n_full[nb], (it >> 1) & 1);
+      const float xn = sm->xnorm2[nb][row_in_tile];
+      const float tau2 = kappa2 * sqrtf(xn) * cmax;  // 2 * tau for this row
+      const int64_t row = tile * TM + row_in_tile;
+      const bool live = row < n;
+      const bool certain = (b2 - b1) > tau2;  // false for NaN as well
+      if (live) labels[row] = i1;             // provisional for uncertain rows (rewritten by the re-check)
+      // append uncertain rows to the re-check list (one atomic per warp)
+      const unsigned m = __ballot_sync(0xffffffffu, live && !certain);
+      if (m) {
+        int base = 0;
+        if (lane == (__ffs(m) - 1)) base = atomicAdd(&ws->count, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+        if (live && !certain) {
+          const int slot = base + __popc(m & ((1u << lane) - 1));
+          if (slot < cap) amb_idx[slot] = (int32_t)(row & 0x7fffffff);
+        }
+      }
+      if (accumulate) {
+        const int ab = it & 1;
+        mbar_wait(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1);
+        sm->lab[ab][row_in_tile] = (live && certain) ? i1 : -1;
+        sm->score[ab][row_in_tile] = fmaxf(xn + b1, 0.f);  // squared distance to the chosen centre
+        mbar_arrive(&sm->a_full[ab]);
+      }
+    }
+  } else if (warp >= 8 && warp < 12) {
+    // ===================== split: fp32 row -> (x1, x2) bf16 pairs in tensor memory; row norms ==========
+    const int w4 = warp - 8;
+    const int r = w4 * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      float xn = 0.f;
+      for (int a = 0; a < KA; ++a) {
+        uint32_t p1[32], p2[32];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int kc = 2 * a + h;
+          mbar_wait(&sm->xs_full[kc], it & 1);
+          const uint8_t* src = xs + (size_t)kc * CHUNK_BYTES + (size_t)r * 128;
+#pragma unroll
+          for (int p = 0; p < 8; ++p) {
+            const float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
+            xn = fmaf(v.x, v.x, xn); xn = fmaf(v.y, v.y, xn); xn = fmaf(v.z, v.z, xn); xn = fmaf(v.w, v.w, xn);
+            const __nv_bfloat162 h01 = __floats2bfloat162_rn(v.x, v.y);  // .x -> low 16 bits = even k
+            const __nv_bfloat162 h23 = __floats2bfloat162_rn(v.z, v.w);
+            const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
+            const __nv_bfloat162 l01 = __floats2bfloat162_rn(v.x - f01.x, v.y - f01.y);
+            const __nv_bfloat162 l23 = __floats2bfloat162_rn(v.z - f23.x, v.w - f23.y);
+            p1[h * 16 + p * 2 + 0] = *reinterpret_cast<const uint32_t*>(&h01);
+            p1[h * 16 + p * 2 + 1] = *reinterpret_cast<const uint32_t*>(&h23);
+            p2[h * 16 + p * 2 + 0] = *reinterpret_cast<const uint32_t*>(&l01);
+            p2[h * 16 + p * 2 + 1] = *reinterpret_cast<const uint32_t*>(&l23);
+          }
+          mbar_arrive(&sm->xs_empty[kc]);
+        }
+        mbar_wait(&sm->xa_empty[a], (it & 1) ^ 1);  // previous tile's MMAs are done with this TMEM atom
+        tc_fence_after();
+        tmem_st32(tmem_base + lane_addr + TB_A1 + a * 32, p1);
+        tmem_st32(tmem_base + lane_addr + TB_A2 + a * 32, p2);
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(&sm->xa_full[a]);
+      }
+      // the epilogue of tile `it` reads the norm only after the last centre tile: the slot written two
+      // tiles ago has long been consumed (its epilogue precedes the MMAs this split had to wait for)
+      sm->xnorm2[it & 1][r] = xn;
+      mbar_arrive(&sm->n_full[it & 1]);
+    }
+  } else if (warp >= 12) {
+    // ===================== accumulate certain rows =====================
+    const int w4 = warp - 12;
+    double cost = 0.0;
+    unsigned long long nrows = 0;
+    float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
+    uint32_t it = 0;
+    if (accumulate) {
+      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int ab = it & 1;
+        mbar_wait(&sm->a_full[ab], (it >> 1) & 1);
+        const int my_lab = sm->lab[ab][w4 * 32 + lane];
+        const float my_sc = sm->score[ab][w4 * 32 + lane];
+        mbar_arrive(&sm->a_empty[ab]);
+        const int64_t r0 = tile * TM + w4 * 32;
+        for (int g = 0; g < 32; g += 8) {
+          float4 xv[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
+            xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (lbl >= 0 && lane * 4 < d) xv[u] = *reinterpret_cast<const float4*>(X + (r0 + g + u) * ld + lane * 4);
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
+            if (lbl >= 0 && lane * 4 < d) red_add_v4(myrep + (size_t)lbl * d + lane * 4, xv[u]);
+          }
+        }
+        if (my_lab >= 0) {
+          cost += (double)my_sc;
+          atomicAdd(cnt + my_lab, 1ull);
+          ++nrows;
+        }
+      }
+      cost = warp_sum(cost);
+      unsigned long long tot = nrows;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+      if (lane == 0) {
+        atomicAdd(payload + (size_t)k * d + k, cost);
+        atomicAdd(payload + (size_t)k * d + k + 1, (double)tot);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 3) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TB_TMEM_COLS)
+                 : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// re-check plumbing: gather listed rows into a compact matrix, scatter their labels back
+// ---------------------------------------------------------------------------------------------
+__global__ void tcb_gather_kernel(const float* __restrict__ X, int64_t ld, int d, TcbWs* __restrict__ ws,
+                                  const int32_t* __restrict__ amb_idx, float* __restrict__ Xamb, int cap) {
+  const int used = min(ws->count, cap);
+  if (blockIdx.x == 0 && threadIdx.x == 0) ws->used = used;
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int i = warp; i < used; i += nwarps) {
+    const float* src = X + (int64_t)amb_idx[i] * ld;
+    float* dst = Xamb + (int64_t)i * d;
+    for (int c = lane * 4; c < d; c += 128) *reinterpret_cast<float4*>(dst + c) = *reinterpret_cast<const float4*>(src + c);
+  }
+}
+
+__global__ void tcb_scatter_kernel(const TcbWs* __restrict__ ws, const int32_t* __restrict__ amb_idx,
+                                   const int32_t* __restrict__ lab_amb, int32_t* __restrict__ labels) {
+  const int used = ws->used;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < used; i += gridDim.x * blockDim.x)
+    labels[amb_idx[i]] = lab_amb[i];
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+struct TcbWsLayout {
+  size_t off_idx, off_lab, off_x, bytes;
+  int cap;
+};
+static TcbWsLayout tcb_ws_layout(int cap, int d) {
+  TcbWsLayout L;
+  L.cap = cap;
+  size_t o = sizeof(TcbWs);
+  L.off_idx = o; o = b2f_align_up(o + (size_t)cap * 4, 1024);
+  L.off_lab = o; o = b2f_align_up(o + (size_t)cap * 4, 1024);
+  L.off_x = o;   o = b2f_align_up(o + (size_t)cap * d * 4, 1024);
+  L.bytes = o;
+  return L;
+}
+static int tcb_cap_for_rows(int64_t n) {
+  int64_t c = (n / 16 + TM - 1) / TM * TM;  // room for 1 row in 16
+  if (c < 4096) c = 4096;
+  if (c > (1 << 30)) c = 1 << 30;
+  return (int)c;
+}
+static int tcb_cap_from_bytes(size_t bytes, int d) {
+  if (bytes < sizeof(TcbWs) + 4096) return 0;
+  int64_t c = (int64_t)((bytes - sizeof(TcbWs) - 3 * 1024) / (8 + (size_t)d * 4));
+  c = c / TM * TM;
+  if (c > (1 << 30)) c = 1 << 30;
+  while (c > 0 && tcb_ws_layout((int)c, d).bytes > bytes) c -= TM;
+  return (int)c;
+}
+
+static int km_tcb_stages(int d) {
+  const int left = 227 * 1024 - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES;
+  int s = left / TB_STAGE_BYTES;
+  return s > 8 ? 8 : s;
+}
+
+bool km_tcb_supported(int k, int d, int64_t ld) {
+  if (d != 64 && d != 128) return false;  // whole 64-k atoms, X hi/lo pairs fit the tensor memory budget
+  if (k % TN != 0 || k < TN) return false;
+  if (ld % 4 != 0) return false;
+  return km_tcb_stages(d) >= 2 * (d / 64) && km_tc_supported(k, d, ld);
+}
+
+size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
+  (void)k;
+  return tcb_ws_layout(tcb_cap_for_rows(n), d).bytes;
+}
+
+int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
+                void* ws, size_t ws_bytes, bool accumulate, cudaStream_t stream) {
+  B2F_REQUIRE(labels, "b2f_kmeans (bf16x3 path): a labels buffer is required");
+  B2F_REQUIRE(ws, "b2f_kmeans (bf16x3 path): a workspace is required (b2f_kmeans_ws_bytes)");
+  B2F_REQUIRE(n < (1ll << 31), "b2f_kmeans (bf16x3 path): at most 2^31-1 rows per call");
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "b2f_kmeans (bf16x3 path): workspace must be 256-byte aligned");
+  const int cap = tcb_cap_from_bytes(ws_bytes, d);
+  B2F_REQUIRE(cap >= TM, "b2f_kmeans (bf16x3 path): workspace of %zu bytes is too small", ws_bytes);
+  TcbWsLayout W = tcb_ws_layout(cap, d);
+  char* wp = static_cast<char*>(ws);
+  TcbWs* hdr = reinterpret_cast<TcbWs*>(wp);
+  int32_t* amb_idx = reinterpret_cast<int32_t*>(wp + W.off_idx);
+  int32_t* lab_amb = reinterpret_cast<int32_t*>(wp + W.off_lab);
+  float* Xamb = reinterpret_cast<float*>(wp + W.off_x);
+  const int nstages = km_tcb_stages(d);
+  KmPrepLayout P = km_prep_layout(k, d);
+  const char* pp = static_cast<const char*>(prep);
+  const float* cn = reinterpret_cast<const float*>(pp + P.off_cn);
+  const float* cmax = reinterpret_cast<const float*>(pp + P.off_misc);
+  CUtensorMap mx, m1, m2;
+  int rc;
+  if ((rc = make_map_f32(&mx, X, (uint64_t)n, (uint64_t)d, (uint64_t)ld)) != B2F_OK) return rc;
+  if ((rc = make_map_bf16(&m1, pp + P.off_cb1, (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
+  if ((rc = make_map_bf16(&m2, pp + P.off_cb2, (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
+  double* payload = nullptr;
+  float* rep = nullptr;
+  unsigned long long* cnt = nullptr;
+  if (accumulate) {
+    KmAccLayout A = km_acc_layout(k, d);
+    char* ap = static_cast<char*>(acc);
+    payload = reinterpret_cast<double*>(ap + A.off_payload);
+    rep = reinterpret_cast<float*>(ap + A.off_rep);
+    cnt = reinterpret_cast<unsigned long long*>(ap + A.off_cnt);
+  }
+  // 2 * tau = kappa2 * ||x|| * max||c||:  dropped products 3 u^2 (u = 2^-8) on c' = -2c, i.e. 6 * 2^-16,
+  // plus fp32 accumulation / rounding slack (3 d + 16) * 2^-23 on |x||c'| = 2 |x||c|
+  const float kappa = 6.0f * 1.02f / 65536.0f + 2.0f * (3.0f * d + 16.0f) / 8388608.0f;
+  const float kappa2 = 2.0f * kappa;
+  B2F_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcbWs), stream));
+  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * TB_STAGE_BYTES + sizeof(SmemB) + 64;
+  const int64_t ntiles = (n + TM - 1) / TM;
+  int grid = b2f_sm_count();
+  if ((int64_t)grid > ntiles) grid = (int)ntiles;
+  B2F_CUDA(cudaFuncSetAttribute(km_tcb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  km_tcb_kernel<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, cn, cmax, kappa2, k, nstages, payload, rep,
+                                                    cnt, labels, accumulate ? 1 : 0, hdr, amb_idx, cap);
+  B2F_LAUNCH_CHECK();
+  tcb_gather_kernel<<<b2f_sm_count() * 4, 256, 0, stream>>>(X, ld, d, hdr, amb_idx, Xamb, cap);
+  B2F_LAUNCH_CHECK();
+  rc = km_tc_step(Xamb, (int64_t)cap, d, (int64_t)d, prep, k, acc, lab_amb, 3, accumulate, &hdr->used, stream);
+  if (rc != B2F_OK) return rc;
+  tcb_scatter_kernel<<<b2f_sm_count() * 2, 256, 0, stream>>>(hdr, amb_idx, lab_amb, labels);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}

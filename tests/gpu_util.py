@@ -33,14 +33,24 @@ def kmeans_state(C, k, d):
     return cen, prep, acc
 
 
-def kmeans_step_raw(X, n, d, ld, C, algo, w=None, want_labels=True):
-    """One b2f_kmeans_step + fold.  Returns labels, sums[k,d], counts[k], cost, nrows (host)."""
+def kmeans_step_raw(X, n, d, ld, C, algo, w=None, want_labels=True, ws_bytes=None, info=None):
+    """One b2f_kmeans_step (or _step_ws for B2F_KM_TCB) + fold.
+    Returns labels, sums[k,d], counts[k], cost, nrows (host)."""
     L = N.lib()
     k = C.shape[0]
     cen, prep, acc = kmeans_state(C, k, d)
     labels = torch.full((n,), -1, dtype=torch.int32, device=dev()) if want_labels else None
-    N.check(L.b2f_kmeans_step(N.ptr(X), n, d, ld, N.ptr(w), N.ptr(prep), k, N.ptr(acc), N.ptr(labels), algo,
-                              stream()), "step")
+    if algo == N.KM_TCB:
+        wsb = int(L.b2f_kmeans_ws_bytes(n, k, d)) if ws_bytes is None else ws_bytes
+        ws = torch.zeros(wsb, dtype=torch.uint8, device=dev())
+        N.check(L.b2f_kmeans_step_ws(N.ptr(X), n, d, ld, N.ptr(w), N.ptr(prep), k, N.ptr(acc), N.ptr(labels),
+                                     N.ptr(ws), wsb, algo, stream()), "step_ws")
+        if info is not None:
+            hdr = ws[:8].view(torch.int32).cpu().numpy()
+            info["uncertain"], info["rechecked"] = int(hdr[0]), int(hdr[1])
+    else:
+        N.check(L.b2f_kmeans_step(N.ptr(X), n, d, ld, N.ptr(w), N.ptr(prep), k, N.ptr(acc), N.ptr(labels), algo,
+                                  stream()), "step")
     N.check(L.b2f_kmeans_fold(N.ptr(acc), k, d, stream()), "fold")
     plen = int(L.b2f_kmeans_payload_len(k, d))
     p = acc[: plen * 8].view(torch.float64).cpu().numpy()

@@ -109,3 +109,72 @@ def test_tc_rejects_unsupported_shapes():
         G.kmeans_step_raw(X, 100, 48, ld, np.zeros((128, 48)), N.KM_TC3)
     with pytest.raises(N.B200FitError):
         G.kmeans_step_raw(X[:, :32].contiguous(), 100, 32, 32, np.zeros((100, 32)), N.KM_TC3)
+
+
+TCB_SHAPES = [(128, 64, 128), (1000, 64, 128), (5000, 128, 256), (4099, 128, 1024), (20000, 128, 128),
+              (30000, 64, 256)]
+
+
+@pytest.mark.parametrize("n,d,k", TCB_SHAPES)
+def test_tcb_step_matches_oracle(n, d, k):
+    """bf16x3 filter pass + 3xTF32 re-check of uncertain rows: same bar as the 3xTF32 kernel."""
+    N, G = _imports()
+    Xh = synth.mixture(n, 0, d, SEED, k, 2.0)
+    rng = np.random.default_rng(n + d + k)
+    C = Xh[rng.choice(n, size=k, replace=False)].astype(np.float64) if n >= k else \
+        synth.mixture_centers(d, SEED, k, 2.0).astype(np.float64)
+    X, _, ld = G.upload_matrix(Xh)
+    info = {}
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCB, info=info)
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
+    bad = (labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)
+    assert not bad.any(), "%d label mismatches outside the 1e-6 gap band" % bad.sum()
+    _, rcost, rsums, rcounts = oracle.kmeans_step(Xh.astype(np.float64), C)
+    assert nrows == n and counts.sum() == n
+    assert info["rechecked"] == info["uncertain"] <= n
+    if (labels == ref_lab).all():
+        np.testing.assert_array_equal(counts, rcounts)
+        scale = np.abs(Xh).astype(np.float64).sum(axis=0).max() / k + 1.0
+        np.testing.assert_allclose(sums, rsums, rtol=1e-5, atol=1e-6 * scale)
+    assert cost == pytest.approx(rcost, rel=1e-5, abs=1e-3 * n)
+
+
+def test_tcb_uncertain_rows_are_rechecked_and_overflow_is_visible():
+    """Two centres almost on top of each other make most of their rows uncertain."""
+    N, G = _imports()
+    n, d, k = 20000, 128, 128
+    Xh = synth.mixture(n, 0, d, SEED, 4, 2.0)
+    C = synth.mixture_centers(d, SEED, k, 2.0).astype(np.float64)
+    C[5] = C[0] + 1e-3  # near-duplicate of component 0's centre
+    X, _, ld = G.upload_matrix(Xh)
+    info = {}
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCB, info=info)
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
+    assert info["uncertain"] > n // 8 and nrows == n
+    assert not ((labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)).any()
+    # a workspace with room for 128 rows only: the excess is dropped and the row count shows it
+    small = 256 + 3 * 1024 + 128 * (8 + 4 * d) + 4096
+    info2 = {}
+    _, _, _, _, nrows2 = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCB, ws_bytes=small, info=info2)
+    assert info2["uncertain"] == info["uncertain"] and info2["rechecked"] < info2["uncertain"]
+    assert nrows2 == n - (info2["uncertain"] - info2["rechecked"])
+
+
+def test_tcb_fit_per_iteration_parity_and_fallback():
+    N, G = _imports()
+    from b200fit.clustering import CudaLloydEngine, lloyd
+    from b200fit.dist import Comm
+    from b200fit.feature import pack_columns
+
+    n, d, k, iters = 60000, 128, 1024, 5
+    Xh = synth.mixture(n, 0, d, SEED, k, 2.0)
+    C0 = Xh[np.random.default_rng(2).choice(n, size=k, replace=False)].astype(np.float64)
+    ref = oracle.kmeans_lloyd(Xh.astype(np.float64), C0, max_iter=iters, tol=0.0)
+    eng = CudaLloydEngine(pack_columns([Xh]), k, algo=N.KM_TCB)
+    eng.set_centers(C0)
+    it, costs, conv, payload = lloyd(eng, Comm(), iters, 0.0)
+    sc = np.abs(ref["centers"]).max()
+    np.testing.assert_allclose(eng.get_centers(), ref["centers"], rtol=1e-5, atol=1e-5 * sc)
+    np.testing.assert_allclose(costs, ref["cost_hist"], rtol=1e-5)
+    np.testing.assert_array_equal(eng.get_counts(payload), ref["counts_hist"][-1])
+    assert eng.fallbacks == 0

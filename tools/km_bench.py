@@ -28,6 +28,8 @@ prep = torch.empty(L.b2f_kmeans_prep_bytes(a.k, a.d), dtype=torch.uint8, device=
 acc = torch.empty(L.b2f_kmeans_acc_bytes(a.k, a.d), dtype=torch.uint8, device=dev)
 N.check(L.b2f_kmeans_prepare(N.ptr(C), a.k, a.d, N.ptr(prep), N.stream_ptr()), "prep")
 lab = torch.empty(a.n, dtype=torch.int32, device=dev)
+wsb = int(L.b2f_kmeans_ws_bytes(a.n, a.k, a.d))
+ws = torch.zeros(wsb, dtype=torch.uint8, device=dev)
 ts = []
 for i in range(a.reps + 2):
     N.check(L.b2f_kmeans_acc_zero(N.ptr(acc), a.k, a.d, N.stream_ptr()), "zero")
@@ -36,6 +38,9 @@ for i in range(a.reps + 2):
     if a.predict:
         N.check(L.b2f_kmeans_predict(N.ptr(X), a.n, a.d, a.d, N.ptr(prep), a.k, N.ptr(lab), None, a.algo,
                                      N.stream_ptr()), "predict")
+    elif a.algo == 4:
+        N.check(L.b2f_kmeans_step_ws(N.ptr(X), a.n, a.d, a.d, None, N.ptr(prep), a.k, N.ptr(acc), N.ptr(lab),
+                                     N.ptr(ws), wsb, a.algo, N.stream_ptr()), "step_ws")
     else:
         N.check(L.b2f_kmeans_step(N.ptr(X), a.n, a.d, a.d, None, N.ptr(prep), a.k, N.ptr(acc), None, a.algo,
                                   N.stream_ptr()), "step")
@@ -45,5 +50,7 @@ for i in range(a.reps + 2):
         ts.append(e0.elapsed_time(e1))
 ms = sum(ts) / len(ts)
 fl = 2.0 * a.n * a.k * a.d
+if a.algo == 4:
+    print("uncertain rows: %s of %d" % (ws[:8].view(torch.int32).cpu().tolist(), a.n))
 print("algo %d n=%d d=%d k=%d: %.3f ms  %.1f TFLOP/s algorithmic  (%.1f ms per 100M rows)" %
       (a.algo, a.n, a.d, a.k, ms, fl / ms / 1e9, ms * 1e8 / a.n))
