@@ -192,18 +192,7 @@ def b200_arm(args):
     eng.set_centers(C0)
 
     def iteration(ev=None):
-        if ev:
-            s = N.stream_ptr()
-            N.check(L.b2f_kmeans_acc_zero(N.ptr(eng.acc), k, d, s), "acc_zero")
-            ev[0].record()
-            N.check(L.b2f_kmeans_step(N.ptr(Xt), n, d, d, None, N.ptr(eng.prep), k, N.ptr(eng.acc), None, args.algo, s),
-                    "step")
-            ev[1].record()
-            N.check(L.b2f_kmeans_fold(N.ptr(eng.acc), k, d, s), "fold")
-            eng.launches += 2
-            payload = eng.payload
-        else:
-            payload = eng.step()
+        payload = eng.step(events=ev)
         comm.all_reduce_sum(payload)
         eng.finalize_async(payload, 0.0)
 
@@ -224,19 +213,25 @@ def b200_arm(args):
     kern_ms = sum(a.elapsed_time(b) for a, b in kev) / args.steps
     launches = eng.launches - launches0
     cost_after = float(eng.status_f64.cpu()[1].item())
+    rows_after = eng.rows_counted(eng.payload)
+    uncertain = int(eng.ws[:4].view(torch.int32).item()) if eng.use_ws else 0
+    algo_name = "bf16x3 filter + 3xTF32 re-check (B2F_KM_TCB)" if eng.use_ws else "algo %d" % args.algo
     value = 1e3 / ms_step
     flops = 2.0 * n * k * d
     achieved = flops / (kern_ms * 1e-3) / 1e12
     line = {"metric": "kmeans_lloyd_iter_per_s", "value": value, "unit": "iter/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "tf32x3->f32 (sums/cost folded in f64)",
+            "scaling": "strong", "vs_baseline": None,
+            "dtype": "bf16x3 filter + tf32x3 re-check -> f32 (sums/cost folded in f64)" if eng.use_ws else
+                     "tf32x3->f32 (sums/cost folded in f64)",
             "data": "synthetic", "config": workload_config(n_total, world), "gpu_launches": launches,
             "clocks": clk.summary(),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["tensor"], "unit": "TFLOP/s",
-                         "frac": achieved / pk["tensor"], "traffic": None, "kernel": "b2f_kmeans_step",
+                         "frac": achieved / pk["tensor"], "traffic": None, "kernel": "b2f_kmeans_step_ws: " + algo_name,
                          "kernel_ms": kern_ms, "peak_source": pk["src"] + " bf16 sustained (no TF32 figure measured)",
                          "algorithmic_flops_per_launch": flops},
-            "check": {"cost_after_last_timed_iter": cost_after}}
+            "check": {"cost_after_last_timed_iter": cost_after, "rows_accumulated_last_iter_this_rank": rows_after,
+                      "rows_this_rank": n, "uncertain_rows_last_iter_this_rank": uncertain}}
     if args.rows:
         line["reduced"] = True
 

@@ -66,12 +66,14 @@ class CudaLloydEngine:
                 "b2f_kmeans_prepare")
         self.launches += 1
 
-    def step(self, labels=None, exact=False):
+    def step(self, labels=None, exact=False, events=None):
         """Zero accumulators, assign + accumulate this shard, fold -> fp64 payload (device).
         exact=True forces the 3xTF32 kernel (used when the re-check list of the bf16x3 pass overflowed)."""
         s = N.stream_ptr()
         X = self.X
         N.check(self.L.b2f_kmeans_acc_zero(N.ptr(self.acc), self.k, self.d, s), "b2f_kmeans_acc_zero")
+        if events:
+            events[0].record()
         if self.use_ws and not exact:
             lab = labels if labels is not None else self.labels_buf
             N.check(self.L.b2f_kmeans_step_ws(N.ptr(X.data), X.n, X.d, X.ld, None, N.ptr(self.prep), self.k,
@@ -83,6 +85,8 @@ class CudaLloydEngine:
             N.check(self.L.b2f_kmeans_step(N.ptr(X.data), X.n, X.d, X.ld, N.ptr(self.w), N.ptr(self.prep), self.k,
                                            N.ptr(self.acc), N.ptr(labels), algo, s), "b2f_kmeans_step")
             self.launches += 1
+        if events:
+            events[1].record()
         N.check(self.L.b2f_kmeans_fold(N.ptr(self.acc), self.k, self.d, s), "b2f_kmeans_fold")
         self.launches += 1
         return self.payload

@@ -112,10 +112,26 @@ __device__ __forceinline__ float4 ldg_stream(const float4* p) {
 }
 #endif
 
+// Optional certainty test of the 3xTF32 kernel: rows whose best / second-best scores are within
+// kappa2 * ||x|| * max||c|| are not accumulated but appended (as ORIGINAL row indices, through src_idx when
+// the kernel runs on a gathered matrix) to idx[0..cap) for the exact fp64 kernel.  count == NULL: off.
+struct KmRecheck {
+  int* count;
+  int32_t* idx;
+  int cap;
+  const int32_t* src_idx;
+  float kappa2;
+  const float* cmax;
+};
+
+// implemented in kmeans_generic.cu: exact (fp64, direct form) assignment + accumulation of listed rows
+int km_exact_rows(const float* X, int64_t ld, int d, const void* prep, int k, void* acc, int32_t* labels,
+                  const int* count, const int32_t* idx, int cap, bool accumulate, cudaStream_t stream);
+
 // implemented in kmeans_tc.cu
 // n_dev (optional, device): the kernel processes min(n, *n_dev) rows (row count known only on the device)
 int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
-               int passes, bool accumulate, const int* n_dev, cudaStream_t stream);
+               int passes, bool accumulate, const int* n_dev, const KmRecheck* recheck, cudaStream_t stream);
 bool km_tc_supported(int k, int d, int64_t ld);
 
 // implemented in kmeans_tcb.cu (bf16x3 filter pass + 3xTF32 re-check of ambiguous rows)

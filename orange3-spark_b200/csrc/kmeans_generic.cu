@@ -207,6 +207,95 @@ static int km_generic_launch(const float* X, int64_t n, int d, int64_t ld, const
 }
 
 // ---------------------------------------------------------------------------------------------
+// exact re-check: one CTA per listed row, every centre, fp64 direct form sum (x - c)^2 on the fp64 master
+// centres, ascending centre order with strict '<' (findClosest tie rule); accumulates straight into the
+// fp64 payload.  Only rows that the tensor-core kernels could not certify come here (a few per million).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) km_exact_kernel(const float* __restrict__ X, int64_t ld, int d,
+                                                       const double* __restrict__ C64, int k,
+                                                       double* __restrict__ payload, int32_t* __restrict__ labels,
+                                                       const int* __restrict__ count, const int32_t* __restrict__ idx,
+                                                       int cap, int accumulate) {
+  // one CTA per listed row: warp w scans centres w, w+8, ... (4 in flight), lanes stride the columns
+  __shared__ double s_best[8];
+  __shared__ int s_bi[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int used = min(*count, cap);
+  double cost = 0.0, rows = 0.0;
+  for (int i = blockIdx.x; i < used; i += gridDim.x) {
+    const int64_t r = idx[i];
+    const float* xr = X + r * ld;
+    double best = INFINITY;
+    int bi = 0x7fffffff;
+    for (int j0 = warp; j0 < k; j0 += 32) {  // centres j0, j0+8, j0+16, j0+24
+      double s[4] = {0.0, 0.0, 0.0, 0.0};
+      for (int t = lane; t < d; t += 32) {
+        const double xv = (double)xr[t];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int j = j0 + 8 * u;
+          if (j < k) {
+            const double df = xv - C64[(size_t)j * d + t];
+            s[u] = fma(df, df, s[u]);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = j0 + 8 * u;
+        const double v = warp_sum(s[u]);
+        if (j < k && (v < best || (v == best && j < bi))) {
+          best = v;
+          bi = j;
+        }
+      }
+    }
+    if (lane == 0) {
+      s_best[warp] = best;
+      s_bi[warp] = bi;
+    }
+    __syncthreads();
+    best = s_best[0];
+    bi = s_bi[0];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) {  // lowest index wins exact ties (findClosest order)
+      const double v = s_best[w];
+      const int j = s_bi[w];
+      if (v < best || (v == best && j < bi)) {
+        best = v;
+        bi = j;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && labels) labels[r] = bi;
+    if (accumulate) {
+      for (int t = threadIdx.x; t < d; t += 256) atomicAdd(payload + (size_t)bi * d + t, (double)xr[t]);
+      if (threadIdx.x == 0) {
+        atomicAdd(payload + (size_t)k * d + bi, 1.0);
+        cost += best;
+        rows += 1.0;
+      }
+    }
+  }
+  if (accumulate && threadIdx.x == 0 && rows > 0.0) {
+    atomicAdd(payload + (size_t)k * d + k, cost);
+    atomicAdd(payload + (size_t)k * d + k + 1, rows);
+  }
+}
+
+int km_exact_rows(const float* X, int64_t ld, int d, const void* prep, int k, void* acc, int32_t* labels,
+                  const int* count, const int32_t* idx, int cap, bool accumulate, cudaStream_t stream) {
+  KmPrepLayout P = km_prep_layout(k, d);
+  const double* c64 = reinterpret_cast<const double*>(static_cast<const char*>(prep) + P.off_c64);
+  double* payload = nullptr;
+  if (accumulate) payload = reinterpret_cast<double*>(static_cast<char*>(acc) + km_acc_layout(k, d).off_payload);
+  km_exact_kernel<<<b2f_sm_count() * 8, 256, 0, stream>>>(X, ld, d, c64, k, payload, labels, count, idx, cap,
+                                                          accumulate ? 1 : 0);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // fold / finalize
 // ---------------------------------------------------------------------------------------------
 __global__ void km_fold_kernel(double* __restrict__ payload, float* __restrict__ rep,
@@ -308,7 +397,7 @@ extern "C" int b2f_kmeans_step(const float* X, int64_t n, int d, int64_t ld, con
   if (algo == B2F_KM_TC3 || algo == B2F_KM_TC1) {
     B2F_REQUIRE(!w, "b2f_kmeans_step: the tensor-core path does not take row weights");
     B2F_REQUIRE(km_tc_supported(k, d, ld), "b2f_kmeans_step: tensor-core path needs d %% 32 == 0, d <= 256, k %% 128 == 0");
-    return km_tc_step(X, n, d, ld, prep, k, acc, labels, algo == B2F_KM_TC3 ? 3 : 1, true, nullptr, b2f_cs(stream));
+    return km_tc_step(X, n, d, ld, prep, k, acc, labels, algo == B2F_KM_TC3 ? 3 : 1, true, nullptr, nullptr, b2f_cs(stream));
   }
   B2F_REQUIRE(algo == B2F_KM_GENERIC, "b2f_kmeans_step: unknown algo %d", algo);
   return km_generic_launch(X, n, d, ld, w, reinterpret_cast<const float*>(pp + P.off_c32), k,
@@ -369,7 +458,7 @@ extern "C" int b2f_kmeans_predict(const float* X, int64_t n, int d, int64_t ld, 
   if (dist2) algo = B2F_KM_GENERIC;  // exact distances come from the direct-form kernel
   if (algo == B2F_KM_TC3 || algo == B2F_KM_TC1) {
     B2F_REQUIRE(km_tc_supported(k, d, ld), "b2f_kmeans_predict: tensor-core path needs d %% 32 == 0, d <= 256, k %% 128 == 0");
-    return km_tc_step(X, n, d, ld, prep, k, nullptr, labels, algo == B2F_KM_TC3 ? 3 : 1, false, nullptr, b2f_cs(stream));
+    return km_tc_step(X, n, d, ld, prep, k, nullptr, labels, algo == B2F_KM_TC3 ? 3 : 1, false, nullptr, nullptr, b2f_cs(stream));
   }
   return km_generic_launch(X, n, d, ld, nullptr, reinterpret_cast<const float*>(pp + P.off_c32), k, nullptr, nullptr,
                            labels, dist2, false, b2f_cs(stream));

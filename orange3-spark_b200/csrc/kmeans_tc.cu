@@ -33,9 +33,11 @@ struct Smem {
   uint64_t b_full[8], b_empty[8];
   uint64_t t_full[2], t_empty[2];
   uint64_t a_full[2], a_empty[2];  // epilogue -> accumulate hand-off (labels / scores of one row tile)
+  uint64_t n_full[2];              // split -> epilogue: squared row norms (only used by the certainty test)
   uint32_t tmem_base;
-  int lab[2][TM];
+  int lab[2][TM];                  // label, or -1 for a row handed to the exact re-check
   float score[2][TM];
+  float xnorm2[2][TM];
 };
 
 }  // namespace
@@ -46,7 +48,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
                  const __grid_constant__ CUtensorMap map_cl, const float* __restrict__ X, int64_t n, int d, int64_t ld,
                  const float* __restrict__ cn, int k, int nstages, double* __restrict__ payload,
                  float* __restrict__ rep, unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels,
-                 int accumulate, int dbg, const int* __restrict__ n_dev) {
+                 int accumulate, int dbg, const int* __restrict__ n_dev, KmRecheck rck) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];  // 128B swizzle atoms need 1024-byte alignment
   uint8_t* base = smem_raw;
   if (smem_u32(base) & 1023u) __trap();
@@ -77,6 +79,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       mbar_init(&sm->t_empty[b], EPI_THREADS);
       mbar_init(&sm->a_full[b], EPI_THREADS);
       mbar_init(&sm->a_empty[b], EPI_THREADS);
+      mbar_init(&sm->n_full[b], EPI_THREADS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -229,10 +232,30 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       const int i1 = a_wins ? i1a : i1b;
       const int64_t row = tile * TM + row_in_tile;
       if (labels && row < n) labels[row] = i1;
+      bool certain = true;
+      if (rck.count) {
+        // certainty test of the 3xTF32 scores: rows whose two best scores are within 2 tau go to the exact
+        // (fp64) kernel instead of being accumulated here
+        const float b2 = fminf(fmaxf(b1a, b1b), fminf(b2a, b2b));
+        mbar_wait(&sm->n_full[it & 1], (it >> 1) & 1);
+        const float tau2 = rck.kappa2 * sqrtf(sm->xnorm2[it & 1][row_in_tile]) * (*rck.cmax);
+        certain = (b2 - b1) > tau2;
+        const bool list_it = row < n && !certain;
+        const unsigned m = __ballot_sync(0xffffffffu, list_it);
+        if (m) {
+          int base = 0;
+          if (lane == (__ffs(m) - 1)) base = atomicAdd(rck.count, __popc(m));
+          base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+          if (list_it) {
+            const int slot = base + __popc(m & ((1u << lane) - 1));
+            if (slot < rck.cap) rck.idx[slot] = rck.src_idx ? rck.src_idx[row] : (int32_t)row;
+          }
+        }
+      }
       if (accumulate) {
         const int ab = it & 1;
         mbar_wait(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1);
-        sm->lab[ab][row_in_tile] = i1;
+        sm->lab[ab][row_in_tile] = certain ? i1 : -1;
         sm->score[ab][row_in_tile] = b1;
         mbar_arrive(&sm->a_full[ab]);  // release semantics order the two stores before the arrive
       }
@@ -247,6 +270,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       // hi / lo, and store them as the A operand in tensor memory (lane = row, column = k).
       const int r = w4 * 32 + lane;
       const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
+      float xn = 0.f;
       for (int kc = 0; kc < KC; ++kc) {
         mbar_wait(&sm->xs_full[kc], it & 1);
         const uint8_t* src = xs + (size_t)kc * CHUNK_BYTES + (size_t)r * 128;
@@ -254,6 +278,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 #pragma unroll
         for (int p = 0; p < 8; ++p) {
           const float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
+          xn = fmaf(v.x, v.x, xn); xn = fmaf(v.y, v.y, xn); xn = fmaf(v.z, v.z, xn); xn = fmaf(v.w, v.w, xn);
           const float h0 = to_tf32(v.x), h1 = to_tf32(v.y), h2 = to_tf32(v.z), h3 = to_tf32(v.w);
           hi[p * 4 + 0] = __float_as_uint(h0); hi[p * 4 + 1] = __float_as_uint(h1);
           hi[p * 4 + 2] = __float_as_uint(h2); hi[p * 4 + 3] = __float_as_uint(h3);
@@ -271,6 +296,8 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         tc_fence_before();
         mbar_arrive(&sm->xa_full[kc]);
       }
+      sm->xnorm2[it & 1][r] = xn;  // read by the epilogue's certainty test after this tile's last centre tile
+      mbar_arrive(&sm->n_full[it & 1]);
     }
   } else if (warp >= 12) {
     // ===================== accumulate finished row tiles (own warps: never delays the split) ==========
@@ -304,7 +331,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
             const int64_t rr = r0 + g + u;
             const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
             const float sc = __shfl_sync(0xffffffffu, my_sc, g + u);
-            if (rr < n) {  // warp-uniform
+            if (rr < n && lbl >= 0) {  // warp-uniform
               float xn = 0.f;
               if (lane * 4 < d) {
                 xn = fmaf(xv[u].x, xv[u].x, xn); xn = fmaf(xv[u].y, xv[u].y, xn);
@@ -367,7 +394,7 @@ bool km_tc_supported(int k, int d, int64_t ld) {
 }
 
 int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
-               int passes, bool accumulate, const int* n_dev, cudaStream_t stream) {
+               int passes, bool accumulate, const int* n_dev, const KmRecheck* recheck, cudaStream_t stream) {
   B2F_REQUIRE(passes == 1 || passes == 3, "km_tc_step: passes must be 1 or 3");
   B2F_REQUIRE(n < (1ll << 31) * (int64_t)TM, "km_tc_step: too many rows for one launch");
   const int nstages = km_tc_stages(d, passes);
@@ -399,15 +426,17 @@ int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, i
   int grid = b2f_sm_count();
   if (const char* g = getenv("B2F_TC_GRID")) grid = atoi(g) > 0 ? atoi(g) : grid;  // dev knob
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
+  KmRecheck rck = {};
+  if (recheck) rck = *recheck;
   const int dbg = getenv("B2F_TC_DBG") ? atoi(getenv("B2F_TC_DBG")) : 0;  // dev knob, results invalid when set
   if (passes == 3) {
     B2F_CUDA(cudaFuncSetAttribute(km_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     km_tc_kernel<3><<<grid, NTHREADS, smem, stream>>>(mx, mh, ml, X, n, d, ld, cn, k, nstages, payload, rep, cnt,
-                                                      labels, accumulate ? 1 : 0, dbg, n_dev);
+                                                      labels, accumulate ? 1 : 0, dbg, n_dev, rck);
   } else {
     B2F_CUDA(cudaFuncSetAttribute(km_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     km_tc_kernel<1><<<grid, NTHREADS, smem, stream>>>(mx, mh, ml, X, n, d, ld, cn, k, nstages, payload, rep, cnt,
-                                                      labels, accumulate ? 1 : 0, dbg, n_dev);
+                                                      labels, accumulate ? 1 : 0, dbg, n_dev, rck);
   }
   B2F_LAUNCH_CHECK();
   return B2F_OK;

@@ -13,14 +13,15 @@
 // Replaces MLlib's findClosest + axpy loop behind KMeans.fit;
 //   reference call site: orangecontrib/spark/base/spark_ml_estimator.py:22.
 //
-// CTA = 512 threads, persistent, one per SM:
+// CTA = 640 threads, persistent, one per SM:
 //   warp 0  X producer (TMA, fp32 staging chunks of 128 rows x 32 floats)
 //   warp 1  MMA issuer (one batch of 12*KA tcgen05.mma per centre tile, A operand from tensor memory)
 //   warp 2  B producer (TMA, stage = 128 centres x 64 k of c1 and of c2, bf16, 128B swizzle)
 //   warp 3  TMEM allocator
-//   warps 4-7   epilogue: tcgen05.ld, + ||c||^2, running best / second best, certainty test
-//   warps 8-11  split: fp32 row -> x1, x2 bf16 pairs -> tcgen05.st into tensor memory; row norms
-//   warps 12-15 accumulate certain rows (16-byte vector reductions), cost, counts
+//   warps 4-11  epilogue (two warps per TMEM lane quarter, 64 columns each): tcgen05.ld, + ||c||^2,
+//               running best / second best, certainty test
+//   warps 12-15 split: fp32 row -> x1, x2 bf16 pairs -> tcgen05.st into tensor memory; row norms
+//   warps 16-19 accumulate certain rows (16-byte vector reductions), cost, counts
 #include <cuda_bf16.h>
 
 #include "tc_common.cuh"
@@ -29,7 +30,8 @@ namespace {
 
 constexpr uint32_t TB_TMEM_COLS = 512;  // [0,256) two accumulators | [256,320) x1 | [320,384) x2 (bf16 pairs)
 constexpr uint32_t TB_A1 = 256, TB_A2 = 320;
-constexpr int TB_THREADS = 512;
+constexpr int TB_THREADS = 640;
+constexpr int TB_EPI_THREADS = 256;  // two epilogue warps per TMEM lane quarter, 64 columns of a tile each
 constexpr int TB_STAGE_BYTES = 2 * CHUNK_BYTES;  // c1 atom + c2 atom (128 centres x 64 bf16 each)
 // kind::f16, bf16 inputs, fp32 accumulate, A and B K-major, M = 128, N = TN
 constexpr uint32_t IDESC_BF16 =
@@ -46,12 +48,15 @@ struct SmemB {
   int lab[2][TM];                    // certain label, or -1 for a row sent to the re-check list
   float score[2][TM];
   float xnorm2[2][TM];
+  float p_b1[2][TM], p_b2[2][TM];    // partial results of the second epilogue warp of each quarter
+  int p_i1[2][TM];
 };
 
 struct TcbWs {  // header of the caller-provided workspace
   int count;    // rows appended to the re-check list (may exceed cap: the excess is dropped)
   int used;     // min(count, cap), written by the gather kernel
-  int pad[62];
+  int count2;   // rows the 3xTF32 re-check could not certify either -> exact fp64 kernel
+  int pad[61];
 };
 
 __device__ __forceinline__ void tc_mma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t accumulate) {
@@ -93,7 +98,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_init(&sm->xa_full[c], EPI_THREADS);
       mbar_init(&sm->xa_empty[c], 1);
       mbar_init(&sm->t_full[c], 1);
-      mbar_init(&sm->t_empty[c], EPI_THREADS);
+      mbar_init(&sm->t_empty[c], TB_EPI_THREADS);
       mbar_init(&sm->a_full[c], EPI_THREADS);
       mbar_init(&sm->a_empty[c], EPI_THREADS);
       mbar_init(&sm->n_full[c], EPI_THREADS);
@@ -195,9 +200,12 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         __syncwarp();
       }
     }
-  } else if (warp >= 4 && warp < 8) {
+  } else if (warp >= 4 && warp < 12) {
     // ===================== epilogue: best / second best per row, certainty test =====================
+    // Two warps share a TMEM lane quarter; warp `half` scans columns [64*half, 64*half + 64) of every
+    // accumulator tile (two resident warps per scheduler hide the min/max dependency latency).
     const int q = warp & 3;
+    const int half = (warp - 4) >> 2;
     const int row_in_tile = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const float cmax = *cmax_ptr;
@@ -209,15 +217,15 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         const int buf = acc_it & 1;
         mbar_wait(&sm->t_full[buf], (acc_it >> 1) & 1);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + lane_addr + (uint32_t)(buf * TN);
+        const uint32_t taddr = tmem_base + lane_addr + (uint32_t)(buf * TN + half * 64);
         uint32_t v[2][32];
         tmem_ld32(taddr, v[0]);
 #pragma unroll
-        for (int c = 0; c < TN / 32; ++c) {
+        for (int c = 0; c < 2; ++c) {
           tmem_ld_wait();
-          if (c + 1 < TN / 32) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
-          const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + c * 32);
-          const int jbase = nt * TN + c * 32;
+          if (c + 1 < 2) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+          const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + half * 64 + c * 32);
+          const int jbase = nt * TN + half * 64 + c * 32;
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
             const float4 cv = __ldg(cn4 + j4);
@@ -235,11 +243,28 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         tc_fence_before();
         mbar_arrive(&sm->t_empty[buf]);
       }
-      const bool a_wins = (b1a < b1b) || (b1a == b1b && i1a < i1b);
-      const float b1 = a_wins ? b1a : b1b;
-      const int i1 = a_wins ? i1a : i1b;
-      const float b2 = fminf(fmaxf(b1a, b1b), fminf(b2a, b2b));  // second smallest over both chains
+      // merge this thread's two chains: smaller score wins, equal scores keep the lower centre index
+      bool a_wins = (b1a < b1b) || (b1a == b1b && i1a < i1b);
+      float b1 = a_wins ? b1a : b1b;
+      int i1 = a_wins ? i1a : i1b;
+      float b2 = fminf(fmaxf(b1a, b1b), fminf(b2a, b2b));  // second smallest over both chains
+      // merge the two column halves (the upper-half warp hands its partial result over in smem)
       const int nb = it & 1;
+      if (half == 1) {
+        sm->p_b1[nb][row_in_tile] = b1;
+        sm->p_b2[nb][row_in_tile] = b2;
+        sm->p_i1[nb][row_in_tile] = i1;
+      }
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+      if (half == 1) continue;
+      {
+        const float ob1 = sm->p_b1[nb][row_in_tile], ob2 = sm->p_b2[nb][row_in_tile];
+        const int oi1 = sm->p_i1[nb][row_in_tile];
+        const bool mine = (b1 < ob1) || (b1 == ob1 && i1 < oi1);
+        b2 = fminf(fmaxf(b1, ob1), fminf(b2, ob2));
+        i1 = mine ? i1 : oi1;
+        b1 = mine ? b1 : ob1;
+      }
       mbar_wait(&sm->n_full[nb], (it >> 1) & 1);
       const float xn = sm->xnorm2[nb][row_in_tile];
       const float tau2 = kappa2 * sqrtf(xn) * cmax;  // 2 * tau for this row
@@ -266,9 +291,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         mbar_arrive(&sm->a_full[ab]);
       }
     }
-  } else if (warp >= 8 && warp < 12) {
+  } else if (warp >= 12 && warp < 16) {
     // ===================== split: fp32 row -> (x1, x2) bf16 pairs in tensor memory; row norms ==========
-    const int w4 = warp - 8;
+    const int w4 = warp - 12;
     const int r = w4 * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
     uint32_t it = 0;
@@ -310,9 +335,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       sm->xnorm2[it & 1][r] = xn;
       mbar_arrive(&sm->n_full[it & 1]);
     }
-  } else if (warp >= 12) {
+  } else if (warp >= 16) {
     // ===================== accumulate certain rows =====================
-    const int w4 = warp - 12;
+    const int w4 = warp - 16;
     double cost = 0.0;
     unsigned long long nrows = 0;
     float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
@@ -390,7 +415,7 @@ __global__ void tcb_scatter_kernel(const TcbWs* __restrict__ ws, const int32_t* 
 // host side
 // ---------------------------------------------------------------------------------------------
 struct TcbWsLayout {
-  size_t off_idx, off_lab, off_x, bytes;
+  size_t off_idx, off_lab, off_idx2, off_x, bytes;
   int cap;
 };
 static TcbWsLayout tcb_ws_layout(int cap, int d) {
@@ -399,6 +424,7 @@ static TcbWsLayout tcb_ws_layout(int cap, int d) {
   size_t o = sizeof(TcbWs);
   L.off_idx = o; o = b2f_align_up(o + (size_t)cap * 4, 1024);
   L.off_lab = o; o = b2f_align_up(o + (size_t)cap * 4, 1024);
+  L.off_idx2 = o; o = b2f_align_up(o + (size_t)cap * 4, 1024);
   L.off_x = o;   o = b2f_align_up(o + (size_t)cap * d * 4, 1024);
   L.bytes = o;
   return L;
@@ -411,7 +437,7 @@ static int tcb_cap_for_rows(int64_t n) {
 }
 static int tcb_cap_from_bytes(size_t bytes, int d) {
   if (bytes < sizeof(TcbWs) + 4096) return 0;
-  int64_t c = (int64_t)((bytes - sizeof(TcbWs) - 3 * 1024) / (8 + (size_t)d * 4));
+  int64_t c = (int64_t)((bytes - sizeof(TcbWs) - 4 * 1024) / (12 + (size_t)d * 4));
   c = c / TM * TM;
   if (c > (1 << 30)) c = 1 << 30;
   while (c > 0 && tcb_ws_layout((int)c, d).bytes > bytes) c -= TM;
@@ -449,6 +475,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   TcbWs* hdr = reinterpret_cast<TcbWs*>(wp);
   int32_t* amb_idx = reinterpret_cast<int32_t*>(wp + W.off_idx);
   int32_t* lab_amb = reinterpret_cast<int32_t*>(wp + W.off_lab);
+  int32_t* idx2 = reinterpret_cast<int32_t*>(wp + W.off_idx2);
   float* Xamb = reinterpret_cast<float*>(wp + W.off_x);
   const int nstages = km_tcb_stages(d);
   KmPrepLayout P = km_prep_layout(k, d);
@@ -474,6 +501,8 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   // plus fp32 accumulation / rounding slack (3 d + 16) * 2^-23 on |x||c'| = 2 |x||c|
   const float kappa = 6.0f * 1.02f / 65536.0f + 2.0f * (3.0f * d + 16.0f) / 8388608.0f;
   const float kappa2 = 2.0f * kappa;
+  const int dbg = getenv("B2F_TC_DBG") ? atoi(getenv("B2F_TC_DBG")) : 0;  // dev knob, results invalid when set
+  const bool acc_main = accumulate && !(dbg & 4);
   B2F_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcbWs), stream));
   const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * TB_STAGE_BYTES + sizeof(SmemB) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
@@ -481,13 +510,22 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
   B2F_CUDA(cudaFuncSetAttribute(km_tcb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   km_tcb_kernel<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, cn, cmax, kappa2, k, nstages, payload, rep,
-                                                    cnt, labels, accumulate ? 1 : 0, hdr, amb_idx, cap);
+                                                    cnt, labels, acc_main ? 1 : 0, hdr, amb_idx, cap);
   B2F_LAUNCH_CHECK();
   tcb_gather_kernel<<<b2f_sm_count() * 4, 256, 0, stream>>>(X, ld, d, hdr, amb_idx, Xamb, cap);
   B2F_LAUNCH_CHECK();
-  rc = km_tc_step(Xamb, (int64_t)cap, d, (int64_t)d, prep, k, acc, lab_amb, 3, accumulate, &hdr->used, stream);
+  // 3xTF32 bound: dropped products 3 u^2 with u = 2^-11 on c' = -2c, plus 48 fp32 accumulation roundings
+  KmRecheck rck;
+  rck.count = &hdr->count2;
+  rck.idx = idx2;
+  rck.cap = cap;
+  rck.src_idx = amb_idx;
+  rck.kappa2 = 2.0f * (6.0f * 1.02f / 4194304.0f + 2.0f * (3.0f * d / 8.0f + 16.0f) / 16777216.0f);
+  rck.cmax = cmax;
+  rc = km_tc_step(Xamb, (int64_t)cap, d, (int64_t)d, prep, k, acc, lab_amb, 3, accumulate, &hdr->used, &rck, stream);
   if (rc != B2F_OK) return rc;
   tcb_scatter_kernel<<<b2f_sm_count() * 2, 256, 0, stream>>>(hdr, amb_idx, lab_amb, labels);
   B2F_LAUNCH_CHECK();
-  return B2F_OK;
+  // rows still uncertain after 3xTF32: exact fp64 assignment + accumulation (writes labels after the scatter)
+  return km_exact_rows(X, ld, d, prep, k, acc, labels, &hdr->count2, idx2, cap, accumulate, stream);
 }

@@ -78,6 +78,55 @@ __global__ void __launch_bounds__(LR_THREADS, (NCH >= 8) ? 1 : 2)
       yy[i] = live ? __ldg(y + r) : 0.f;
       ww[i] = live ? (w ? __ldg(w + r) : 1.f) : 0.f;
     }
+    if constexpr (LR_BATCH == 4) {
+      // per-lane partial margins of the 4 rows (hi and lo parts of beta; the lo part only has to remove the
+      // SYSTEMATIC error of rounding beta to fp32, so adding it per lane is enough)
+      float pm[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float mh = 0.f, ml = 0.f;
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+          mh = fmaf(x[i][ch].x, bh[ch].x, mh); mh = fmaf(x[i][ch].y, bh[ch].y, mh);
+          mh = fmaf(x[i][ch].z, bh[ch].z, mh); mh = fmaf(x[i][ch].w, bh[ch].w, mh);
+          ml = fmaf(x[i][ch].x, bl[ch].x, ml); ml = fmaf(x[i][ch].y, bl[ch].y, ml);
+          ml = fmaf(x[i][ch].z, bl[ch].z, ml); ml = fmaf(x[i][ch].w, bl[ch].w, ml);
+        }
+        pm[i] = mh + ml;
+      }
+      // transposed warp reduction: 6 shuffles leave every 8-lane group with the full margin of ONE row
+      // (row = 2 * bit4 + bit3 of the lane id), so sigmoid / softplus run once for all four rows
+      const bool up16 = lane & 16, up8 = lane & 8;
+      float k0 = (up16 ? pm[2] : pm[0]) + __shfl_xor_sync(0xffffffffu, up16 ? pm[0] : pm[2], 16);
+      float k1 = (up16 ? pm[3] : pm[1]) + __shfl_xor_sync(0xffffffffu, up16 ? pm[1] : pm[3], 16);
+      float v = (up8 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, up8 ? k0 : k1, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 4);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      const int myrow = (up16 ? 2 : 0) + (up8 ? 1 : 0);
+      const float yi = myrow == 0 ? yy[0] : myrow == 1 ? yy[1] : myrow == 2 ? yy[2] : yy[3];
+      const float wi = myrow == 0 ? ww[0] : myrow == 1 ? ww[1] : myrow == 2 ? ww[2] : ww[3];
+      const float m = (v + b0l) + b0h;
+      const float e = __expf(-fabsf(m));               // one exponential serves sigmoid and softplus
+      const float inv = __fdividef(1.f, 1.f + e);
+      const float p = m >= 0.f ? inv : e * inv;
+      const float softplus = fmaxf(m, 0.f) + log1pf(e);
+      const float mymult = wi * (p - yi);
+      if ((lane & 7) == 0) {
+        loss += (double)(wi * (softplus - yi * m));
+        smult += (double)mymult;
+        sw += (double)wi;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float mult = __shfl_sync(0xffffffffu, mymult, i * 8);
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+          g[ch].x = fmaf(mult, x[i][ch].x, g[ch].x); g[ch].y = fmaf(mult, x[i][ch].y, g[ch].y);
+          g[ch].z = fmaf(mult, x[i][ch].z, g[ch].z); g[ch].w = fmaf(mult, x[i][ch].w, g[ch].w);
+        }
+      }
+    } else {
 #pragma unroll
     for (int i = 0; i < LR_BATCH; ++i) {
       float mh = 0.f, ml = 0.f;
@@ -88,17 +137,22 @@ __global__ void __launch_bounds__(LR_THREADS, (NCH >= 8) ? 1 : 2)
         ml = fmaf(x[i][ch].x, bl[ch].x, ml); ml = fmaf(x[i][ch].y, bl[ch].y, ml);
         ml = fmaf(x[i][ch].z, bl[ch].z, ml); ml = fmaf(x[i][ch].w, bl[ch].w, ml);
       }
-      const float m = warp_sum(mh) + (warp_sum(ml) + b0l) + b0h;
-      const float p = 1.f / (1.f + expf(-m));
+      const float m = (warp_sum(mh + ml) + b0l) + b0h;
+      const float e = __expf(-fabsf(m));
+      const float inv = __fdividef(1.f, 1.f + e);
+      const float p = m >= 0.f ? inv : e * inv;
       const float mult = ww[i] * (p - yy[i]);
-      loss += (double)(ww[i] * (log1pexp_f(m) - yy[i] * m));
-      smult += (double)mult;
-      sw += (double)ww[i];
+      if (lane == 0) {
+        loss += (double)(ww[i] * (fmaxf(m, 0.f) + log1pf(e) - yy[i] * m));
+        smult += (double)mult;
+        sw += (double)ww[i];
+      }
 #pragma unroll
       for (int ch = 0; ch < NCH; ++ch) {
         g[ch].x = fmaf(mult, x[i][ch].x, g[ch].x); g[ch].y = fmaf(mult, x[i][ch].y, g[ch].y);
         g[ch].z = fmaf(mult, x[i][ch].z, g[ch].z); g[ch].w = fmaf(mult, x[i][ch].w, g[ch].w);
       }
+    }
     }
     if (++since_flush == LR_FLUSH) {
       since_flush = 0;
@@ -116,6 +170,9 @@ __global__ void __launch_bounds__(LR_THREADS, (NCH >= 8) ? 1 : 2)
     p[0] += (double)g[ch].x; p[1] += (double)g[ch].y; p[2] += (double)g[ch].z; p[3] += (double)g[ch].w;
   }
   __shared__ double red[3][LR_WARPS];
+  loss = warp_sum(loss);
+  smult = warp_sum(smult);
+  sw = warp_sum(sw);
   if (lane == 0) {
     red[0][warp] = loss;
     red[1][warp] = smult;

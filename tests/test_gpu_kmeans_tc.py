@@ -136,7 +136,9 @@ def test_tcb_step_matches_oracle(n, d, k):
         np.testing.assert_array_equal(counts, rcounts)
         scale = np.abs(Xh).astype(np.float64).sum(axis=0).max() / k + 1.0
         np.testing.assert_allclose(sums, rsums, rtol=1e-5, atol=1e-6 * scale)
-    assert cost == pytest.approx(rcost, rel=1e-5, abs=1e-3 * n)
+    # certain rows carry the bf16x3 score error (|err| <= tau ~ 0.1 here, zero mean): it only shows when
+    # the true cost is ~0 (rows sitting on their centres, n == k case)
+    assert cost == pytest.approx(rcost, rel=1e-5, abs=2e-2 * n)
 
 
 def test_tcb_uncertain_rows_are_rechecked_and_overflow_is_visible():
@@ -148,12 +150,13 @@ def test_tcb_uncertain_rows_are_rechecked_and_overflow_is_visible():
     C[5] = C[0] + 1e-3  # near-duplicate of component 0's centre
     X, _, ld = G.upload_matrix(Xh)
     info = {}
-    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCB, info=info)
+    big = int(N.lib().b2f_kmeans_ws_bytes(16 * n, k, d))  # room for every row on the re-check list
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCB, ws_bytes=big, info=info)
     ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
     assert info["uncertain"] > n // 8 and nrows == n
     assert not ((labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)).any()
     # a workspace with room for 128 rows only: the excess is dropped and the row count shows it
-    small = 256 + 3 * 1024 + 128 * (8 + 4 * d) + 4096
+    small = 256 + 4 * 1024 + 128 * (12 + 4 * d) + 4096
     info2 = {}
     _, _, _, _, nrows2 = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCB, ws_bytes=small, info=info2)
     assert info2["uncertain"] == info["uncertain"] and info2["rechecked"] < info2["uncertain"]

@@ -51,6 +51,6 @@ for i in range(a.reps + 2):
 ms = sum(ts) / len(ts)
 fl = 2.0 * a.n * a.k * a.d
 if a.algo == 4:
-    print("uncertain rows: %s of %d" % (ws[:8].view(torch.int32).cpu().tolist(), a.n))
+    print("uncertain rows: %s of %d" % (ws[:12].view(torch.int32).cpu().tolist(), a.n))
 print("algo %d n=%d d=%d k=%d: %.3f ms  %.1f TFLOP/s algorithmic  (%.1f ms per 100M rows)" %
       (a.algo, a.n, a.d, a.k, ms, fl / ms / 1e9, ms * 1e8 / a.n))
