@@ -25,6 +25,7 @@ for _p in (ROOT, os.path.join(ROOT, "orange3-spark_b200")):
 SEED = 20240611
 KM = dict(n=100_000_000, d=128, k=1024, comps=1024, center_scale=2.0)
 LR = dict(n=50_000_000, d=256)
+LRM = dict(n=20_000_000, d=512, K=20)
 
 
 def parse():
@@ -35,6 +36,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=0, help="DEV ONLY: override the row count (marks the line reduced)")
     ap.add_argument("--lr-rows", type=int, default=0, help="DEV ONLY: override the LR row count")
+    ap.add_argument("--lrm-rows", type=int, default=0, help="DEV ONLY: override the multinomial LR row count")
     ap.add_argument("--algo", type=int, default=0, help="B2F_KM_* code (0 = auto)")
     ap.add_argument("--no-e2e", action="store_true", help="DEV ONLY: skip the host-buffer end-to-end leg")
     ap.add_argument("--no-lr", action="store_true", help="DEV ONLY: skip the LR leg")
@@ -246,6 +248,9 @@ def b200_arm(args):
     if not args.no_lr:
         line["lr"] = lr_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, DeviceMatrix, shard_bounds,
                             max_over_ranks, sync_all)
+    if not args.no_lr:
+        line["lr_multinomial"] = lrm_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, DeviceMatrix,
+                                         shard_bounds, max_over_ranks, sync_all)
     if rank == 0 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(n_total)
     if rank == 0:
@@ -337,6 +342,53 @@ def lr_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, Devi
                          "traffic": None, "kernel": "lr_binary_kernel", "algorithmic_bytes_per_launch": bytes_pass,
                          "peak_source": pk["src"]},
             "check": {"loss": float(p[d + 1] / p[d + 2]), "weight_sum": float(p[d + 2])}}
+
+
+def lrm_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, DeviceMatrix, shard_bounds,
+            max_over_ranks, sync_all):
+    """BASELINE configs[3]: multinomial LR (20 classes) loss+gradient pass on 20M x 512."""
+    import numpy as np
+
+    n_total = args.lrm_rows or (LRM["n"] if not args.rows else max(args.rows // 4, 1))
+    d, K = LRM["d"], LRM["K"]
+    lo, hi = shard_bounds(n_total, rank, world)
+    n = hi - lo
+    rng = np.random.default_rng(SEED + 2)
+    scale = np.exp(rng.uniform(np.log(0.5), np.log(2.0), size=d)).astype(np.float32)
+    w_true = (rng.standard_normal((K, d)) / np.sqrt(d)).astype(np.float32)
+    Xt = torch.empty((n, d), dtype=torch.float32, device=dev)
+    y = torch.empty(n, dtype=torch.float32, device=dev)
+    N.check(L.b2f_synth_logistic(N.ptr(Xt), N.ptr(y), n, lo, d, d, SEED + 2, N.ptr(torch.from_numpy(scale).to(dev)),
+                                 N.ptr(torch.from_numpy(w_true).to(dev)),
+                                 N.ptr(torch.zeros(K, dtype=torch.float32, device=dev)), K, N.stream_ptr()),
+            "b2f_synth_logistic")
+    eng = CudaLogRegEngine(DeviceMatrix(Xt, d, lo), y, None, K)
+    eng.beta.copy_(torch.from_numpy((rng.standard_normal((K, d)) * 0.05 / scale[None, :]).ravel()).to(dev))
+
+    def one_pass():
+        comm.all_reduce_sum(eng.lossgrad_device())
+
+    for _ in range(args.warmup):
+        one_pass()
+    sync_all()
+    steps = max(args.steps, 5)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(steps):
+        one_pass()
+    t1.record()
+    sync_all()
+    ms = max_over_ranks(t0.elapsed_time(t1)) / steps
+    p = eng.out.cpu().numpy()
+    bytes_pass = n * (4.0 * d + 4.0)
+    gbs = bytes_pass / (ms * 1e-3) / 1e9
+    return {"metric": "lr_multinomial_lossgrad_pass_per_s", "value": 1e3 / ms, "unit": "pass/s", "ms_per_step": ms,
+            "config": {"workload": "multinomial LogisticRegression (20 classes) loss+gradient pass on synthetic "
+                                   "%dx512 fp32 (BASELINE configs[3])" % n_total, "rows": n_total, "d": d, "K": K},
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
+                         "traffic": None, "kernel": "lr_multinomial_kernel (CUDA-core)",
+                         "algorithmic_bytes_per_launch": bytes_pass, "peak_source": pk["src"]},
+            "check": {"loss": float(p[K * d + K] / p[K * d + K + 1]), "weight_sum": float(p[K * d + K + 1])}}
 
 
 def cpu_baseline(n_total):

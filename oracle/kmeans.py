@@ -41,7 +41,7 @@ def find_closest_scalar(x, xn, C, Cn):
     return bi, best
 
 
-def kmeans_assign(X, C, Xn=None, chunk=65536, return_second=False):
+def kmeans_assign(X, C, Xn=None, chunk=16384, return_second=False):
     """Vectorised findClosest over all rows (result-equivalent to the scalar loop:
     the lower-bound skip can never change an argmin).  Returns labels (int32) and
     squared distances (fp64); optionally the second-best distance per row (used by
@@ -53,18 +53,31 @@ def kmeans_assign(X, C, Xn=None, chunk=65536, return_second=False):
     labels = np.empty(n, dtype=np.int32)
     dist = np.empty(n, dtype=np.float64)
     second = np.empty(n, dtype=np.float64) if return_second else None
+    Cn2 = Cn * Cn
+    order = np.argsort(Cn, kind="stable")
+    Cn_sorted = Cn[order]
+    cn_max = Cn.max() if len(Cn) else 0.0
     for a in range(0, n, chunk):
         b = min(n, a + chunk)
         Xc = X[a:b]
         xn = np.sqrt((Xc * Xc).sum(axis=1)) if Xn is None else Xn[a:b]
-        s = xn[:, None] ** 2 + Cn[None, :] ** 2
-        D = s - 2.0 * (Xc @ C.T)
-        nd = xn[:, None] - Cn[None, :]
-        bound = 2.0 * EPS * s / (nd * nd + EPS)
-        bad = np.argwhere(bound >= 1e-6)
-        for i, j in bad:  # rare: norms equal to ~1e-5 relative -> exact form
-            diff = Xc[i] - C[j]
-            D[i, j] = diff @ diff
+        D = Xc @ C.T
+        D *= -2.0
+        D += Cn2[None, :]
+        D += (xn * xn)[:, None]
+        # fastSquaredDistance switches to the exact form when bound = 2 EPS s / (nd^2 + EPS) >= 1e-6, i.e. when
+        # the two norms agree to ~2e-5 relative.  Find those (rare) pairs through the sorted centre norms
+        # instead of forming the full bound matrix, then apply the literal test to them.
+        thr = 2.2e-5 * (xn + cn_max) + 1e-300
+        lo = np.searchsorted(Cn_sorted, xn - thr, side="left")
+        hi = np.searchsorted(Cn_sorted, xn + thr, side="right")
+        for i in np.nonzero(hi > lo)[0]:
+            for j in order[lo[i]:hi[i]]:
+                s_ = xn[i] * xn[i] + Cn2[j]
+                nd = xn[i] - Cn[j]
+                if 2.0 * EPS * s_ / (nd * nd + EPS) >= 1e-6:
+                    diff = Xc[i] - C[j]
+                    D[i, j] = diff @ diff
         lab = np.argmin(D, axis=1)  # first minimum == lowest index on ties
         labels[a:b] = lab
         dist[a:b] = D[np.arange(b - a), lab]
@@ -79,15 +92,24 @@ def kmeans_assign(X, C, Xn=None, chunk=65536, return_second=False):
     return labels, dist
 
 
-def kmeans_step(X, C, w=None, chunk=65536):
+def kmeans_step(X, C, w=None, chunk=16384):
     """One Lloyd assignment+accumulate pass: labels, cost, sums[k,d], counts[k]."""
     X = np.asarray(X, dtype=np.float64)
     k, d = C.shape
     labels, dist = kmeans_assign(X, C, chunk=chunk)
     ww = np.ones(X.shape[0]) if w is None else np.asarray(w, dtype=np.float64)
     cost = float((np.maximum(dist, 0.0) * ww).sum())
-    sums = np.zeros((k, d))
-    np.add.at(sums, labels, X * ww[:, None])
+    # sums[j] = sum of w_i x_i over rows with label j: a one-hot (k x n) sparse product, the same
+    # block formulation Spark >= 3.4 hands to BLAS (far faster than np.add.at, identical result)
+    n = X.shape[0]
+    try:
+        from scipy import sparse
+
+        onehot = sparse.csr_matrix((ww, (labels, np.arange(n))), shape=(k, n))
+        sums = np.asarray(onehot @ X)
+    except ImportError:  # pragma: no cover
+        sums = np.zeros((k, d))
+        np.add.at(sums, labels, X * ww[:, None])
     counts = np.bincount(labels, weights=ww, minlength=k).astype(np.float64)
     return labels, cost, sums, counts
 
@@ -108,7 +130,7 @@ def kmeans_update(C, sums, counts, tol):
     return newC, converged
 
 
-def kmeans_lloyd(X, C0, max_iter=20, tol=1e-4, w=None, chunk=65536):
+def kmeans_lloyd(X, C0, max_iter=20, tol=1e-4, w=None, chunk=16384):
     """A.2 iteration loop with a fixed initial model.  Returns a dict with
     per-iteration centres (after each update), costs (cost of each assignment
     step, i.e. measured before that iteration's update), counts, numIter and

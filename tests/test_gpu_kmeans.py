@@ -236,3 +236,32 @@ def test_kmeans_init_modes_give_a_sane_clustering(mode):
             assert m.summary.trainingCost == pytest.approx(float(opt.sum()), rel=0.01)
     if mode == "k-means||":
         assert found_all >= 3
+
+
+def test_standard_scaler_then_kmeans_pipeline_cfg5_shape():
+    """BASELINE config 5 at reduced N: VectorAssembler -> StandardScaler(withStd) -> KMeans(k=256, d=64)
+    with a fixed initialModel in scaled space, against the oracle's scaler + Lloyd."""
+    N, G = _imports()
+    import b200fit
+    from b200fit.frame import ColumnarFrame
+
+    n, d, k = 40000, 64, 256
+    rng = np.random.default_rng(55)
+    col_scale = np.exp(rng.uniform(np.log(0.1), np.log(10.0), size=d)).astype(np.float32)
+    Xh = synth.mixture(n, 0, d, SEED, k, 2.0, col_scale)
+    df = ColumnarFrame({"c%d" % j: Xh[:, j] for j in range(d)})
+    df = b200fit.feature.VectorAssembler(inputCols=["c%d" % j for j in range(d)], outputCol="raw").transform(df)
+    sm = b200fit.feature.StandardScaler(inputCol="raw", outputCol="features").fit(df)
+    rmean, rstd = oracle.standard_scaler_fit(Xh.astype(np.float64))
+    np.testing.assert_allclose(sm.std, rstd, rtol=1e-9)
+    np.testing.assert_allclose(sm.mean, rmean, rtol=1e-9, atol=1e-9)
+    scaled = sm.transform(df)
+    Xs = oracle.standard_scaler_transform(Xh.astype(np.float64), rmean, rstd)
+    np.testing.assert_allclose(scaled.col("features").numpy(), Xs, rtol=2e-7, atol=1e-7)
+    C0 = Xs[rng.choice(n, size=k, replace=False)]
+    ref = oracle.kmeans_lloyd(scaled.col("features").numpy().astype(np.float64), C0, max_iter=6, tol=0.0)
+    m = b200fit.clustering.KMeans(k=k, maxIter=6, tol=0.0, initialModel=C0).fit(scaled)
+    sc = np.abs(ref["centers"]).max()
+    np.testing.assert_allclose(np.array(m.clusterCenters()), ref["centers"], rtol=1e-5, atol=1e-5 * sc)
+    np.testing.assert_allclose(m.summary.costHistory, ref["cost_hist"], rtol=1e-5)
+    assert m.summary.clusterSizes == [int(c) for c in ref["counts_hist"][-1]]
