@@ -139,3 +139,9 @@ bool km_tcb_supported(int k, int d, int64_t ld);
 size_t km_tcb_ws_bytes(int64_t n, int k, int d);
 int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
                 void* ws, size_t ws_bytes, bool accumulate, cudaStream_t stream);
+
+// implemented in lr_tc.cu (tcgen05 multinomial loss + gradient)
+bool lr_mn_tc_supported(int d, int64_t ld, int K);
+size_t lr_mn_tc_extra_scratch(int d);
+int lr_mn_tc_launch(const float* X, const float* y, const float* w, int64_t n, int d, int K, const double* beta,
+                    const double* icpt, double* partials, int grid, void* wbuf, cudaStream_t st);

@@ -4,6 +4,8 @@
 //   orangecontrib/spark/widgets/ml/spark_ml_classification.py:15); semantics: SURVEY.md A.3.
 // Standardisation never touches X: the caller passes beta = coef / sigma and rescales the raw
 // gradient sum by 1 / sigma afterwards.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 #define LR_THREADS 256
@@ -470,7 +472,9 @@ extern "C" size_t b2f_lr_scratch_bytes(int d, int n_classes) {
   const int K = (n_classes == 2) ? 1 : n_classes;
   const size_t len = (size_t)K * d + K + 2;
   const size_t parts = (size_t)((K == 1) ? lr_grid_binary() : lr_grid_multi());
-  return b2f_align_up(parts * len * sizeof(double), 256);
+  size_t bytes = b2f_align_up(parts * len * sizeof(double), 1024);
+  if (K > 1) bytes += lr_mn_tc_extra_scratch(d);  // W' as TF32 hi / lo for the tensor-core kernel
+  return bytes;
 }
 
 template <int NCH>
@@ -536,6 +540,17 @@ extern "C" int b2f_lr_multinomial_lossgrad(const float* X, const float* y, const
               "b2f_lr_multinomial_lossgrad: unsupported shape K=%d d=%d (need ceil(K/8)*8 * ceil(d/256) <= 64)", K, d);
   const int grid = lr_grid_multi();
   double* partials = static_cast<double*>(scratch);
+  if (lr_mn_tc_supported(d, ld, K) && !getenv("B2F_LR_NO_TC")) {
+    const size_t plen_ = (size_t)K * d + K + 2;
+    void* wbuf = static_cast<char*>(scratch) + b2f_align_up((size_t)grid * plen_ * sizeof(double), 1024);
+    int rc_ = lr_mn_tc_launch(X, y, w, n, d, K, beta, icpt, partials, grid, wbuf, st);
+    if (rc_ != B2F_OK) return rc_;
+    lr_fold_kernel<<<((int)plen_ + 127) / 128, 128, 0, st>>>(partials, grid, (int)plen_, out);
+    B2F_LAUNCH_CHECK();
+    return B2F_OK;
+  }
+  const int kp0 = (K + 7) / 8 * 8;
+  (void)kp0;
   int rc = B2F_EUNSUPPORTED;
 #define MN_CASE(KPV, NJV)                                                                            \
   if (kp == KPV && (nj == NJV || (NJV == 4 && nj == 3)))                                             \

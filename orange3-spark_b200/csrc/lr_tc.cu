@@ -1,0 +1,459 @@
+// K4 on the tensor cores: fused multinomial (softmax) LogisticRegression loss + gradient pass
+// (sm_100a only).  Per 128-row tile, with K classes padded to N = 32:
+//   GEMM1  margins[128 x 32]  = X_tile[128 x d] . W'^T            tcgen05 kind::tf32, 3xTF32 split,
+//                                                                 A (x_hi / x_lo) from tensor memory
+//   softmax / loss / (P - Y) per row (thread == row), written to shared memory as bf16 pairs
+//   GEMM2  G^T[d x 32]       += X_tile^T[d x 128] . (P - Y)[128 x 32]   tcgen05 kind::f16, bf16x3,
+//                                                                 A = X^T read MN-major from smem
+// X is streamed from HBM once (GEMM1) and re-read from L2 for GEMM2; G^T stays in tensor memory for the
+// CTA's lifetime.  Replaces the treeAggregate of MultinomialLogisticBlockAggregator;
+//   reference call site: orangecontrib/spark/base/spark_ml_estimator.py:22 with module = classification
+//   (orangecontrib/spark/widgets/ml/spark_ml_classification.py:15).
+//
+// CTA = 512 threads, persistent, one per SM:
+//   warp 0  X producer (TMA chunks of 128 rows x 32 floats): GEMM1 chunks of tile t+1, then GEMM2 chunks of t
+//   warp 1  MMA issuer (software pipelined: GEMM1(t+1) is issued before GEMM2(t))
+//   warp 2  W producer (TMA, [32 classes x 32 k] of W_hi and W_lo per chunk)
+//   warp 3  TMEM allocator
+//   warps 4-7   softmax epilogue (thread == row)
+//   warps 8-15  split: fp32 chunk -> tf32 hi/lo into tensor memory (GEMM1) or bf16 x1/x2 into the MN-major
+//               shared-memory operand tile (GEMM2); two threads per row, 16 columns each
+#include <cuda_bf16.h>
+
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr int LT_THREADS = 512;
+constexpr int LT_SPLIT_THREADS = 256;
+constexpr int LT_NP = 32;          // classes padded to the MMA N
+constexpr int LT_XS = 4;           // X staging slots (16 KB each)
+constexpr int LT_WS = 4;           // W stages (hi + lo, 8 KB each)
+constexpr int LT_WSTAGE = 2 * LT_NP * 128;
+// tensor memory columns
+constexpr uint32_t LT_TMEM_COLS = 512;
+constexpr uint32_t LT_D1 = 0;      // margins, 2 buffers x 32 columns
+constexpr uint32_t LT_A1 = 64;     // GEMM1 operand ring: 4 slots x (32 hi + 32 lo) columns
+constexpr uint32_t LT_G = 320;     // G^T: d/128 blocks x 32 columns (features on lanes)
+// GEMM1: kind::tf32, A (TMEM) and B K-major, M = 128, N = 32
+constexpr uint32_t IDESC_G1 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(LT_NP >> 3) << 17) | (8u << 24);
+// GEMM2: kind::f16 bf16, A MN-major (bit 15), B K-major, M = 128, N = 32
+constexpr uint32_t IDESC_G2 = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | ((uint32_t)(LT_NP >> 3) << 17) | (8u << 24);
+
+struct SmemL {
+  uint64_t xs_full[LT_XS], xs_empty[LT_XS];
+  uint64_t w_full[LT_WS], w_empty[LT_WS];
+  uint64_t a1_full[4], a1_empty[4];
+  uint64_t d1_full[2], d1_empty[2];
+  uint64_t py_full[2], py_empty[2];
+  uint64_t a2_full, a2_empty;
+  uint64_t g_done;
+  uint32_t tmem_base;
+  float icpt[LT_NP];
+  double red[4][LT_NP + 2];
+};
+
+__device__ __forceinline__ void mma_tf32_ts(uint32_t d, uint32_t a, uint64_t b, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
+      "r"(a), "l"(b), "r"(IDESC_G1), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void mma_bf16_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+      "l"(a), "l"(b), "r"(IDESC_G2), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+      "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+}  // namespace
+
+__global__ void __launch_bounds__(LT_THREADS, 1)
+    lr_mn_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_wh,
+                    const __grid_constant__ CUtensorMap map_wl, const float* __restrict__ y,
+                    const float* __restrict__ w, int64_t n, int d, int K, const double* __restrict__ icpt,
+                    double* __restrict__ partials) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  if (smem_u32(smem_raw) & 1023u) __trap();
+  const int KC = d / 32;   // GEMM1 chunks per tile
+  const int FB = d / 128;  // GEMM2 feature blocks per tile
+  uint8_t* xs = smem_raw;                                  // LT_XS x 16 KB   fp32 staging
+  uint8_t* wst = xs + LT_XS * CHUNK_BYTES;                 // LT_WS x 8 KB    W_hi | W_lo chunk
+  uint8_t* a2 = wst + LT_WS * LT_WSTAGE;                   // 64 KB           x1 (2 atoms) | x2 (2 atoms), MN-major
+  uint8_t* py = a2 + 4 * CHUNK_BYTES;                      // 2 x 16 KB       p1 (2 atoms of 4 KB) | p2
+  SmemL* sm = reinterpret_cast<SmemL*>(py + 2 * 16384);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t ntiles = (n + TM - 1) / TM;
+  // tiles of this CTA: blockIdx.x, + gridDim.x, ...
+  const int my_tiles = (int)((ntiles > blockIdx.x) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0);
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < LT_XS; ++i) {
+      mbar_init(&sm->xs_full[i], 1);
+      mbar_init(&sm->xs_empty[i], LT_SPLIT_THREADS);
+    }
+    for (int i = 0; i < LT_WS; ++i) {
+      mbar_init(&sm->w_full[i], 1);
+      mbar_init(&sm->w_empty[i], 1);
+    }
+    for (int i = 0; i < 4; ++i) {
+      mbar_init(&sm->a1_full[i], LT_SPLIT_THREADS);
+      mbar_init(&sm->a1_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&sm->d1_full[i], 1);
+      mbar_init(&sm->d1_empty[i], EPI_THREADS);
+      mbar_init(&sm->py_full[i], EPI_THREADS);
+      mbar_init(&sm->py_empty[i], 1);
+    }
+    mbar_init(&sm->a2_full, LT_SPLIT_THREADS);
+    mbar_init(&sm->a2_empty, 1);
+    mbar_init(&sm->g_done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (threadIdx.x < LT_NP) sm->icpt[threadIdx.x] = (threadIdx.x < K) ? (float)icpt[threadIdx.x] : 0.f;
+  if (warp == 3) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm->tmem_base)),
+                 "r"(LT_TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = sm->tmem_base;
+
+  // Work order shared by the producer, the split warps and the MMA issuer:
+  //   G1(0), then for t = 0 .. my_tiles-1:  G1(t+1) (if any), G2(t)
+  if (warp == 0) {
+    // ===================== X producer =====================
+    if (lane == 0) {
+      uint32_t g = 0;  // running chunk counter -> staging slot g % LT_XS
+      auto load_chunk = [&](int64_t tile, int col0) {
+        const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
+        mbar_wait(&sm->xs_empty[slot], ph ^ 1);
+        mbar_expect_tx(&sm->xs_full[slot], (uint32_t)CHUNK_BYTES);
+        tma_load_2d(xs + (size_t)slot * CHUNK_BYTES, &map_x, col0, (int)(tile * TM), &sm->xs_full[slot]);
+        ++g;
+      };
+      for (int t = -1; t < my_tiles; ++t) {
+        if (t + 1 < my_tiles) {
+          const int64_t tile = blockIdx.x + (int64_t)(t + 1) * gridDim.x;
+          for (int c = 0; c < KC; ++c) load_chunk(tile, c * 32);
+        }
+        if (t >= 0) {
+          const int64_t tile = blockIdx.x + (int64_t)t * gridDim.x;
+          for (int c = 0; c < KC; ++c) load_chunk(tile, c * 32);
+        }
+      }
+    }
+  } else if (warp == 2) {
+    // ===================== W producer (GEMM1 chunks only) =====================
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int t = 0; t < my_tiles; ++t) {
+        for (int c = 0; c < KC; ++c, ++g) {
+          const uint32_t slot = g % LT_WS, ph = (g / LT_WS) & 1;
+          mbar_wait(&sm->w_empty[slot], ph ^ 1);
+          mbar_expect_tx(&sm->w_full[slot], (uint32_t)LT_WSTAGE);
+          uint8_t* dst = wst + (size_t)slot * LT_WSTAGE;
+          tma_load_2d(dst, &map_wh, c * 32, 0, &sm->w_full[slot]);
+          tma_load_2d(dst + LT_NP * 128, &map_wl, c * 32, 0, &sm->w_full[slot]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint64_t kdesc = (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);  // K-major, SW128, SBO 1024
+    // MN-major, SW128: LBO = 16 KB between 64-feature atoms, SBO = 1 KB between 8-row groups
+    const uint64_t mndesc = ((uint64_t)(CHUNK_BYTES >> 4) << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+    const uint32_t w_a = smem_u32(wst) >> 4, a2_a = smem_u32(a2) >> 4, py_a = smem_u32(py) >> 4;
+    uint32_t g1 = 0;  // GEMM1 chunk counter (operand ring slot g1 % 4, W stage g1 % LT_WS)
+    uint32_t g2 = 0;  // GEMM2 block counter (a2 phase)
+    auto gemm1 = [&](int t) {
+      const uint32_t buf = t & 1;
+      mbar_wait(&sm->d1_empty[buf], ((t >> 1) & 1) ^ 1);
+      const uint32_t dd = tmem_base + LT_D1 + buf * LT_NP;
+      for (int c = 0; c < KC; ++c, ++g1) {
+        const uint32_t slot = g1 & 3, ph = (g1 >> 2) & 1;
+        const uint32_t ws = g1 % LT_WS, wph = (g1 / LT_WS) & 1;
+        mbar_wait(&sm->a1_full[slot], ph);
+        mbar_wait(&sm->w_full[ws], wph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t ah = tmem_base + LT_A1 + slot * 64, al = ah + 32;
+          const uint64_t bh = kdesc | (uint64_t)(w_a + ws * (LT_WSTAGE >> 4));
+          const uint64_t bl = bh + ((LT_NP * 128) >> 4);
+#pragma unroll
+          for (int s = 0; s < 4; ++s) {
+            mma_tf32_ts(dd, ah + 8 * s, bh + 2 * s, (c | s) ? 1u : 0u);
+            mma_tf32_ts(dd, ah + 8 * s, bl + 2 * s, 1u);
+            mma_tf32_ts(dd, al + 8 * s, bh + 2 * s, 1u);
+          }
+          tc_commit(&sm->a1_empty[slot]);
+          tc_commit(&sm->w_empty[ws]);
+          if (c == KC - 1) tc_commit(&sm->d1_full[buf]);
+        }
+        __syncwarp();
+      }
+    };
+    auto gemm2 = [&](int t) {
+      const uint32_t buf = t & 1;
+      mbar_wait(&sm->py_full[buf], (t >> 1) & 1);
+      for (int fb = 0; fb < FB; ++fb, ++g2) {
+        mbar_wait(&sm->a2_full, g2 & 1);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t dg = tmem_base + LT_G + fb * LT_NP;
+          const uint64_t ax1 = mndesc | (uint64_t)a2_a;                       // x1: atoms 0, 1
+          const uint64_t ax2 = mndesc | (uint64_t)(a2_a + 2 * (CHUNK_BYTES >> 4));  // x2: atoms 2, 3
+          const uint64_t bp1 = kdesc | (uint64_t)(py_a + buf * (16384 >> 4));
+          const uint64_t bp2 = bp1 + (8192 >> 4);
+#pragma unroll
+          for (int s = 0; s < 8; ++s) {  // 16 rows of K per instruction
+            const uint32_t aoff = (uint32_t)s * (2048 >> 4);                       // 16 rows x 128 B
+            const uint32_t boff = (uint32_t)(s >> 2) * (4096 >> 4) + (s & 3) * 2;  // atom of 64 rows, 32 B steps
+            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, (t | s) ? 1u : 0u);
+            mma_bf16_ss(dg, ax1 + aoff, bp2 + boff, 1u);
+            mma_bf16_ss(dg, ax2 + aoff, bp1 + boff, 1u);
+          }
+          tc_commit(&sm->a2_empty);
+          if (fb == FB - 1) tc_commit(&sm->py_empty[buf]);
+        }
+        __syncwarp();
+      }
+    };
+    if (my_tiles > 0) gemm1(0);
+    for (int t = 0; t < my_tiles; ++t) {
+      if (t + 1 < my_tiles) gemm1(t + 1);
+      gemm2(t);
+    }
+    if (elect_one()) tc_commit(&sm->g_done);
+    __syncwarp();
+  } else if (warp >= 4 && warp < 8) {
+    // ===================== softmax epilogue (thread == row) =====================
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    double loss = 0.0, sw = 0.0;
+    float gb[LT_NP];
+#pragma unroll
+    for (int k = 0; k < LT_NP; ++k) gb[k] = 0.f;
+    for (int t = 0; t < my_tiles; ++t) {
+      const int buf = t & 1;
+      const int64_t row = (blockIdx.x + (int64_t)t * gridDim.x) * TM + r;
+      const bool live = row < n;
+      const float wi = live ? (w ? w[row] : 1.f) : 0.f;
+      const int yi = live ? (int)y[row] : 0;
+      mbar_wait(&sm->d1_full[buf], (t >> 1) & 1);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld32(tmem_base + lane_addr + LT_D1 + buf * LT_NP, v);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&sm->d1_empty[buf]);
+      float m[LT_NP];
+      float mx = 0.f;  // "subtract max if > 0"
+#pragma unroll
+      for (int k = 0; k < LT_NP; ++k) {
+        m[k] = __uint_as_float(v[k]) + sm->icpt[k];
+        if (k < K) mx = fmaxf(mx, m[k]);
+      }
+      float s = 0.f, my = 0.f;
+#pragma unroll
+      for (int k = 0; k < LT_NP; ++k) {
+        if (k == yi) my = m[k];
+        m[k] = (k < K) ? __expf(m[k] - mx) : 0.f;
+        s += m[k];
+      }
+      const float inv = __fdividef(1.f, s);
+      if (live) {
+        loss += (double)(wi * (logf(s) + mx - my));
+        sw += (double)wi;
+      }
+      // (P - Y) * w as bf16 pairs p1 + p2 into the GEMM2 B operand: [32 classes x 128 rows], K-major,
+      // 2 atoms of 64 rows (128 B per class row), 128B swizzle
+      mbar_wait(&sm->py_empty[buf], ((t >> 1) & 1) ^ 1);
+      uint8_t* pbase = py + (size_t)buf * 16384 + (size_t)(r >> 6) * 4096;
+      const int cb = (r & 63) * 2;  // byte column of this row inside the 128-byte class row
+#pragma unroll
+      for (int k = 0; k < LT_NP; ++k) {
+        const float pk = wi * (m[k] * inv - ((k == yi) ? 1.f : 0.f));
+        const float val = (k < K) ? pk : 0.f;
+        gb[k] += val;
+        const __nv_bfloat16 h1 = __float2bfloat16_rn(val);
+        const __nv_bfloat16 h2 = __float2bfloat16_rn(val - __bfloat162float(h1));
+        const int off = k * 128 + ((((cb >> 4) ^ (k & 7)) << 4) | (cb & 15));
+        *reinterpret_cast<__nv_bfloat16*>(pbase + off) = h1;
+        *reinterpret_cast<__nv_bfloat16*>(pbase + 8192 + off) = h2;
+      }
+      fence_async_smem();
+      mbar_arrive(&sm->py_full[buf]);
+    }
+    // ---- final: G^T from tensor memory, intercept gradient, loss
+    mbar_wait(&sm->g_done, 0);
+    tc_fence_after();
+    const int plen = K * d + K + 2;
+    double* part = partials + (size_t)blockIdx.x * plen;
+    for (int fb = 0; fb < FB; ++fb) {
+      uint32_t v[32];
+      tmem_ld32(tmem_base + lane_addr + LT_G + fb * LT_NP, v);
+      tmem_ld_wait();
+      const int f = fb * 128 + r;  // lane == feature
+#pragma unroll
+      for (int k = 0; k < LT_NP; ++k)
+        if (k < K) part[(size_t)k * d + f] = (my_tiles > 0) ? (double)__uint_as_float(v[k]) : 0.0;
+    }
+#pragma unroll
+    for (int k = 0; k < LT_NP; ++k) {
+      const double t = warp_sum((double)gb[k]);
+      if (lane == 0) sm->red[q][k] = t;
+    }
+    loss = warp_sum(loss);
+    sw = warp_sum(sw);
+    if (lane == 0) {
+      sm->red[q][LT_NP] = loss;
+      sm->red[q][LT_NP + 1] = sw;
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (r < K + 2) {
+      const int src = (r < K) ? r : LT_NP + (r - K);
+      part[(size_t)K * d + r] = sm->red[0][src] + sm->red[1][src] + sm->red[2][src] + sm->red[3][src];
+    }
+  } else if (warp >= 8) {
+    // ===================== split warps: two threads per row, 16 columns of each chunk =====================
+    const int w8 = warp - 8;
+    const int q = w8 & 3, h = w8 >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+    uint32_t g = 0;   // staging chunk counter (same order as the producer)
+    uint32_t g1 = 0;  // GEMM1 operand ring counter
+    uint32_t g2 = 0;  // GEMM2 block counter
+    auto split1 = [&]() {  // one tile of GEMM1: KC chunks -> tf32 hi / lo into tensor memory
+      for (int c = 0; c < KC; ++c, ++g, ++g1) {
+        const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
+        mbar_wait(&sm->xs_full[slot], ph);
+        const uint8_t* src = xs + (size_t)slot * CHUNK_BYTES + (size_t)r * 128;
+        uint32_t hi[16], lo[16];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const float4 v = *reinterpret_cast<const float4*>(src + (((4 * h + p) ^ (r & 7)) << 4));
+          const float h0 = to_tf32(v.x), h1 = to_tf32(v.y), h2 = to_tf32(v.z), h3 = to_tf32(v.w);
+          hi[p * 4 + 0] = __float_as_uint(h0); hi[p * 4 + 1] = __float_as_uint(h1);
+          hi[p * 4 + 2] = __float_as_uint(h2); hi[p * 4 + 3] = __float_as_uint(h3);
+          lo[p * 4 + 0] = __float_as_uint(to_tf32(v.x - h0)); lo[p * 4 + 1] = __float_as_uint(to_tf32(v.y - h1));
+          lo[p * 4 + 2] = __float_as_uint(to_tf32(v.z - h2)); lo[p * 4 + 3] = __float_as_uint(to_tf32(v.w - h3));
+        }
+        mbar_arrive(&sm->xs_empty[slot]);
+        const uint32_t aslot = g1 & 3, aph = (g1 >> 2) & 1;
+        mbar_wait(&sm->a1_empty[aslot], aph ^ 1);
+        tc_fence_after();
+        tmem_st16(tmem_base + lane_addr + LT_A1 + aslot * 64 + h * 16, hi);
+        tmem_st16(tmem_base + lane_addr + LT_A1 + aslot * 64 + 32 + h * 16, lo);
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(&sm->a1_full[aslot]);
+      }
+    };
+    auto split2 = [&]() {  // one tile of GEMM2: FB blocks of 4 chunks -> bf16 x1 / x2, MN-major smem tile
+      for (int fb = 0; fb < FB; ++fb, ++g2) {
+        mbar_wait(&sm->a2_empty, (g2 & 1) ^ 1);
+        for (int kc = 0; kc < 4; ++kc, ++g) {
+          const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
+          mbar_wait(&sm->xs_full[slot], ph);
+          const uint8_t* src = xs + (size_t)slot * CHUNK_BYTES + (size_t)r * 128;
+          // features kc*32 + h*16 .. +15 of this block -> atom kc/2, 16-byte chunks (kc%2)*4 + h*2 + {0,1}
+          uint8_t* d1 = a2 + (size_t)(kc >> 1) * CHUNK_BYTES + (size_t)r * 128;
+          uint8_t* d2 = d1 + 2 * CHUNK_BYTES;
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const float4 va = *reinterpret_cast<const float4*>(src + (((4 * h + 2 * hh) ^ (r & 7)) << 4));
+            const float4 vb = *reinterpret_cast<const float4*>(src + (((4 * h + 2 * hh + 1) ^ (r & 7)) << 4));
+            const float f[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
+            uint32_t o1[4], o2[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const __nv_bfloat162 b1 = __floats2bfloat162_rn(f[2 * e], f[2 * e + 1]);
+              const float2 fb1 = __bfloat1622float2(b1);
+              const __nv_bfloat162 b2 = __floats2bfloat162_rn(f[2 * e] - fb1.x, f[2 * e + 1] - fb1.y);
+              o1[e] = *reinterpret_cast<const uint32_t*>(&b1);
+              o2[e] = *reinterpret_cast<const uint32_t*>(&b2);
+            }
+            const int cidx = (kc & 1) * 4 + h * 2 + hh;
+            const int off = (cidx ^ (r & 7)) << 4;
+            *reinterpret_cast<uint4*>(d1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+            *reinterpret_cast<uint4*>(d2 + off) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+          }
+          mbar_arrive(&sm->xs_empty[slot]);
+        }
+        fence_async_smem();
+        mbar_arrive(&sm->a2_full);
+      }
+    };
+    if (my_tiles > 0) split1();
+    for (int t = 0; t < my_tiles; ++t) {
+      if (t + 1 < my_tiles) split1();
+      split2();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 3) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(LT_TMEM_COLS)
+                 : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+// W' = beta (fp64, [K, d]) as explicit TF32 hi / lo, padded to 32 class rows
+__global__ void lr_mn_prep_kernel(const double* __restrict__ beta, int K, int d, float* __restrict__ wh,
+                                  float* __restrict__ wl) {
+  const int total = LT_NP * d;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int k = i / d;
+    const double v = (k < K) ? beta[i] : 0.0;
+    const float hi = to_tf32((float)v);
+    wh[i] = hi;
+    wl[i] = to_tf32((float)(v - (double)hi));
+  }
+}
+
+bool lr_mn_tc_supported(int d, int64_t ld, int K) { return d % 128 == 0 && d >= 128 && d <= 512 && ld == d && K >= 2 && K <= LT_NP; }
+
+size_t lr_mn_tc_extra_scratch(int d) { return (size_t)2 * LT_NP * d * sizeof(float) + 2048; }
+
+// scratch layout: [ per-CTA fp64 partials (grid x plen) | pad to 1 KB | W_hi | W_lo ]
+int lr_mn_tc_launch(const float* X, const float* y, const float* w, int64_t n, int d, int K, const double* beta,
+                    const double* icpt, double* partials, int grid, void* wbuf, cudaStream_t st) {
+  float* wh = static_cast<float*>(wbuf);
+  float* wl = wh + (size_t)LT_NP * d;
+  lr_mn_prep_kernel<<<(LT_NP * d + 255) / 256, 256, 0, st>>>(beta, K, d, wh, wl);
+  B2F_LAUNCH_CHECK();
+  CUtensorMap mx, mh, ml;
+  int rc;
+  if ((rc = make_map_f32(&mx, X, (uint64_t)n, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
+  if ((rc = make_map_2d(&mh, wh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, LT_NP, (uint64_t)d, (uint64_t)d, LT_NP)) != B2F_OK)
+    return rc;
+  if ((rc = make_map_2d(&ml, wl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, LT_NP, (uint64_t)d, (uint64_t)d, LT_NP)) != B2F_OK)
+    return rc;
+  const size_t smem = (size_t)LT_XS * CHUNK_BYTES + (size_t)LT_WS * LT_WSTAGE + 4 * CHUNK_BYTES + 2 * 16384 +
+                      sizeof(SmemL) + 64;
+  B2F_CUDA(cudaFuncSetAttribute(lr_mn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  lr_mn_tc_kernel<<<grid, LT_THREADS, smem, st>>>(mx, mh, ml, y, w, n, d, K, icpt, partials);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}

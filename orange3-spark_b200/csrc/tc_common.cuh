@@ -143,7 +143,7 @@ static inline EncodeTiledFn get_encode_fn() {
 
 // 2-D row-major [rows, cols] tensor (row pitch `pitch` ELEMENTS), box = 128 bytes x 128 rows, 128B swizzle
 static inline int make_map_2d(CUtensorMap* m, const void* base, CUtensorMapDataType dt, int elem_bytes, uint64_t rows,
-                              uint64_t cols, uint64_t pitch) {
+                              uint64_t cols, uint64_t pitch, uint32_t box_rows = (uint32_t)TM) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     b2f_set_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -151,7 +151,7 @@ static inline int make_map_2d(CUtensorMap* m, const void* base, CUtensorMapDataT
   }
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {pitch * (uint64_t)elem_bytes};
-  cuuint32_t box[2] = {(cuuint32_t)(128 / elem_bytes), (cuuint32_t)TM};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / elem_bytes), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

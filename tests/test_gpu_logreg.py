@@ -62,7 +62,8 @@ def test_lr_binary_lossgrad_matches_oracle(n, d, weighted):
 
 
 @pytest.mark.parametrize("n,d,K", [(7, 3, 3), (1000, 16, 4), (3000, 100, 10), (2500, 512, 20), (1200, 257, 8),
-                                   (800, 700, 5), (600, 64, 32)])
+                                   (800, 700, 5), (600, 64, 32), (1000, 128, 3), (3000, 256, 20),
+                                   (5000, 512, 32), (129, 384, 7), (40000, 512, 20)])
 def test_lr_multinomial_lossgrad_matches_oracle(n, d, K):
     N, G = _imports()
     Xh, yh = _multi_data(n, d, K, n + d + K)
