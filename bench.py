@@ -386,7 +386,7 @@ def lrm_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, Dev
             "config": {"workload": "multinomial LogisticRegression (20 classes) loss+gradient pass on synthetic "
                                    "%dx512 fp32 (BASELINE configs[3])" % n_total, "rows": n_total, "d": d, "K": K},
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
-                         "traffic": None, "kernel": "lr_multinomial_kernel (CUDA-core)",
+                         "traffic": None, "kernel": "lr_mn_tc_kernel (tcgen05: 3xTF32 margins GEMM + bf16x3 gradient GEMM)",
                          "algorithmic_bytes_per_launch": bytes_pass, "peak_source": pk["src"]},
             "check": {"loss": float(p[K * d + K] / p[K * d + K + 1]), "weight_sum": float(p[K * d + K + 1])}}
 
