@@ -17,7 +17,7 @@
 //   warp 3  TMEM allocator
 //   warps 4-7   softmax epilogue (thread == row)
 //   warps 8-15  split: fp32 chunk -> tf32 hi/lo into tensor memory (GEMM1) or bf16 x1/x2 into the MN-major
-//               shared-memory operand tile (GEMM2); two threads per row, 16 columns each
+//               shared-memory operand tile (GEMM2); two groups of 4 warps (thread == row) alternate chunks
 #include <cuda_bf16.h>
 
 #include "tc_common.cuh"
@@ -26,8 +26,9 @@ namespace {
 
 constexpr int LT_THREADS = 512;
 constexpr int LT_SPLIT_THREADS = 256;
+constexpr bool LT_PIPELINED = true;  // true: issue GEMM1(t+1) before GEMM2(t) (keeps two tiles per SM alive in L2)
 constexpr int LT_NP = 32;          // classes padded to the MMA N
-constexpr int LT_XS = 4;           // X staging slots (16 KB each)
+constexpr int LT_XS = 6;           // X staging slots (16 KB each)
 constexpr int LT_WS = 4;           // W stages (hi + lo, 8 KB each)
 constexpr int LT_WSTAGE = 2 * LT_NP * 128;
 // tensor memory columns
@@ -67,14 +68,6 @@ __device__ __forceinline__ void mma_bf16_ss(uint32_t d, uint64_t a, uint64_t b, 
       "l"(a), "l"(b), "r"(IDESC_G2), "r"(acc)
       : "memory");
 }
-__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
-      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
-      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
-      "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
-      : "memory");
-}
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 }  // namespace
@@ -102,14 +95,14 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
   if (threadIdx.x == 0) {
     for (int i = 0; i < LT_XS; ++i) {
       mbar_init(&sm->xs_full[i], 1);
-      mbar_init(&sm->xs_empty[i], LT_SPLIT_THREADS);
+      mbar_init(&sm->xs_empty[i], EPI_THREADS);
     }
     for (int i = 0; i < LT_WS; ++i) {
       mbar_init(&sm->w_full[i], 1);
       mbar_init(&sm->w_empty[i], 1);
     }
     for (int i = 0; i < 4; ++i) {
-      mbar_init(&sm->a1_full[i], LT_SPLIT_THREADS);
+      mbar_init(&sm->a1_full[i], EPI_THREADS);
       mbar_init(&sm->a1_empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
@@ -141,21 +134,24 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     // ===================== X producer =====================
     if (lane == 0) {
       uint32_t g = 0;  // running chunk counter -> staging slot g % LT_XS
-      auto load_chunk = [&](int64_t tile, int col0) {
+      // GEMM1 reads a tile from HBM and asks L2 to keep it (evict-last); GEMM2 re-reads it a few microseconds
+      // later and releases it (evict-first), so the second pass is served by L2 instead of DRAM
+      auto load_chunk = [&](int64_t tile, int col0, uint64_t policy) {
         const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
         mbar_wait(&sm->xs_empty[slot], ph ^ 1);
         mbar_expect_tx(&sm->xs_full[slot], (uint32_t)CHUNK_BYTES);
-        tma_load_2d(xs + (size_t)slot * CHUNK_BYTES, &map_x, col0, (int)(tile * TM), &sm->xs_full[slot]);
+        tma_load_2d_hint(xs + (size_t)slot * CHUNK_BYTES, &map_x, col0, (int)(tile * TM), &sm->xs_full[slot], policy);
         ++g;
       };
-      for (int t = -1; t < my_tiles; ++t) {
-        if (t + 1 < my_tiles) {
-          const int64_t tile = blockIdx.x + (int64_t)(t + 1) * gridDim.x;
-          for (int c = 0; c < KC; ++c) load_chunk(tile, c * 32);
+      for (int t = (LT_PIPELINED ? -1 : 0); t < my_tiles; ++t) {
+        const int t1 = LT_PIPELINED ? t + 1 : t;
+        if (t1 < my_tiles) {
+          const int64_t tile = blockIdx.x + (int64_t)t1 * gridDim.x;
+          for (int c = 0; c < KC; ++c) load_chunk(tile, c * 32, L2_EVICT_LAST);
         }
         if (t >= 0) {
           const int64_t tile = blockIdx.x + (int64_t)t * gridDim.x;
-          for (int c = 0; c < KC; ++c) load_chunk(tile, c * 32);
+          for (int c = 0; c < KC; ++c) load_chunk(tile, c * 32, L2_EVICT_FIRST);
         }
       }
     }
@@ -235,9 +231,13 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
         __syncwarp();
       }
     };
-    if (my_tiles > 0) gemm1(0);
+    if (LT_PIPELINED && my_tiles > 0) gemm1(0);
     for (int t = 0; t < my_tiles; ++t) {
-      if (t + 1 < my_tiles) gemm1(t + 1);
+      if (LT_PIPELINED) {
+        if (t + 1 < my_tiles) gemm1(t + 1);
+      } else {
+        gemm1(t);
+      }
       gemm2(t);
     }
     if (elect_one()) tc_commit(&sm->g_done);
@@ -333,35 +333,41 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
       part[(size_t)K * d + r] = sm->red[0][src] + sm->red[1][src] + sm->red[2][src] + sm->red[3][src];
     }
   } else if (warp >= 8) {
-    // ===================== split warps: two threads per row, 16 columns of each chunk =====================
+    // ===================== split warps: two groups of 4 warps, thread == row, alternate chunks =====================
+    // Each chunk is converted by ONE group (all 32 columns per thread), so two chunks are in flight at once and
+    // the per-chunk latency chain (wait, LDS, convert, tcgen05.st / STS, fence, arrive) overlaps across groups.
     const int w8 = warp - 8;
-    const int q = w8 & 3, h = w8 >> 2;
+    const int q = w8 & 3, grp = w8 >> 2;
     const int r = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-    uint32_t g = 0;   // staging chunk counter (same order as the producer)
+    uint32_t g = 0;   // staging chunk counter (same order as the producer); this group takes g % 2 == grp
     uint32_t g1 = 0;  // GEMM1 operand ring counter
     uint32_t g2 = 0;  // GEMM2 block counter
     auto split1 = [&]() {  // one tile of GEMM1: KC chunks -> tf32 hi / lo into tensor memory
       for (int c = 0; c < KC; ++c, ++g, ++g1) {
+        if ((g & 1u) != (uint32_t)grp) continue;
         const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
         mbar_wait(&sm->xs_full[slot], ph);
         const uint8_t* src = xs + (size_t)slot * CHUNK_BYTES + (size_t)r * 128;
-        uint32_t hi[16], lo[16];
+        uint32_t hi[32], lo[32];
 #pragma unroll
-        for (int p = 0; p < 4; ++p) {
-          const float4 v = *reinterpret_cast<const float4*>(src + (((4 * h + p) ^ (r & 7)) << 4));
-          const float h0 = to_tf32(v.x), h1 = to_tf32(v.y), h2 = to_tf32(v.z), h3 = to_tf32(v.w);
-          hi[p * 4 + 0] = __float_as_uint(h0); hi[p * 4 + 1] = __float_as_uint(h1);
-          hi[p * 4 + 2] = __float_as_uint(h2); hi[p * 4 + 3] = __float_as_uint(h3);
-          lo[p * 4 + 0] = __float_as_uint(to_tf32(v.x - h0)); lo[p * 4 + 1] = __float_as_uint(to_tf32(v.y - h1));
-          lo[p * 4 + 2] = __float_as_uint(to_tf32(v.z - h2)); lo[p * 4 + 3] = __float_as_uint(to_tf32(v.w - h3));
+        for (int p = 0; p < 8; ++p) {
+          const float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
+          // hi = x rounded to TF32 (nearest, ties away) with two full-rate integer ops instead of cvt.rna;
+          // lo = x - hi is exact in fp32 and is left unrounded: whatever the tensor core drops of it is
+          // below 2^-21 |x|
+          const uint32_t h0 = (__float_as_uint(v.x) + 0x1000u) & 0xFFFFE000u, h1 = (__float_as_uint(v.y) + 0x1000u) & 0xFFFFE000u;
+          const uint32_t h2 = (__float_as_uint(v.z) + 0x1000u) & 0xFFFFE000u, h3 = (__float_as_uint(v.w) + 0x1000u) & 0xFFFFE000u;
+          hi[p * 4 + 0] = h0; hi[p * 4 + 1] = h1; hi[p * 4 + 2] = h2; hi[p * 4 + 3] = h3;
+          lo[p * 4 + 0] = __float_as_uint(v.x - __uint_as_float(h0)); lo[p * 4 + 1] = __float_as_uint(v.y - __uint_as_float(h1));
+          lo[p * 4 + 2] = __float_as_uint(v.z - __uint_as_float(h2)); lo[p * 4 + 3] = __float_as_uint(v.w - __uint_as_float(h3));
         }
         mbar_arrive(&sm->xs_empty[slot]);
         const uint32_t aslot = g1 & 3, aph = (g1 >> 2) & 1;
         mbar_wait(&sm->a1_empty[aslot], aph ^ 1);
         tc_fence_after();
-        tmem_st16(tmem_base + lane_addr + LT_A1 + aslot * 64 + h * 16, hi);
-        tmem_st16(tmem_base + lane_addr + LT_A1 + aslot * 64 + 32 + h * 16, lo);
+        tmem_st32(tmem_base + lane_addr + LT_A1 + aslot * 64, hi);
+        tmem_st32(tmem_base + lane_addr + LT_A1 + aslot * 64 + 32, lo);
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(&sm->a1_full[aslot]);
@@ -371,28 +377,31 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
       for (int fb = 0; fb < FB; ++fb, ++g2) {
         mbar_wait(&sm->a2_empty, (g2 & 1) ^ 1);
         for (int kc = 0; kc < 4; ++kc, ++g) {
+          if ((g & 1u) != (uint32_t)grp) continue;
           const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
           mbar_wait(&sm->xs_full[slot], ph);
           const uint8_t* src = xs + (size_t)slot * CHUNK_BYTES + (size_t)r * 128;
-          // features kc*32 + h*16 .. +15 of this block -> atom kc/2, 16-byte chunks (kc%2)*4 + h*2 + {0,1}
+          // features kc*32 .. +31 of this block -> atom kc/2, 16-byte chunks (kc%2)*4 + {0..3} of the row
           uint8_t* d1 = a2 + (size_t)(kc >> 1) * CHUNK_BYTES + (size_t)r * 128;
           uint8_t* d2 = d1 + 2 * CHUNK_BYTES;
 #pragma unroll
-          for (int hh = 0; hh < 2; ++hh) {
-            const float4 va = *reinterpret_cast<const float4*>(src + (((4 * h + 2 * hh) ^ (r & 7)) << 4));
-            const float4 vb = *reinterpret_cast<const float4*>(src + (((4 * h + 2 * hh + 1) ^ (r & 7)) << 4));
+          for (int hh = 0; hh < 4; ++hh) {
+            const float4 va = *reinterpret_cast<const float4*>(src + (((2 * hh) ^ (r & 7)) << 4));
+            const float4 vb = *reinterpret_cast<const float4*>(src + (((2 * hh + 1) ^ (r & 7)) << 4));
             const float f[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
             uint32_t o1[4], o2[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              const __nv_bfloat162 b1 = __floats2bfloat162_rn(f[2 * e], f[2 * e + 1]);
-              const float2 fb1 = __bfloat1622float2(b1);
-              const __nv_bfloat162 b2 = __floats2bfloat162_rn(f[2 * e] - fb1.x, f[2 * e + 1] - fb1.y);
-              o1[e] = *reinterpret_cast<const uint32_t*>(&b1);
-              o2[e] = *reinterpret_cast<const uint32_t*>(&b2);
+              // x1 = x rounded to bf16 (nearest, ties away) and x2 = (x - x1) truncated to bf16, with
+              // full-rate integer ops; __byte_perm packs the two high halves (even k in the low 16 bits)
+              const uint32_t ra = (__float_as_uint(f[2 * e]) + 0x8000u) & 0xFFFF0000u;
+              const uint32_t rb = (__float_as_uint(f[2 * e + 1]) + 0x8000u) & 0xFFFF0000u;
+              const uint32_t la = __float_as_uint(f[2 * e] - __uint_as_float(ra));
+              const uint32_t lb = __float_as_uint(f[2 * e + 1] - __uint_as_float(rb));
+              o1[e] = __byte_perm(ra, rb, 0x7632);
+              o2[e] = __byte_perm(la, lb, 0x7632);
             }
-            const int cidx = (kc & 1) * 4 + h * 2 + hh;
-            const int off = (cidx ^ (r & 7)) << 4;
+            const int off = (((kc & 1) * 4 + hh) ^ (r & 7)) << 4;
             *reinterpret_cast<uint4*>(d1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
             *reinterpret_cast<uint4*>(d2 + off) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
           }
@@ -402,9 +411,13 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
         mbar_arrive(&sm->a2_full);
       }
     };
-    if (my_tiles > 0) split1();
+    if (LT_PIPELINED && my_tiles > 0) split1();
     for (int t = 0; t < my_tiles; ++t) {
-      if (t + 1 < my_tiles) split1();
+      if (LT_PIPELINED) {
+        if (t + 1 < my_tiles) split1();
+      } else {
+        split1();
+      }
       split2();
     }
   }
