@@ -44,6 +44,16 @@ def parse():
     return ap.parse_args()
 
 
+def measured_traffic(kernel, rows):
+    """DRAM bytes per launch from the committed ncu capture, only when this launch has the captured size."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            e = json.load(f)[kernel]
+        return e["traffic"] if e["rows"] == rows else None
+    except Exception:
+        return None
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -229,7 +239,9 @@ def b200_arm(args):
             "data": "synthetic", "config": workload_config(n_total, world), "gpu_launches": launches,
             "clocks": clk.summary(),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["tensor"], "unit": "TFLOP/s",
-                         "frac": achieved / pk["tensor"], "traffic": None, "kernel": "b2f_kmeans_step_ws: " + algo_name,
+                         "frac": achieved / pk["tensor"],
+                         "traffic": measured_traffic("km_tcb_kernel", n) if eng.use_ws else None,
+                         "kernel": "b2f_kmeans_step_ws: " + algo_name,
                          "kernel_ms": kern_ms, "peak_source": pk["src"] + " bf16 sustained (no TF32 figure measured)",
                          "algorithmic_flops_per_launch": flops},
             "check": {"cost_after_last_timed_iter": cost_after, "rows_accumulated_last_iter_this_rank": rows_after,
@@ -339,7 +351,7 @@ def lr_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, Devi
             "config": {"workload": "binary LogisticRegression loss+gradient pass on synthetic %dx256 fp32 "
                                    "(BASELINE configs[2])" % n_total, "rows": n_total, "d": d},
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
-                         "traffic": None, "kernel": "lr_binary_kernel", "algorithmic_bytes_per_launch": bytes_pass,
+                         "traffic": measured_traffic("lr_binary_kernel", n), "kernel": "lr_binary_kernel", "algorithmic_bytes_per_launch": bytes_pass,
                          "peak_source": pk["src"]},
             "check": {"loss": float(p[d + 1] / p[d + 2]), "weight_sum": float(p[d + 2])}}
 
@@ -386,7 +398,7 @@ def lrm_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, Dev
             "config": {"workload": "multinomial LogisticRegression (20 classes) loss+gradient pass on synthetic "
                                    "%dx512 fp32 (BASELINE configs[3])" % n_total, "rows": n_total, "d": d, "K": K},
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
-                         "traffic": None, "kernel": "lr_mn_tc_kernel (tcgen05: 3xTF32 margins GEMM + bf16x3 gradient GEMM)",
+                         "traffic": measured_traffic("lr_mn_tc_kernel", n), "kernel": "lr_mn_tc_kernel (tcgen05: 3xTF32 margins GEMM + bf16x3 gradient GEMM)",
                          "algorithmic_bytes_per_launch": bytes_pass, "peak_source": pk["src"]},
             "check": {"loss": float(p[K * d + K] / p[K * d + K + 1]), "weight_sum": float(p[K * d + K + 1])}}
 
