@@ -28,7 +28,8 @@ constexpr int LT_THREADS = 512;
 constexpr int LT_SPLIT_THREADS = 256;
 constexpr bool LT_PIPELINED = true;  // true: issue GEMM1(t+1) before GEMM2(t) (keeps two tiles per SM alive in L2)
 constexpr int LT_NP = 32;          // classes padded to the MMA N
-constexpr int LT_XS = 6;           // X staging slots (16 KB each)
+constexpr int LT_XS = 6;           // X staging slots (16 KB each); must stay a multiple of the number of split groups (2):
+                                   // a slot is then always consumed by the same group and its parity waits cannot alias
 constexpr int LT_WS = 4;           // W stages (hi + lo, 8 KB each)
 constexpr int LT_WSTAGE = 2 * LT_NP * 128;
 // tensor memory columns
