@@ -322,10 +322,11 @@ def lr_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, Devi
     w_true = (rng.standard_normal(d) / np.sqrt(d)).astype(np.float32)
     Xt = torch.empty((n, d), dtype=torch.float32, device=dev)
     y = torch.empty(n, dtype=torch.float32, device=dev)
-    N.check(L.b2f_synth_logistic(N.ptr(Xt), N.ptr(y), n, lo, d, d, SEED + 1, N.ptr(torch.from_numpy(scale).to(dev)),
-                                 N.ptr(torch.from_numpy(w_true).to(dev)),
-                                 N.ptr(torch.tensor([0.3], dtype=torch.float32, device=dev)), 2, N.stream_ptr()),
-            "b2f_synth_logistic")
+    sc_d, w_d = torch.from_numpy(scale).to(dev), torch.from_numpy(w_true).to(dev)  # keep alive across the call
+    b_d = torch.tensor([0.3], dtype=torch.float32, device=dev)
+    N.check(L.b2f_synth_logistic(N.ptr(Xt), N.ptr(y), n, lo, d, d, SEED + 1, N.ptr(sc_d), N.ptr(w_d), N.ptr(b_d), 2,
+                                 N.stream_ptr()), "b2f_synth_logistic")
+    torch.cuda.synchronize()
     eng = CudaLogRegEngine(DeviceMatrix(Xt, d, lo), y, None, 2)
     beta = (rng.standard_normal(d) * 0.05 / scale)
     eng.beta.copy_(torch.from_numpy(beta).to(dev))
@@ -370,10 +371,11 @@ def lrm_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, Dev
     w_true = (rng.standard_normal((K, d)) / np.sqrt(d)).astype(np.float32)
     Xt = torch.empty((n, d), dtype=torch.float32, device=dev)
     y = torch.empty(n, dtype=torch.float32, device=dev)
-    N.check(L.b2f_synth_logistic(N.ptr(Xt), N.ptr(y), n, lo, d, d, SEED + 2, N.ptr(torch.from_numpy(scale).to(dev)),
-                                 N.ptr(torch.from_numpy(w_true).to(dev)),
-                                 N.ptr(torch.zeros(K, dtype=torch.float32, device=dev)), K, N.stream_ptr()),
-            "b2f_synth_logistic")
+    sc_d, w_d = torch.from_numpy(scale).to(dev), torch.from_numpy(w_true).to(dev)  # keep alive across the call
+    b_d = torch.zeros(K, dtype=torch.float32, device=dev)
+    N.check(L.b2f_synth_logistic(N.ptr(Xt), N.ptr(y), n, lo, d, d, SEED + 2, N.ptr(sc_d), N.ptr(w_d), N.ptr(b_d), K,
+                                 N.stream_ptr()), "b2f_synth_logistic")
+    torch.cuda.synchronize()
     eng = CudaLogRegEngine(DeviceMatrix(Xt, d, lo), y, None, K)
     eng.beta.copy_(torch.from_numpy((rng.standard_normal((K, d)) * 0.05 / scale[None, :]).ravel()).to(dev))
 

@@ -286,9 +286,10 @@ class LogisticRegression(Estimator):
                 raw = np.log1p(hist[:K])
                 x0[K * d:] = raw - raw.mean()
         if lam1 == 0.0:
-            opt = LBFGS(max_iter, 10, tol)
+            opt = LBFGS(max_iter, 10, tol, resolution=1e-9)
         else:
-            opt = OWLQN(max_iter, 10, np.concatenate([np.tile(l1w, K), np.zeros(K if fit_icpt else 0)]), tol)
+            opt = OWLQN(max_iter, 10, np.concatenate([np.tile(l1w, K), np.zeros(K if fit_icpt else 0)]), tol,
+                        resolution=1e-9)
         trail = opt.run(f, x0)
         last = trail[-1]
         Cs = last.x[: K * d].reshape(K, d) * active[None, :]
@@ -301,6 +302,7 @@ class LogisticRegression(Estimator):
                 coef = coef - coef.mean(axis=0, keepdims=True)
         summ = LogisticRegressionSummary([s.adj_value for s in trail], last.iter, last.n_evals)
         summ.iterates = [s.x.copy() for s in trail]
+        summ.passesAtState = [s.n_evals for s in trail]
         summ.featuresStd, summ.featuresMean, summ.weightSum, summ.histogram = std, mean, W, hist
         model = LogisticRegressionModel(coef, b, 2 if binomial else K, summ)
         model._set(featuresCol=g("featuresCol"), labelCol=g("labelCol"), predictionCol=g("predictionCol"),

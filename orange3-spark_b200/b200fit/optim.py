@@ -111,8 +111,13 @@ class StrongWolfe:
 
 
 class LBFGS:
-    def __init__(self, max_iter=100, memory=10, tol=1e-6, window=10):
+    def __init__(self, max_iter=100, memory=10, tol=1e-6, window=10, resolution=0.0):
+        """`resolution`: relative resolution of the objective (0 = exact arithmetic, Breeze's behaviour).
+        The GPU passes evaluate margins in fp32, so objective differences below ~1e-9 relative are noise;
+        when a line search fails while the last accepted step improved the objective by less than that, the
+        run stops at once instead of burning ~20 more passes on Breeze's reset-and-retry."""
         self.max_iter, self.memory, self.tol, self.window = max_iter, memory, tol, window
+        self.resolution = resolution
 
     # ---- pieces OWL-QN overrides ------------------------------------------------------
     def adjust(self, x, grad, value):
@@ -196,7 +201,9 @@ class LBFGS:
                               (st.fvals + [v])[-self.window:], False, fn.count)
                 retried = False
             except LineSearchError:
-                if retried:
+                at_resolution = (self.resolution > 0.0 and len(trail) >= 2 and
+                                 abs(trail[-2].adj_value - st.adj_value) <= self.resolution * abs(st.adj_value))
+                if retried or at_resolution:
                     st = OptState(st.x, st.value, st.grad, st.adj_value, st.adj_grad, st.iter, st.init_adj_value,
                                   st.mem_s, st.mem_y, st.fvals, True, fn.count)
                 else:
@@ -208,8 +215,8 @@ class LBFGS:
 class OWLQN(LBFGS):
     """Orthant-wise L-BFGS; `l1` holds the per-coordinate L1 weight (0 = unpenalised)."""
 
-    def __init__(self, max_iter, memory, l1, tol):
-        super().__init__(max_iter, memory, tol)
+    def __init__(self, max_iter, memory, l1, tol, resolution=0.0):
+        super().__init__(max_iter, memory, tol, resolution=resolution)
         self.l1 = np.asarray(l1, dtype=np.float64)
 
     def adjust(self, x, grad, value):

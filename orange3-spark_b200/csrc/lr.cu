@@ -109,8 +109,8 @@ __global__ void __launch_bounds__(LR_THREADS, (NCH >= 8) ? 1 : 2)
       const float yi = myrow == 0 ? yy[0] : myrow == 1 ? yy[1] : myrow == 2 ? yy[2] : yy[3];
       const float wi = myrow == 0 ? ww[0] : myrow == 1 ? ww[1] : myrow == 2 ? ww[2] : ww[3];
       const float m = (v + b0l) + b0h;
-      const float e = __expf(-fabsf(m));               // one exponential serves sigmoid and softplus
-      const float inv = __fdividef(1.f, 1.f + e);
+      const float e = expf(-fabsf(m));                 // one exponential serves sigmoid and softplus
+      const float inv = 1.f / (1.f + e);  // IEEE division: the gradient must match the loss to ~1e-8 near convergence
       const float p = m >= 0.f ? inv : e * inv;
       const float softplus = fmaxf(m, 0.f) + log1pf(e);
       const float mymult = wi * (p - yi);
@@ -140,8 +140,8 @@ __global__ void __launch_bounds__(LR_THREADS, (NCH >= 8) ? 1 : 2)
         ml = fmaf(x[i][ch].z, bl[ch].z, ml); ml = fmaf(x[i][ch].w, bl[ch].w, ml);
       }
       const float m = (warp_sum(mh + ml) + b0l) + b0h;
-      const float e = __expf(-fabsf(m));
-      const float inv = __fdividef(1.f, 1.f + e);
+      const float e = expf(-fabsf(m));
+      const float inv = 1.f / (1.f + e);  // IEEE division: the gradient must match the loss to ~1e-8 near convergence
       const float p = m >= 0.f ? inv : e * inv;
       const float mult = ww[i] * (p - yy[i]);
       if (lane == 0) {

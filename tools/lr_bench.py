@@ -25,8 +25,10 @@ X = torch.empty((a.n, a.d), dtype=torch.float32, device=dev)
 y = torch.empty(a.n, dtype=torch.float32, device=dev)
 KM = 1 if a.K == 2 else a.K
 wt = torch.from_numpy((rng.standard_normal((KM, a.d)) / np.sqrt(a.d)).astype(np.float32)).to(dev)
-N.check(L.b2f_synth_logistic(N.ptr(X), N.ptr(y), a.n, 0, a.d, a.d, 7, None, N.ptr(wt),
-                             N.ptr(torch.zeros(KM, dtype=torch.float32, device=dev)), a.K, N.stream_ptr()), "synth")
+bt = torch.zeros(KM, dtype=torch.float32, device=dev)
+N.check(L.b2f_synth_logistic(N.ptr(X), N.ptr(y), a.n, 0, a.d, a.d, 7, None, N.ptr(wt), N.ptr(bt), a.K,
+                             N.stream_ptr()), "synth")
+torch.cuda.synchronize()
 eng = CudaLogRegEngine(DeviceMatrix(X, a.d), y, None, a.K)
 eng.beta.copy_(torch.from_numpy(rng.standard_normal(KM * a.d) * 0.05).to(dev))
 ts = []
