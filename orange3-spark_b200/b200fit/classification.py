@@ -286,10 +286,10 @@ class LogisticRegression(Estimator):
                 raw = np.log1p(hist[:K])
                 x0[K * d:] = raw - raw.mean()
         if lam1 == 0.0:
-            opt = LBFGS(max_iter, 10, tol, resolution=1e-9)
+            opt = LBFGS(max_iter, 10, tol, resolution=1e-8)
         else:
             opt = OWLQN(max_iter, 10, np.concatenate([np.tile(l1w, K), np.zeros(K if fit_icpt else 0)]), tol,
-                        resolution=1e-9)
+                        resolution=1e-8)
         trail = opt.run(f, x0)
         last = trail[-1]
         Cs = last.x[: K * d].reshape(K, d) * active[None, :]

@@ -57,8 +57,11 @@ class StrongWolfe:
 
     C1, C2 = 1e-4, 0.9
 
-    def __init__(self, max_zoom=10, max_search=10):
-        self.max_zoom, self.max_search = max_zoom, max_search
+    def __init__(self, max_zoom=10, max_search=10, slack=0.0):
+        """`slack`: absolute resolution of the objective values.  Every comparison BETWEEN OBJECTIVE VALUES is
+        relaxed by it, so that once the true decrease of a step falls below the rounding noise of the fp32 passes the
+        slope tests (whose inputs are accurate to ~1e-9) decide alone.  0 reproduces Breeze exactly."""
+        self.max_zoom, self.max_search, self.slack = max_zoom, max_search, slack
 
     @staticmethod
     def _cubic(a, b):
@@ -76,6 +79,7 @@ class StrongWolfe:
     def search(self, phi, t0):
         start = Bracket(0.0, *phi(0.0))
         f0, g0 = start.f, start.df
+        eps = self.slack
         if g0 > 0:
             raise LineSearchError("not a descent direction (slope %g)" % g0)
 
@@ -83,7 +87,7 @@ class StrongWolfe:
             for _ in range(self.max_zoom):
                 t = self._cubic(hi, lo) if lo.t > hi.t else self._cubic(lo, hi)
                 c = Bracket(t, *phi(t))
-                if c.f > f0 + self.C1 * c.t * g0 or c.f >= lo.f:
+                if c.f > f0 + self.C1 * c.t * g0 + eps or c.f >= lo.f + eps:
                     hi = c
                     continue
                 if abs(c.df) <= self.C2 * abs(g0):
@@ -99,7 +103,7 @@ class StrongWolfe:
             if math.isinf(c.f) or math.isnan(c.f):
                 t *= 0.5
                 continue
-            if c.f > f0 + self.C1 * t * g0 or (i > 0 and c.f >= prev.f):
+            if c.f > f0 + self.C1 * t * g0 + eps or (i > 0 and c.f >= prev.f + eps):
                 return zoom(prev, c)
             if abs(c.df) <= self.C2 * abs(g0):
                 return c.t
@@ -113,8 +117,11 @@ class StrongWolfe:
 class LBFGS:
     def __init__(self, max_iter=100, memory=10, tol=1e-6, window=10, resolution=0.0):
         """`resolution`: relative resolution of the objective (0 = exact arithmetic, Breeze's behaviour).
-        The GPU passes evaluate margins in fp32, so objective differences below ~1e-9 relative are noise;
-        when a line search fails while the last accepted step improved the objective by less than that, the
+        The GPU passes evaluate margins in fp32, so objective differences below ~1e-8 relative are noise
+        (measured: ~5e-10 between neighbouring points at n = 5000, tools/lr_noise_check.py), while the gradient is
+        good to ~3e-9 absolute.  Two consequences: the line searches compare objective values with a slack of
+        resolution * |f| (so the last, superlinear steps are accepted on their slopes, as they are in fp64), and when
+        a line search still fails while the last accepted step improved the objective by less than the resolution the
         run stops at once instead of burning ~20 more passes on Breeze's reset-and-retry."""
         self.max_iter, self.memory, self.tol, self.window = max_iter, memory, tol, window
         self.resolution = resolution
@@ -135,7 +142,7 @@ class LBFGS:
             return v, float(np.dot(g, direction))
 
         t0 = 1.0 / float(np.linalg.norm(direction)) if st.iter == 0 else 1.0
-        alpha = StrongWolfe().search(phi, t0)
+        alpha = StrongWolfe(slack=self.resolution * abs(st.value)).search(phi, t0)
         if alpha * float(np.linalg.norm(st.grad)) < 1e-10:
             raise LineSearchError("step size underflow")
         return alpha
@@ -245,18 +252,18 @@ class OWLQN(LBFGS):
 
         first = st.iter < 1
         t0 = 0.5 / float(np.linalg.norm(st.grad)) if first else 1.0
-        return backtrack(phi, st.value, t0, 0.1 if first else 0.5)
+        return backtrack(phi, st.value, t0, 0.1 if first else 0.5, slack=self.resolution * abs(st.adj_value))
 
 
 def backtrack(phi, f_at_zero_hint, t0, shrink, grow=2.1, c_armijo=1e-4, c_wolfe=0.9, max_iter=20, t_min=1e-10,
-              t_max=1e10):
+              t_max=1e10, slack=0.0):
     """Breeze's BacktrackingLineSearch, including its first-trial behaviour: the first test
     pairs the caller-supplied value at 0 with the slope measured at t0."""
     f0, g0 = phi(0.0)
     f_t, g_t = f_at_zero_hint, phi(t0)[1]
     t = t0
     for k in range(max_iter):
-        if f_t > f0 + t * g0 * c_armijo:
+        if f_t > f0 + t * g0 * c_armijo + slack:
             factor = shrink
         elif g_t < c_wolfe * g0:
             factor = grow

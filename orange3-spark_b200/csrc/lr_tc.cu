@@ -276,10 +276,10 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
 #pragma unroll
       for (int k = 0; k < LT_NP; ++k) {
         if (k == yi) my = m[k];
-        m[k] = (k < K) ? __expf(m[k] - mx) : 0.f;
+        m[k] = (k < K) ? expf(m[k] - mx) : 0.f;
         s += m[k];
       }
-      const float inv = __fdividef(1.f, s);
+      const float inv = 1.f / s;
       if (live) {
         loss += (double)(wi * (logf(s) + mx - my));
         sw += (double)wi;
