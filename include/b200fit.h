@@ -47,6 +47,8 @@ extern "C" {
 #define B2F_KM_TC1 3     /* tcgen05 1xTF32 contraction (filter pass; labels need refine) */
 #define B2F_KM_TCB 4     /* tcgen05 bf16x3 filter pass + 3xTF32 re-check of uncertain rows; d in {64,128},
                             k % 128 == 0; only through b2f_kmeans_step_ws (needs labels + workspace)    */
+#define B2F_KM_TCH 5     /* same pipeline with a single-MMA fp16 filter pass (a third of the tensor work, a
+                            wider uncertainty band); same shapes and entry point as B2F_KM_TCB           */
 
 typedef void* b2f_stream_t;
 
@@ -110,11 +112,11 @@ int b2f_kmeans_acc_zero(void* acc, int k, int d, b2f_stream_t stream);
 int b2f_kmeans_step(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep, int k,
                     void* acc, int32_t* labels, int algo, b2f_stream_t stream);
 /* Same pass with a caller-provided workspace (b2f_kmeans_ws_bytes(n, k, d) bytes, 256-byte aligned),
- * which enables B2F_KM_TCB: rows whose label the bf16x3 pass cannot certify are listed in the
- * workspace, gathered and re-assigned by the 3xTF32 kernel.  The list holds n/16 rows; if more rows are
- * uncertain the excess is DROPPED and the payload's row count (last entry) comes out below n -- the
- * caller must then redo the pass with B2F_KM_TC3.  B2F_KM_AUTO picks TCB when the shape allows it and
- * labels / ws are given, else behaves like b2f_kmeans_step.  Same reference call site as above.        */
+ * which enables B2F_KM_TCB / B2F_KM_TCH: rows whose label the low-precision filter pass cannot certify
+ * are listed in the workspace, gathered and re-assigned by the 3xTF32 kernel.  The list holds n/8 rows; if
+ * more rows are uncertain the excess is DROPPED and the payload's row count (last entry) comes out below
+ * n -- the caller must then redo the pass with B2F_KM_TC3.  B2F_KM_AUTO picks TCH when the shape allows it
+ * and labels / ws are given, else behaves like b2f_kmeans_step.  Same reference call site as above.    */
 size_t b2f_kmeans_ws_bytes(int64_t n, int k, int d);
 int b2f_kmeans_step_ws(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep, int k,
                        void* acc, int32_t* labels, void* ws, size_t ws_bytes, int algo, b2f_stream_t stream);

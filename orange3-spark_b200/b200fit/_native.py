@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libb200fit.so")
 
 # dtype codes (include/b200fit.h)
 F32, F64, I32, I64, U8 = 0, 1, 2, 3, 4
-KM_AUTO, KM_GENERIC, KM_TC3, KM_TC1, KM_TCB = 0, 1, 2, 3, 4
+KM_AUTO, KM_GENERIC, KM_TC3, KM_TC1, KM_TCB, KM_TCH = 0, 1, 2, 3, 4, 5
 
 _vp, _i32, _i64, _u64, _f32, _f64, _sz = (C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_float, C.c_double,
                                           C.c_size_t)

@@ -43,11 +43,12 @@ class CudaLloydEngine:
         self.status_f64 = torch.zeros(2, dtype=torch.float64, device=dev)
         self.launches = 0
         self.fallbacks = 0
-        # bf16x3 filter pass + 3xTF32 re-check (B2F_KM_TCB) needs a labels buffer and a workspace
-        self.use_ws = (algo in (N.KM_AUTO, N.KM_TCB) and w is None and self.d in (64, 128) and self.k % 128 == 0
-                       and X.ld % 4 == 0 and X.n > 0)
-        if algo == N.KM_TCB and not self.use_ws:
-            raise ValueError("B2F_KM_TCB needs d in {64, 128}, k % 128 == 0 and no row weights")
+        # low-precision filter pass + 3xTF32 re-check (B2F_KM_TCH fp16 / B2F_KM_TCB bf16x3; AUTO = TCH) needs a
+        # labels buffer and a workspace
+        self.use_ws = (algo in (N.KM_AUTO, N.KM_TCB, N.KM_TCH) and w is None and self.d in (64, 128)
+                       and self.k % 128 == 0 and X.ld % 4 == 0 and X.n > 0)
+        if algo in (N.KM_TCB, N.KM_TCH) and not self.use_ws:
+            raise ValueError("B2F_KM_TCB / B2F_KM_TCH need d in {64, 128}, k % 128 == 0 and no row weights")
         if self.use_ws:
             self.ws_bytes = int(self.L.b2f_kmeans_ws_bytes(X.n, self.k, self.d))
             self.ws = torch.zeros(self.ws_bytes, dtype=torch.uint8, device=dev)
@@ -68,7 +69,7 @@ class CudaLloydEngine:
 
     def step(self, labels=None, exact=False, events=None):
         """Zero accumulators, assign + accumulate this shard, fold -> fp64 payload (device).
-        exact=True forces the 3xTF32 kernel (used when the re-check list of the bf16x3 pass overflowed)."""
+        exact=True forces the 3xTF32 kernel (used when the re-check list of the filter pass overflowed)."""
         s = N.stream_ptr()
         X = self.X
         N.check(self.L.b2f_kmeans_acc_zero(N.ptr(self.acc), self.k, self.d, s), "b2f_kmeans_acc_zero")
@@ -79,9 +80,10 @@ class CudaLloydEngine:
             N.check(self.L.b2f_kmeans_step_ws(N.ptr(X.data), X.n, X.d, X.ld, None, N.ptr(self.prep), self.k,
                                               N.ptr(self.acc), N.ptr(lab), N.ptr(self.ws), self.ws_bytes, self.algo,
                                               s), "b2f_kmeans_step_ws")
-            self.launches += 4  # filter kernel, gather, 3xTF32 re-check, scatter
+            # filter kernel, gather, 3xTF32 re-check, scatter, exact tail (+ 2 cost-term kernels around the fp16 filter)
+            self.launches += 5 if self.algo == N.KM_TCB else 7
         else:
-            algo = N.KM_TC3 if (exact or self.algo == N.KM_TCB) else self.algo
+            algo = N.KM_TC3 if (exact or self.algo in (N.KM_TCB, N.KM_TCH)) else self.algo
             N.check(self.L.b2f_kmeans_step(N.ptr(X.data), X.n, X.d, X.ld, N.ptr(self.w), N.ptr(self.prep), self.k,
                                            N.ptr(self.acc), N.ptr(labels), algo, s), "b2f_kmeans_step")
             self.launches += 1
@@ -93,7 +95,7 @@ class CudaLloydEngine:
 
     def rows_counted(self, payload):
         """Rows that were accumulated (last payload entry); below the row total means the re-check list
-        of the bf16x3 pass overflowed and the pass must be redone with exact=True."""
+        of the filter pass overflowed and the pass must be redone with exact=True."""
         return float(payload[self.k * self.d + self.k + 1].item())
 
     def finalize_async(self, payload, tol):

@@ -46,9 +46,16 @@ static inline size_t b2f_align_up(size_t x, size_t a) { return (x + a - 1) / a *
 //          C64  double[k*d]  copy of the fp64 master (refine / exact paths)
 //          CB1  bf16[k*d]    -2*c rounded to bf16          (operands of the bf16x3 kernel)
 //          CB2  bf16[k*d]    -2*c - CB1, rounded to bf16
-//          MISC float[64]    [0] = max_j ||c_j|| (as float bits, written with atomicMax) ]
+//          CH16 fp16[k*d]    -2*c * S rounded to fp16, S a power of two (operand of the fp16 filter kernel)
+//          CN64 double[k]    ||c||^2 in fp64 (exact re-check)
+//          MISC float[64]    [0] = max_j ||c_j|| rounded up   [1] = max |c_jl|   (float bits, atomicMax)
+//                            [2] = S   [3] = 1 / S^2   (written by the second prepare kernel)            ]
+#define KM_MISC_CMAX 0
+#define KM_MISC_CABS 1
+#define KM_MISC_SCALE 2
+#define KM_MISC_INV_SCALE2 3
 struct KmPrepLayout {
-  size_t off_c32, off_ch, off_cl, off_cn, off_c64, off_cb1, off_cb2, off_misc, bytes;
+  size_t off_c32, off_ch, off_cl, off_cn, off_c64, off_cb1, off_cb2, off_ch16, off_cn64, off_misc, bytes;
 };
 static inline KmPrepLayout km_prep_layout(int k, int d) {
   KmPrepLayout L;
@@ -61,6 +68,8 @@ static inline KmPrepLayout km_prep_layout(int k, int d) {
   L.off_c64 = o; o = b2f_align_up(o + kd * 8, 1024);
   L.off_cb1 = o; o = b2f_align_up(o + kd * 2, 1024);
   L.off_cb2 = o; o = b2f_align_up(o + kd * 2, 1024);
+  L.off_ch16 = o; o = b2f_align_up(o + kd * 2, 1024);
+  L.off_cn64 = o; o = b2f_align_up(o + (size_t)k * 8, 1024);
   L.off_misc = o; o = b2f_align_up(o + 256, 1024);
   L.bytes = o;
   return L;
@@ -134,11 +143,14 @@ int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, i
                int passes, bool accumulate, const int* n_dev, const KmRecheck* recheck, cudaStream_t stream);
 bool km_tc_supported(int k, int d, int64_t ld);
 
-// implemented in kmeans_tcb.cu (bf16x3 filter pass + 3xTF32 re-check of ambiguous rows)
+// implemented in kmeans_tcb.cu (filter pass + 3xTF32 re-check of uncertain rows + exact fp64 tail)
+// filter: KM_FILTER_BF16X3 = three bf16 MMAs per product, KM_FILTER_FP16 = one fp16 MMA (scaled operands)
+#define KM_FILTER_BF16X3 0
+#define KM_FILTER_FP16 1
 bool km_tcb_supported(int k, int d, int64_t ld);
 size_t km_tcb_ws_bytes(int64_t n, int k, int d);
 int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
-                void* ws, size_t ws_bytes, bool accumulate, cudaStream_t stream);
+                void* ws, size_t ws_bytes, bool accumulate, int filter, cudaStream_t stream);
 
 // implemented in lr_tc.cu (tcgen05 multinomial loss + gradient)
 bool lr_mn_tc_supported(int d, int64_t ld, int K);

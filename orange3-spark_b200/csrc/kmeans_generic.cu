@@ -5,6 +5,7 @@
 //   orangecontrib/spark/widgets/ml/spark_ml_clustering.py:14) and
 //   orangecontrib/spark/widgets/ml/spark_ml_model.py:53;  MLlib semantics: SURVEY.md A.2.
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include "common.cuh"
 
@@ -14,16 +15,19 @@
 __global__ void km_prepare_kernel(const double* __restrict__ C, int k, int d, float* __restrict__ c32,
                                   float* __restrict__ ch, float* __restrict__ cl, float* __restrict__ cn,
                                   double* __restrict__ c64, __nv_bfloat16* __restrict__ cb1,
-                                  __nv_bfloat16* __restrict__ cb2, unsigned int* __restrict__ misc) {
+                                  __nv_bfloat16* __restrict__ cb2, double* __restrict__ cn64,
+                                  unsigned int* __restrict__ misc) {
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
   for (int j = warp; j < k; j += nwarps) {
     double nn = 0.0;
+    float amax = 0.f;
     for (int c = lane; c < d; c += 32) {
       const size_t i = (size_t)j * d + c;
       const double v = C[i];
       nn += v * v;
+      amax = fmaxf(amax, __double2float_ru(fabs(v)));
       c32[i] = (float)v;
       c64[i] = v;
       const double m2 = -2.0 * v;
@@ -37,10 +41,37 @@ __global__ void km_prepare_kernel(const double* __restrict__ C, int k, int d, fl
     nn = warp_sum(nn);
     if (lane == 0) {
       cn[j] = (float)nn;
+      cn64[j] = nn;
       // max_j ||c_j|| rounded up: non-negative floats order like their bit patterns
-      atomicMax(misc, __float_as_uint(__fsqrt_ru((float)nn * 1.0000002f)));
+      atomicMax(misc + KM_MISC_CMAX, __float_as_uint(__fsqrt_ru((float)nn * 1.0000002f)));
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if (lane == 0 && amax > 0.f && amax < INFINITY) atomicMax(misc + KM_MISC_CABS, __float_as_uint(amax));
   }
+}
+
+// Second prepare kernel: fp16 operand plane of the single-MMA filter kernel.  S = 2^e is chosen so that
+// max |-2 c_jl| * S lies in [2^11, 2^12]: centre entries keep full fp16 precision down to 2^-26 of the largest one
+// and data entries up to ~16x the largest |-2c| entry stay finite (rows beyond that are sent to the re-check).
+__global__ void km_prepare_h16_kernel(const double* __restrict__ C, int k, int d, __half* __restrict__ ch16,
+                                      float* __restrict__ misc) {
+  const float cabs = misc[KM_MISC_CABS];
+  int e = 0;
+  if (cabs > 0.f) {
+    int ex;
+    frexpf(2.f * cabs, &ex);  // 2 cabs = m * 2^ex, m in [0.5, 1)
+    e = 12 - ex;
+    e = max(-60, min(60, e));
+  }
+  const float S = exp2f((float)e);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    misc[KM_MISC_SCALE] = S;
+    misc[KM_MISC_INV_SCALE2] = exp2f((float)(-2 * e));
+  }
+  const size_t kd = (size_t)k * d;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < kd; i += (size_t)gridDim.x * blockDim.x)
+    ch16[i] = __float2half_rn((float)(-2.0 * C[i]) * S);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -207,77 +238,108 @@ static int km_generic_launch(const float* X, int64_t n, int d, int64_t ld, const
 }
 
 // ---------------------------------------------------------------------------------------------
-// exact re-check: one CTA per listed row, every centre, fp64 direct form sum (x - c)^2 on the fp64 master
-// centres, ascending centre order with strict '<' (findClosest tie rule); accumulates straight into the
-// fp64 payload.  Only rows that the tensor-core kernels could not certify come here (a few per million).
+// exact re-check: fp64 assignment of the listed rows against every centre, on the fp64 master centres:
+//   dist(r, j) = ||x_r||^2 + ||c_j||^2 - 2 x_r . c_j   (all fp64; each dot product is summed in the same order
+//   whichever thread computes it, so duplicate centres tie exactly and the lowest index wins: findClosest order).
+// A CTA takes KX_ROWS listed rows: warp w owns rows 4w .. 4w+3, lane l owns centre jb + l of the current block of
+// 32 centres, whose coordinates pass through a padded shared-memory tile; so the centre table is read from L2 once
+// per 32 rows.  Accumulates straight into the fp64 payload.  Only rows that the tensor-core kernels could not
+// certify come here (tens per million).
 // ---------------------------------------------------------------------------------------------
+#define KX_ROWS 32
+#define KX_MAX_D 512
 __global__ void __launch_bounds__(256) km_exact_kernel(const float* __restrict__ X, int64_t ld, int d,
-                                                       const double* __restrict__ C64, int k,
+                                                       const double* __restrict__ C64,
+                                                       const double* __restrict__ CN64, int k,
                                                        double* __restrict__ payload, int32_t* __restrict__ labels,
                                                        const int* __restrict__ count, const int32_t* __restrict__ idx,
                                                        int cap, int accumulate) {
-  // one CTA per listed row: warp w scans centres w, w+8, ... (4 in flight), lanes stride the columns
-  __shared__ double s_best[8];
-  __shared__ int s_bi[8];
+  extern __shared__ __align__(16) double kx_smem[];
+  const int dpad = (d + 31) & ~31;
+  double* xs = kx_smem;                     // [KX_ROWS][dpad]
+  double* cs = xs + (size_t)KX_ROWS * dpad; // [32 centres][34]: rows 16-byte aligned, conflict-free column reads
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int used = min(*count, cap);
   double cost = 0.0, rows = 0.0;
-  for (int i = blockIdx.x; i < used; i += gridDim.x) {
-    const int64_t r = idx[i];
-    const float* xr = X + r * ld;
-    double best = INFINITY;
-    int bi = 0x7fffffff;
-    for (int j0 = warp; j0 < k; j0 += 32) {  // centres j0, j0+8, j0+16, j0+24
-      double s[4] = {0.0, 0.0, 0.0, 0.0};
-      for (int t = lane; t < d; t += 32) {
-        const double xv = (double)xr[t];
+  for (int g0 = blockIdx.x * KX_ROWS; g0 < used; g0 += gridDim.x * KX_ROWS) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < KX_ROWS * dpad; i += 256) {
+      const int r = i / dpad, t = i - r * dpad;
+      xs[i] = (g0 + r < used && t < d) ? (double)X[(int64_t)idx[g0 + r] * ld + t] : 0.0;
+    }
+    __syncthreads();
+    double xn[4], best[4];
+    int bi[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int j = j0 + 8 * u;
-          if (j < k) {
-            const double df = xv - C64[(size_t)j * d + t];
-            s[u] = fma(df, df, s[u]);
+    for (int u = 0; u < 4; ++u) {
+      double a = 0.0;
+      for (int t = lane; t < dpad; t += 32) a = fma(xs[(4 * warp + u) * dpad + t], xs[(4 * warp + u) * dpad + t], a);
+      xn[u] = warp_sum(a);
+      best[u] = INFINITY;
+      bi[u] = 0x7fffffff;
+    }
+    for (int jb = 0; jb < k; jb += 32) {
+      double s[4] = {0.0, 0.0, 0.0, 0.0};
+      for (int t0 = 0; t0 < dpad; t0 += 32) {
+        __syncthreads();
+#pragma unroll
+        for (int e = threadIdx.x; e < 1024; e += 256) {
+          const int c = e >> 5, tt = e & 31;
+          cs[c * 34 + tt] = (jb + c < k && t0 + tt < d) ? C64[(size_t)(jb + c) * d + t0 + tt] : 0.0;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int tt = 0; tt < 32; tt += 2) {
+          const double2 cv = *reinterpret_cast<const double2*>(cs + lane * 34 + tt);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const double2 xv = *reinterpret_cast<const double2*>(xs + (4 * warp + u) * dpad + t0 + tt);
+            s[u] = fma(xv.x, cv.x, s[u]);
+            s[u] = fma(xv.y, cv.y, s[u]);
           }
         }
       }
+      const int j = jb + lane;
+      if (j < k) {
+        const double cn = CN64[j];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int j = j0 + 8 * u;
-        const double v = warp_sum(s[u]);
-        if (j < k && (v < best || (v == best && j < bi))) {
-          best = v;
-          bi = j;
+        for (int u = 0; u < 4; ++u) {
+          const double v = fmax(xn[u] + cn - 2.0 * s[u], 0.0);
+          if (v < best[u]) {  // a thread sees its centres in ascending order: strict '<' keeps the lowest index
+            best[u] = v;
+            bi[u] = j;
+          }
         }
       }
     }
-    if (lane == 0) {
-      s_best[warp] = best;
-      s_bi[warp] = bi;
-    }
-    __syncthreads();
-    best = s_best[0];
-    bi = s_bi[0];
 #pragma unroll
-    for (int w = 1; w < 8; ++w) {  // lowest index wins exact ties (findClosest order)
-      const double v = s_best[w];
-      const int j = s_bi[w];
-      if (v < best || (v == best && j < bi)) {
-        best = v;
-        bi = j;
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, best[u], o);
+        const int oj = __shfl_xor_sync(0xffffffffu, bi[u], o);
+        if (ov < best[u] || (ov == best[u] && oj < bi[u])) {
+          best[u] = ov;
+          bi[u] = oj;
+        }
       }
-    }
-    __syncthreads();
-    if (threadIdx.x == 0 && labels) labels[r] = bi;
-    if (accumulate) {
-      for (int t = threadIdx.x; t < d; t += 256) atomicAdd(payload + (size_t)bi * d + t, (double)xr[t]);
-      if (threadIdx.x == 0) {
-        atomicAdd(payload + (size_t)k * d + bi, 1.0);
-        cost += best;
-        rows += 1.0;
+      const int li = g0 + 4 * warp + u;
+      if (li < used) {
+        const int64_t r = idx[li];
+        if (lane == 0 && labels) labels[r] = bi[u];
+        if (accumulate) {
+          for (int t = lane; t < d; t += 32)
+            atomicAdd(payload + (size_t)bi[u] * d + t, xs[(4 * warp + u) * dpad + t]);
+          if (lane == 0) {
+            atomicAdd(payload + (size_t)k * d + bi[u], 1.0);
+            cost += best[u];
+            rows += 1.0;
+          }
+        }
       }
     }
   }
-  if (accumulate && threadIdx.x == 0 && rows > 0.0) {
+  if (accumulate && lane == 0 && rows > 0.0) {
     atomicAdd(payload + (size_t)k * d + k, cost);
     atomicAdd(payload + (size_t)k * d + k + 1, rows);
   }
@@ -285,12 +347,19 @@ __global__ void __launch_bounds__(256) km_exact_kernel(const float* __restrict__
 
 int km_exact_rows(const float* X, int64_t ld, int d, const void* prep, int k, void* acc, int32_t* labels,
                   const int* count, const int32_t* idx, int cap, bool accumulate, cudaStream_t stream) {
+  B2F_REQUIRE(d <= KX_MAX_D, "exact re-check: d = %d above %d", d, KX_MAX_D);
   KmPrepLayout P = km_prep_layout(k, d);
   const double* c64 = reinterpret_cast<const double*>(static_cast<const char*>(prep) + P.off_c64);
+  const double* cn64 = reinterpret_cast<const double*>(static_cast<const char*>(prep) + P.off_cn64);
   double* payload = nullptr;
   if (accumulate) payload = reinterpret_cast<double*>(static_cast<char*>(acc) + km_acc_layout(k, d).off_payload);
-  km_exact_kernel<<<b2f_sm_count() * 8, 256, 0, stream>>>(X, ld, d, c64, k, payload, labels, count, idx, cap,
-                                                          accumulate ? 1 : 0);
+  const int dpad = (d + 31) & ~31;
+  const size_t smem = ((size_t)KX_ROWS * dpad + 32 * 34) * sizeof(double);
+  B2F_CUDA(cudaFuncSetAttribute(km_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = (cap + KX_ROWS - 1) / KX_ROWS;
+  if (grid > b2f_sm_count() * 4) grid = b2f_sm_count() * 4;
+  km_exact_kernel<<<grid, 256, smem, stream>>>(X, ld, d, c64, cn64, k, payload, labels, count, idx, cap,
+                                               accumulate ? 1 : 0);
   B2F_LAUNCH_CHECK();
   return B2F_OK;
 }
@@ -367,7 +436,12 @@ extern "C" int b2f_kmeans_prepare(const double* centers, int k, int d, void* pre
       centers, k, d, reinterpret_cast<float*>(p + L.off_c32), reinterpret_cast<float*>(p + L.off_ch),
       reinterpret_cast<float*>(p + L.off_cl), reinterpret_cast<float*>(p + L.off_cn),
       reinterpret_cast<double*>(p + L.off_c64), reinterpret_cast<__nv_bfloat16*>(p + L.off_cb1),
-      reinterpret_cast<__nv_bfloat16*>(p + L.off_cb2), reinterpret_cast<unsigned int*>(p + L.off_misc));
+      reinterpret_cast<__nv_bfloat16*>(p + L.off_cb2), reinterpret_cast<double*>(p + L.off_cn64),
+      reinterpret_cast<unsigned int*>(p + L.off_misc));
+  B2F_LAUNCH_CHECK();
+  km_prepare_h16_kernel<<<(int)(((size_t)k * d + 255) / 256 > 1184 ? 1184 : ((size_t)k * d + 255) / 256), 256, 0,
+                          b2f_cs(stream)>>>(centers, k, d, reinterpret_cast<__half*>(p + L.off_ch16),
+                                            reinterpret_cast<float*>(p + L.off_misc));
   B2F_LAUNCH_CHECK();
   return B2F_OK;
 }
@@ -414,13 +488,16 @@ extern "C" int b2f_kmeans_step_ws(const float* X, int64_t n, int d, int64_t ld, 
                                   b2f_stream_t stream) {
   B2F_REQUIRE(X && prep && acc, "b2f_kmeans_step_ws: null pointer");
   B2F_REQUIRE(n >= 0 && d > 0 && k > 0 && ld >= d && ld % 4 == 0, "b2f_kmeans_step_ws: need ld >= d, ld %% 4 == 0");
-  if (algo == B2F_KM_AUTO && !w && labels && ws && km_tcb_supported(k, d, ld)) algo = B2F_KM_TCB;
-  if (algo != B2F_KM_TCB) return b2f_kmeans_step(X, n, d, ld, w, prep, k, acc, labels, algo, stream);
+  if (algo == B2F_KM_AUTO && !w && labels && ws && km_tcb_supported(k, d, ld)) algo = B2F_KM_TCH;
+  if (algo != B2F_KM_TCB && algo != B2F_KM_TCH)
+    return b2f_kmeans_step(X, n, d, ld, w, prep, k, acc, labels, algo, stream);
   B2F_REQUIRE(!w, "b2f_kmeans_step_ws: the tensor-core path does not take row weights");
-  B2F_REQUIRE(km_tcb_supported(k, d, ld), "b2f_kmeans_step_ws: B2F_KM_TCB needs d in {64, 128} and k %% 128 == 0");
+  B2F_REQUIRE(km_tcb_supported(k, d, ld),
+              "b2f_kmeans_step_ws: B2F_KM_TCB / B2F_KM_TCH need d in {64, 128} and k %% 128 == 0");
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_kmeans_step_ws: X must be 16-byte aligned");
   if (n == 0) return B2F_OK;
-  return km_tcb_step(X, n, d, ld, prep, k, acc, labels, ws, ws_bytes, true, b2f_cs(stream));
+  return km_tcb_step(X, n, d, ld, prep, k, acc, labels, ws, ws_bytes, true,
+                     algo == B2F_KM_TCH ? KM_FILTER_FP16 : KM_FILTER_BF16X3, b2f_cs(stream));
 }
 
 extern "C" int b2f_kmeans_fold(void* acc, int k, int d, b2f_stream_t stream) {

@@ -23,6 +23,7 @@
 //   warps 12-15 split: fp32 row -> x1, x2 bf16 pairs -> tcgen05.st into tensor memory; row norms
 //   warps 16-19 accumulate certain rows (16-byte vector reductions), cost, counts
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include "tc_common.cuh"
 
@@ -32,10 +33,12 @@ constexpr uint32_t TB_TMEM_COLS = 512;  // [0,256) two accumulators | [256,320) 
 constexpr uint32_t TB_A1 = 256, TB_A2 = 320;
 constexpr int TB_THREADS = 640;
 constexpr int TB_EPI_THREADS = 256;  // two epilogue warps per TMEM lane quarter, 64 columns of a tile each
-constexpr int TB_STAGE_BYTES = 2 * CHUNK_BYTES;  // c1 atom + c2 atom (128 centres x 64 bf16 each)
-// kind::f16, bf16 inputs, fp32 accumulate, A and B K-major, M = 128, N = TN
+// stage = 128 centres x 64 k: c1 atom + c2 atom (bf16x3), or the single scaled fp16 atom (fp16 filter)
+template <int MODE> __host__ __device__ constexpr int tb_stage_bytes() { return MODE == KM_FILTER_FP16 ? CHUNK_BYTES : 2 * CHUNK_BYTES; }
+// kind::f16, fp32 accumulate, A and B K-major, M = 128, N = TN; input format 1 = bf16, 0 = fp16
 constexpr uint32_t IDESC_BF16 =
     (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+constexpr uint32_t IDESC_FP16 = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 
 struct SmemB {
   uint64_t xs_full[4], xs_empty[4];  // fp32 staging, per 32-float chunk
@@ -59,24 +62,28 @@ struct TcbWs {  // header of the caller-provided workspace
   int pad[61];
 };
 
-__device__ __forceinline__ void tc_mma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t accumulate) {
+__device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
-      "r"(tmem_a), "l"(bdesc), "r"(IDESC_BF16), "r"(accumulate)
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
 
 }  // namespace
 
+template <int MODE>
 __global__ void __launch_bounds__(TB_THREADS, 1)
     km_tcb_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c1,
                   const __grid_constant__ CUtensorMap map_c2, const float* __restrict__ X, int64_t n, int d,
-                  int64_t ld, const float* __restrict__ cn, const float* __restrict__ cmax_ptr, float kappa2, int k,
-                  int nstages, double* __restrict__ payload, float* __restrict__ rep,
+                  int64_t ld, const float* __restrict__ cn, const float* __restrict__ misc, float kappa2,
+                  float kappa0, int k, int nstages, double* __restrict__ payload, float* __restrict__ rep,
                   unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels, int accumulate,
                   TcbWs* __restrict__ ws, int32_t* __restrict__ amb_idx, int cap) {
+  constexpr int TB_STAGE_BYTES = tb_stage_bytes<MODE>();
+  constexpr bool H16 = MODE == KM_FILTER_FP16;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   if (smem_u32(smem_raw) & 1023u) __trap();
   const int KC = d / 32;  // fp32 staging chunks
@@ -143,7 +150,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             mbar_expect_tx(&sm->b_full[s], (uint32_t)TB_STAGE_BYTES);
             uint8_t* dst = stages + (size_t)s * TB_STAGE_BYTES;
             tma_load_2d(dst, &map_c1, a * 64, nt * TN, &sm->b_full[s]);
-            tma_load_2d(dst + CHUNK_BYTES, &map_c2, a * 64, nt * TN, &sm->b_full[s]);
+            if (!H16) tma_load_2d(dst + CHUNK_BYTES, &map_c2, a * 64, nt * TN, &sm->b_full[s]);
             if (++s == (uint32_t)nstages) {
               s = 0;
               ph ^= 1;
@@ -153,7 +160,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer: one batch (12 * KA instructions) per centre tile =====================
+    // ===================== MMA issuer: one batch (12 * KA or 4 * KA instructions) per centre tile ============
     const uint64_t desc_fixed = (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
     const uint32_t st_a = smem_u32(stages) >> 4;
     const uint32_t chunk16 = CHUNK_BYTES >> 4, stage16 = (uint32_t)TB_STAGE_BYTES >> 4;
@@ -186,10 +193,14 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
               const uint64_t b1 = desc_fixed | (uint64_t)(st_a + st_idx[a] * stage16);
               const uint64_t b2 = b1 + chunk16;
 #pragma unroll
-              for (int s = 0; s < 4; ++s) {  // 16 bf16 of k = 32 bytes = 2 descriptor units, 8 TMEM columns
-                tc_mma_bf16_ts(tmem_d, a1 + 8 * s, b1 + 2 * s, (a | s) ? 1u : 0u);
-                tc_mma_bf16_ts(tmem_d, a1 + 8 * s, b2 + 2 * s, 1u);
-                tc_mma_bf16_ts(tmem_d, a2 + 8 * s, b1 + 2 * s, 1u);
+              for (int s = 0; s < 4; ++s) {  // 16 halves of k = 32 bytes = 2 descriptor units, 8 TMEM columns
+                if (H16) {
+                  tc_mma_f16_ts(tmem_d, a1 + 8 * s, b1 + 2 * s, IDESC_FP16, (a | s) ? 1u : 0u);
+                } else {
+                  tc_mma_f16_ts(tmem_d, a1 + 8 * s, b1 + 2 * s, IDESC_BF16, (a | s) ? 1u : 0u);
+                  tc_mma_f16_ts(tmem_d, a1 + 8 * s, b2 + 2 * s, IDESC_BF16, 1u);
+                  tc_mma_f16_ts(tmem_d, a2 + 8 * s, b1 + 2 * s, IDESC_BF16, 1u);
+                }
               }
               tc_commit(&sm->b_empty[st_idx[a]]);
               if (nt == NT - 1) tc_commit(&sm->xa_empty[a]);
@@ -208,7 +219,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     const int half = (warp - 4) >> 2;
     const int row_in_tile = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-    const float cmax = *cmax_ptr;
+    const float cmax = misc[KM_MISC_CMAX];
+    // fp16 filter: the accumulator holds S^2 * (x . -2c); the extra term of the bound covers fp16 underflow
+    const float inv = H16 ? misc[KM_MISC_INV_SCALE2] : 1.f;
+    const float tau0 = H16 ? kappa0 / misc[KM_MISC_SCALE] : 0.f;
     uint32_t it = 0, acc_it = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       float b1a = INFINITY, b2a = INFINITY, b1b = INFINITY, b2b = INFINITY;
@@ -229,10 +243,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
             const float4 cv = __ldg(cn4 + j4);
-            const float s0 = __uint_as_float(v[c & 1][j4 * 4 + 0]) + cv.x;
-            const float s1 = __uint_as_float(v[c & 1][j4 * 4 + 1]) + cv.y;
-            const float s2 = __uint_as_float(v[c & 1][j4 * 4 + 2]) + cv.z;
-            const float s3 = __uint_as_float(v[c & 1][j4 * 4 + 3]) + cv.w;
+            const float s0 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 0]), inv, cv.x);  // inv is a power of two
+            const float s1 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 1]), inv, cv.y);
+            const float s2 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 2]), inv, cv.z);
+            const float s3 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 3]), inv, cv.w);
             const int j = jbase + j4 * 4;
             i1a = (s0 < b1a) ? j : i1a;       b2a = fminf(b2a, fmaxf(b1a, s0)); b1a = fminf(b1a, s0);
             i1b = (s1 < b1b) ? j + 1 : i1b;   b2b = fminf(b2b, fmaxf(b1b, s1)); b1b = fminf(b1b, s1);
@@ -267,7 +281,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
       mbar_wait(&sm->n_full[nb], (it >> 1) & 1);
       const float xn = sm->xnorm2[nb][row_in_tile];
-      const float tau2 = kappa2 * sqrtf(xn) * cmax;  // 2 * tau for this row
+      const float xl = sqrtf(xn);  // xn = +inf marks a row whose scaled entries overflow fp16: never certain
+      const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax);  // 2 * tau for this row
       const int64_t row = tile * TM + row_in_tile;
       const bool live = row < n;
       const bool certain = (b2 - b1) > tau2;  // false for NaN as well
@@ -287,18 +302,23 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         const int ab = it & 1;
         mbar_wait(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1);
         sm->lab[ab][row_in_tile] = (live && certain) ? i1 : -1;
-        sm->score[ab][row_in_tile] = fmaxf(xn + b1, 0.f);  // squared distance to the chosen centre
+        // bf16x3: squared distance to the chosen centre.  fp16: ||x||^2 only -- the remaining part of the cost,
+        // sum_j (n_j ||c_j||^2 - 2 c_j . S_j), is added exactly from the sums (tcb_cost_terms_kernel)
+        sm->score[ab][row_in_tile] = H16 ? xn : fmaxf(xn + b1, 0.f);
         mbar_arrive(&sm->a_full[ab]);
       }
     }
   } else if (warp >= 12 && warp < 16) {
-    // ===================== split: fp32 row -> (x1, x2) bf16 pairs in tensor memory; row norms ==========
+    // ===================== split: fp32 row -> (x1, x2) bf16 pairs, or S * x as fp16 pairs, in tensor memory;
+    // row norms
     const int w4 = warp - 12;
     const int r = w4 * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
+    const float S = H16 ? misc[KM_MISC_SCALE] : 1.f;
+    const float xlim = 65504.f / S;  // entries beyond this overflow fp16 after scaling
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      float xn = 0.f;
+      float xn = 0.f, amax = 0.f;
       for (int a = 0; a < KA; ++a) {
         uint32_t p1[32], p2[32];
 #pragma unroll
@@ -310,6 +330,14 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           for (int p = 0; p < 8; ++p) {
             const float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
             xn = fmaf(v.x, v.x, xn); xn = fmaf(v.y, v.y, xn); xn = fmaf(v.z, v.z, xn); xn = fmaf(v.w, v.w, xn);
+            if (H16) {
+              amax = fmaxf(fmaxf(amax, fabsf(v.x)), fmaxf(fabsf(v.y), fmaxf(fabsf(v.z), fabsf(v.w))));
+              const __half2 g01 = __floats2half2_rn(v.x * S, v.y * S);  // .x -> low 16 bits = even k
+              const __half2 g23 = __floats2half2_rn(v.z * S, v.w * S);
+              p1[h * 16 + p * 2 + 0] = *reinterpret_cast<const uint32_t*>(&g01);
+              p1[h * 16 + p * 2 + 1] = *reinterpret_cast<const uint32_t*>(&g23);
+              continue;
+            }
             const __nv_bfloat162 h01 = __floats2bfloat162_rn(v.x, v.y);  // .x -> low 16 bits = even k
             const __nv_bfloat162 h23 = __floats2bfloat162_rn(v.z, v.w);
             const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
@@ -325,14 +353,14 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         mbar_wait(&sm->xa_empty[a], (it & 1) ^ 1);  // previous tile's MMAs are done with this TMEM atom
         tc_fence_after();
         tmem_st32(tmem_base + lane_addr + TB_A1 + a * 32, p1);
-        tmem_st32(tmem_base + lane_addr + TB_A2 + a * 32, p2);
+        if (!H16) tmem_st32(tmem_base + lane_addr + TB_A2 + a * 32, p2);
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(&sm->xa_full[a]);
       }
       // the epilogue of tile `it` reads the norm only after the last centre tile: the slot written two
       // tiles ago has long been consumed (its epilogue precedes the MMAs this split had to wait for)
-      sm->xnorm2[it & 1][r] = xn;
+      sm->xnorm2[it & 1][r] = (H16 && !(amax <= xlim)) ? INFINITY : xn;
       mbar_arrive(&sm->n_full[it & 1]);
     }
   } else if (warp >= 16) {
@@ -411,6 +439,35 @@ __global__ void tcb_scatter_kernel(const TcbWs* __restrict__ ws, const int32_t* 
     labels[amb_idx[i]] = lab_amb[i];
 }
 
+// Centre-dependent part of the cost of everything accumulated so far:
+//   F = sum_j ( n_j ||c_j||^2 - 2 c_j . S_j ),   S_j / n_j = fp64 payload + fp32 replicas / integer counts.
+// The fp16 filter kernel adds only sum ||x||^2 of its certain rows to the cost; the exact remainder of their cost is
+// F(after the kernel) - F(before it), whatever the accumulator held on entry.  One warp per centre, fp64.
+__global__ void tcb_cost_terms_kernel(double* __restrict__ payload, const float* __restrict__ rep,
+                                      const unsigned long long* __restrict__ cnt, const double* __restrict__ c64,
+                                      int k, int d, double sign) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  const size_t kd = (size_t)k * d;
+  double f = 0.0;
+  for (int j = warp; j < k; j += nwarps) {
+    double dot = 0.0, nn = 0.0;
+    for (int c = lane; c < d; c += 32) {
+      const size_t i = (size_t)j * d + c;
+      double sum = payload[i];
+#pragma unroll
+      for (int rp = 0; rp < KM_REPLICAS; ++rp) sum += (double)rep[rp * kd + i];
+      const double cv = c64[i];
+      dot += cv * sum;
+      nn += cv * cv;
+    }
+    dot = warp_sum(dot);
+    nn = warp_sum(nn);
+    f += (payload[kd + j] + (double)cnt[j]) * nn - 2.0 * dot;
+  }
+  if (lane == 0 && f != 0.0) atomicAdd(payload + kd + k, sign * f);
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -430,7 +487,7 @@ static TcbWsLayout tcb_ws_layout(int cap, int d) {
   return L;
 }
 static int tcb_cap_for_rows(int64_t n) {
-  int64_t c = (n / 16 + TM - 1) / TM * TM;  // room for 1 row in 16
+  int64_t c = (n / 8 + TM - 1) / TM * TM;  // room for 1 row in 8
   if (c < 4096) c = 4096;
   if (c > (1 << 30)) c = 1 << 30;
   return (int)c;
@@ -444,9 +501,9 @@ static int tcb_cap_from_bytes(size_t bytes, int d) {
   return (int)c;
 }
 
-static int km_tcb_stages(int d) {
+static int km_tcb_stages(int d, int filter) {
   const int left = 227 * 1024 - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES;
-  int s = left / TB_STAGE_BYTES;
+  int s = left / (filter == KM_FILTER_FP16 ? tb_stage_bytes<KM_FILTER_FP16>() : tb_stage_bytes<KM_FILTER_BF16X3>());
   return s > 8 ? 8 : s;
 }
 
@@ -454,7 +511,7 @@ bool km_tcb_supported(int k, int d, int64_t ld) {
   if (d != 64 && d != 128) return false;  // whole 64-k atoms, X hi/lo pairs fit the tensor memory budget
   if (k % TN != 0 || k < TN) return false;
   if (ld % 4 != 0) return false;
-  return km_tcb_stages(d) >= 2 * (d / 64) && km_tc_supported(k, d, ld);
+  return km_tcb_stages(d, KM_FILTER_BF16X3) >= 2 * (d / 64) && km_tc_supported(k, d, ld);
 }
 
 size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
@@ -463,13 +520,13 @@ size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
 }
 
 int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
-                void* ws, size_t ws_bytes, bool accumulate, cudaStream_t stream) {
-  B2F_REQUIRE(labels, "b2f_kmeans (bf16x3 path): a labels buffer is required");
-  B2F_REQUIRE(ws, "b2f_kmeans (bf16x3 path): a workspace is required (b2f_kmeans_ws_bytes)");
-  B2F_REQUIRE(n < (1ll << 31), "b2f_kmeans (bf16x3 path): at most 2^31-1 rows per call");
-  B2F_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "b2f_kmeans (bf16x3 path): workspace must be 256-byte aligned");
+                void* ws, size_t ws_bytes, bool accumulate, int filter, cudaStream_t stream) {
+  B2F_REQUIRE(labels, "b2f_kmeans (filter path): a labels buffer is required");
+  B2F_REQUIRE(ws, "b2f_kmeans (filter path): a workspace is required (b2f_kmeans_ws_bytes)");
+  B2F_REQUIRE(n < (1ll << 31), "b2f_kmeans (filter path): at most 2^31-1 rows per call");
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "b2f_kmeans (filter path): workspace must be 256-byte aligned");
   const int cap = tcb_cap_from_bytes(ws_bytes, d);
-  B2F_REQUIRE(cap >= TM, "b2f_kmeans (bf16x3 path): workspace of %zu bytes is too small", ws_bytes);
+  B2F_REQUIRE(cap >= TM, "b2f_kmeans (filter path): workspace of %zu bytes is too small", ws_bytes);
   TcbWsLayout W = tcb_ws_layout(cap, d);
   char* wp = static_cast<char*>(ws);
   TcbWs* hdr = reinterpret_cast<TcbWs*>(wp);
@@ -477,15 +534,19 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   int32_t* lab_amb = reinterpret_cast<int32_t*>(wp + W.off_lab);
   int32_t* idx2 = reinterpret_cast<int32_t*>(wp + W.off_idx2);
   float* Xamb = reinterpret_cast<float*>(wp + W.off_x);
-  const int nstages = km_tcb_stages(d);
+  const bool h16 = filter == KM_FILTER_FP16;
+  const int nstages = km_tcb_stages(d, filter);
   KmPrepLayout P = km_prep_layout(k, d);
   const char* pp = static_cast<const char*>(prep);
   const float* cn = reinterpret_cast<const float*>(pp + P.off_cn);
-  const float* cmax = reinterpret_cast<const float*>(pp + P.off_misc);
+  const float* misc = reinterpret_cast<const float*>(pp + P.off_misc);
+  const float* cmax = misc + KM_MISC_CMAX;
   CUtensorMap mx, m1, m2;
   int rc;
   if ((rc = make_map_f32(&mx, X, (uint64_t)n, (uint64_t)d, (uint64_t)ld)) != B2F_OK) return rc;
-  if ((rc = make_map_bf16(&m1, pp + P.off_cb1, (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
+  // (the fp16 plane goes through a 16-bit map as well: the copy does not interpret the elements)
+  if ((rc = make_map_bf16(&m1, pp + (h16 ? P.off_ch16 : P.off_cb1), (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK)
+    return rc;
   if ((rc = make_map_bf16(&m2, pp + P.off_cb2, (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
   double* payload = nullptr;
   float* rep = nullptr;
@@ -499,18 +560,38 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   }
   // 2 * tau = kappa2 * ||x|| * max||c||:  dropped products 3 u^2 (u = 2^-8) on c' = -2c, i.e. 6 * 2^-16,
   // plus fp32 accumulation / rounding slack (3 d + 16) * 2^-23 on |x||c'| = 2 |x||c|
-  const float kappa = 6.0f * 1.02f / 65536.0f + 2.0f * (3.0f * d + 16.0f) / 8388608.0f;
+  // fp16 filter (one product, x and -2c each rounded once, u = 2^-11):  |error| <= (2u + u^2) |x||c'| = 4.01 u |x||c|
+  // plus the accumulation slack for d products; operands below the fp16 normal range carry an absolute error of
+  // eta = 2^-25 / S per entry instead:  + sqrt(d) eta (|c'| + |x|)  ->  kappa0 (divided by S in the kernel)
+  const float kappa = h16 ? 4.0f * 1.01f / 2048.0f + 2.0f * (d + 16.0f) / 8388608.0f
+                          : 6.0f * 1.02f / 65536.0f + 2.0f * (3.0f * d + 16.0f) / 8388608.0f;
   const float kappa2 = 2.0f * kappa;
+  const float kappa0 = h16 ? 2.0f * 1.01f * sqrtf((float)d) / 33554432.0f : 0.f;
   const int dbg = getenv("B2F_TC_DBG") ? atoi(getenv("B2F_TC_DBG")) : 0;  // dev knob, results invalid when set
   const bool acc_main = accumulate && !(dbg & 4);
   B2F_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcbWs), stream));
-  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * TB_STAGE_BYTES + sizeof(SmemB) + 64;
+  const size_t stage_bytes = h16 ? tb_stage_bytes<KM_FILTER_FP16>() : tb_stage_bytes<KM_FILTER_BF16X3>();
+  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * stage_bytes + sizeof(SmemB) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
-  B2F_CUDA(cudaFuncSetAttribute(km_tcb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  km_tcb_kernel<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, cn, cmax, kappa2, k, nstages, payload, rep,
-                                                    cnt, labels, acc_main ? 1 : 0, hdr, amb_idx, cap);
+  if (h16) {
+    const double* c64 = reinterpret_cast<const double*>(pp + P.off_c64);
+    const int cgrid = (k + 7) / 8;
+    if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, -1.0);
+    B2F_CUDA(cudaFuncSetAttribute(km_tcb_kernel<KM_FILTER_FP16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    km_tcb_kernel<KM_FILTER_FP16><<<grid, TB_THREADS, smem, stream>>>(mx, m1, m1, X, n, d, ld, cn, misc, kappa2, kappa0,
+                                                                      k, nstages, payload, rep, cnt, labels,
+                                                                      acc_main ? 1 : 0, hdr, amb_idx, cap);
+    B2F_LAUNCH_CHECK();
+    if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, 1.0);
+  } else {
+    B2F_CUDA(cudaFuncSetAttribute(km_tcb_kernel<KM_FILTER_BF16X3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+    km_tcb_kernel<KM_FILTER_BF16X3><<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, cn, misc, kappa2,
+                                                                        kappa0, k, nstages, payload, rep, cnt, labels,
+                                                                        acc_main ? 1 : 0, hdr, amb_idx, cap);
+  }
   B2F_LAUNCH_CHECK();
   tcb_gather_kernel<<<b2f_sm_count() * 4, 256, 0, stream>>>(X, ld, d, hdr, amb_idx, Xamb, cap);
   B2F_LAUNCH_CHECK();

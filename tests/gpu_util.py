@@ -34,13 +34,13 @@ def kmeans_state(C, k, d):
 
 
 def kmeans_step_raw(X, n, d, ld, C, algo, w=None, want_labels=True, ws_bytes=None, info=None):
-    """One b2f_kmeans_step (or _step_ws for B2F_KM_TCB) + fold.
+    """One b2f_kmeans_step (or _step_ws for B2F_KM_TCB / B2F_KM_TCH) + fold.
     Returns labels, sums[k,d], counts[k], cost, nrows (host)."""
     L = N.lib()
     k = C.shape[0]
     cen, prep, acc = kmeans_state(C, k, d)
     labels = torch.full((n,), -1, dtype=torch.int32, device=dev()) if want_labels else None
-    if algo == N.KM_TCB:
+    if algo in (N.KM_TCB, N.KM_TCH):
         wsb = int(L.b2f_kmeans_ws_bytes(n, k, d)) if ws_bytes is None else ws_bytes
         ws = torch.zeros(wsb, dtype=torch.uint8, device=dev())
         N.check(L.b2f_kmeans_step_ws(N.ptr(X), n, d, ld, N.ptr(w), N.ptr(prep), k, N.ptr(acc), N.ptr(labels),

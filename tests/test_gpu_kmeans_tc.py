@@ -115,17 +115,22 @@ TCB_SHAPES = [(128, 64, 128), (1000, 64, 128), (5000, 128, 256), (4099, 128, 102
               (30000, 64, 256)]
 
 
+FILTERS = ["TCB", "TCH"]  # bf16x3 filter (three MMAs per product) / fp16 filter (one MMA, scaled operands)
+
+
+@pytest.mark.parametrize("filt", FILTERS)
 @pytest.mark.parametrize("n,d,k", TCB_SHAPES)
-def test_tcb_step_matches_oracle(n, d, k):
-    """bf16x3 filter pass + 3xTF32 re-check of uncertain rows: same bar as the 3xTF32 kernel."""
+def test_tcb_step_matches_oracle(n, d, k, filt):
+    """Low-precision filter pass + 3xTF32 re-check of uncertain rows: same bar as the 3xTF32 kernel."""
     N, G = _imports()
+    algo = getattr(N, "KM_" + filt)
     Xh = synth.mixture(n, 0, d, SEED, k, 2.0)
     rng = np.random.default_rng(n + d + k)
     C = Xh[rng.choice(n, size=k, replace=False)].astype(np.float64) if n >= k else \
         synth.mixture_centers(d, SEED, k, 2.0).astype(np.float64)
     X, _, ld = G.upload_matrix(Xh)
     info = {}
-    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCB, info=info)
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, algo, info=info)
     ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
     bad = (labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)
     assert not bad.any(), "%d label mismatches outside the 1e-6 gap band" % bad.sum()
@@ -136,14 +141,17 @@ def test_tcb_step_matches_oracle(n, d, k):
         np.testing.assert_array_equal(counts, rcounts)
         scale = np.abs(Xh).astype(np.float64).sum(axis=0).max() / k + 1.0
         np.testing.assert_allclose(sums, rsums, rtol=1e-5, atol=1e-6 * scale)
-    # certain rows carry the bf16x3 score error (|err| <= tau ~ 0.1 here, zero mean): it only shows when
-    # the true cost is ~0 (rows sitting on their centres, n == k case)
+    # bf16x3: certain rows carry the score error (|err| <= tau ~ 0.1 here, zero mean); fp16: the cost comes from
+    # sum ||x||^2 and the accumulated sums, i.e. a difference of large terms.  Either only shows when the true
+    # cost is ~0 (rows sitting on their centres, n == k case)
     assert cost == pytest.approx(rcost, rel=1e-5, abs=2e-2 * n)
 
 
-def test_tcb_uncertain_rows_are_rechecked_and_overflow_is_visible():
+@pytest.mark.parametrize("filt", FILTERS)
+def test_tcb_uncertain_rows_are_rechecked_and_overflow_is_visible(filt):
     """Two centres almost on top of each other make most of their rows uncertain."""
     N, G = _imports()
+    algo = getattr(N, "KM_" + filt)
     n, d, k = 20000, 128, 128
     Xh = synth.mixture(n, 0, d, SEED, 4, 2.0)
     C = synth.mixture_centers(d, SEED, k, 2.0).astype(np.float64)
@@ -151,19 +159,44 @@ def test_tcb_uncertain_rows_are_rechecked_and_overflow_is_visible():
     X, _, ld = G.upload_matrix(Xh)
     info = {}
     big = int(N.lib().b2f_kmeans_ws_bytes(16 * n, k, d))  # room for every row on the re-check list
-    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCB, ws_bytes=big, info=info)
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, algo, ws_bytes=big, info=info)
     ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
     assert info["uncertain"] > n // 8 and nrows == n
     assert not ((labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)).any()
     # a workspace with room for 128 rows only: the excess is dropped and the row count shows it
     small = 256 + 4 * 1024 + 128 * (12 + 4 * d) + 4096
     info2 = {}
-    _, _, _, _, nrows2 = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCB, ws_bytes=small, info=info2)
+    _, _, _, _, nrows2 = G.kmeans_step_raw(X, n, d, ld, C, algo, ws_bytes=small, info=info2)
     assert info2["uncertain"] == info["uncertain"] and info2["rechecked"] < info2["uncertain"]
     assert nrows2 == n - (info2["uncertain"] - info2["rechecked"])
 
 
-def test_tcb_fit_per_iteration_parity_and_fallback():
+@pytest.mark.parametrize("scale", [1e-6, 1.0, 3e5])
+def test_tch_operand_scaling_and_fp16_overflow_rows(scale):
+    """The fp16 filter scales its operands by a power of two taken from the centres; rows with entries far above
+    the centres' range overflow fp16 and must come back through the re-check with the right label."""
+    N, G = _imports()
+    n, d, k = 6000, 128, 128
+    Xh = synth.mixture(n, 0, d, SEED, k, 2.0)
+    C = synth.mixture_centers(d, SEED, k, 2.0).astype(np.float64) * scale
+    Xh = (Xh * np.float32(scale)).astype(np.float32)
+    Xh[17, 5] = np.float32(1e4 * scale)   # beyond 65504 / S for these centres
+    Xh[4000, :] *= np.float32(500.0)
+    Xh[123, :] = 0.0
+    X, _, ld = G.upload_matrix(Xh)
+    info = {}
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCH, info=info)
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
+    assert nrows == n and counts.sum() == n and 2 <= info["uncertain"] < n // 4
+    assert not ((labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)).any()
+    _, rcost, rsums, rcounts = oracle.kmeans_step(Xh.astype(np.float64), C)
+    assert cost == pytest.approx(rcost, rel=1e-5)
+    if (labels == ref_lab).all():
+        np.testing.assert_array_equal(counts, rcounts)
+
+
+@pytest.mark.parametrize("filt", FILTERS)
+def test_tcb_fit_per_iteration_parity_and_fallback(filt):
     N, G = _imports()
     from b200fit.clustering import CudaLloydEngine, lloyd
     from b200fit.dist import Comm
@@ -173,7 +206,7 @@ def test_tcb_fit_per_iteration_parity_and_fallback():
     Xh = synth.mixture(n, 0, d, SEED, k, 2.0)
     C0 = Xh[np.random.default_rng(2).choice(n, size=k, replace=False)].astype(np.float64)
     ref = oracle.kmeans_lloyd(Xh.astype(np.float64), C0, max_iter=iters, tol=0.0)
-    eng = CudaLloydEngine(pack_columns([Xh]), k, algo=N.KM_TCB)
+    eng = CudaLloydEngine(pack_columns([Xh]), k, algo=getattr(N, "KM_" + filt))
     eng.set_centers(C0)
     it, costs, conv, payload = lloyd(eng, Comm(), iters, 0.0)
     sc = np.abs(ref["centers"]).max()

@@ -17,6 +17,7 @@ ap.add_argument("--k", type=int, default=1024)
 ap.add_argument("--algo", type=int, default=2)
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--predict", action="store_true", help="labels only (no accumulation)")
+ap.add_argument("--lloyd", type=int, default=0, help="run this many real Lloyd iterations first (centres move)")
 a = ap.parse_args()
 L = N.lib()
 dev = torch.device("cuda", 0)
@@ -30,6 +31,16 @@ N.check(L.b2f_kmeans_prepare(N.ptr(C), a.k, a.d, N.ptr(prep), N.stream_ptr()), "
 lab = torch.empty(a.n, dtype=torch.int32, device=dev)
 wsb = int(L.b2f_kmeans_ws_bytes(a.n, a.k, a.d))
 ws = torch.zeros(wsb, dtype=torch.uint8, device=dev)
+status = torch.zeros(2, dtype=torch.int32, device=dev)
+status_f64 = torch.zeros(2, dtype=torch.float64, device=dev)
+for i in range(a.lloyd):
+    N.check(L.b2f_kmeans_acc_zero(N.ptr(acc), a.k, a.d, N.stream_ptr()), "zero")
+    N.check(L.b2f_kmeans_step_ws(N.ptr(X), a.n, a.d, a.d, None, N.ptr(prep), a.k, N.ptr(acc), N.ptr(lab),
+                                 N.ptr(ws), wsb, 0, N.stream_ptr()), "step_ws")
+    N.check(L.b2f_kmeans_fold(N.ptr(acc), a.k, a.d, N.stream_ptr()), "fold")
+    N.check(L.b2f_kmeans_finalize(N.ptr(acc), a.k, a.d, 0.0, N.ptr(C), N.ptr(status), N.ptr(status_f64),
+                                  N.stream_ptr()), "finalize")
+    N.check(L.b2f_kmeans_prepare(N.ptr(C), a.k, a.d, N.ptr(prep), N.stream_ptr()), "prep")
 ts = []
 for i in range(a.reps + 2):
     N.check(L.b2f_kmeans_acc_zero(N.ptr(acc), a.k, a.d, N.stream_ptr()), "zero")
@@ -38,7 +49,7 @@ for i in range(a.reps + 2):
     if a.predict:
         N.check(L.b2f_kmeans_predict(N.ptr(X), a.n, a.d, a.d, N.ptr(prep), a.k, N.ptr(lab), None, a.algo,
                                      N.stream_ptr()), "predict")
-    elif a.algo == 4:
+    elif a.algo in (4, 5):
         N.check(L.b2f_kmeans_step_ws(N.ptr(X), a.n, a.d, a.d, None, N.ptr(prep), a.k, N.ptr(acc), N.ptr(lab),
                                      N.ptr(ws), wsb, a.algo, N.stream_ptr()), "step_ws")
     else:
@@ -50,7 +61,7 @@ for i in range(a.reps + 2):
         ts.append(e0.elapsed_time(e1))
 ms = sum(ts) / len(ts)
 fl = 2.0 * a.n * a.k * a.d
-if a.algo == 4:
+if a.algo in (4, 5):
     print("uncertain rows: %s of %d" % (ws[:12].view(torch.int32).cpu().tolist(), a.n))
 print("algo %d n=%d d=%d k=%d: %.3f ms  %.1f TFLOP/s algorithmic  (%.1f ms per 100M rows)" %
       (a.algo, a.n, a.d, a.k, ms, fl / ms / 1e9, ms * 1e8 / a.n))
