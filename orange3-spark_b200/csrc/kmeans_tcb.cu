@@ -25,14 +25,33 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
+#include <cstdio>
+#include <vector>
+
 #include "tc_common.cuh"
 
 namespace {
 
-constexpr uint32_t TB_TMEM_COLS = 512;  // [0,256) two accumulators | [256,320) x1 | [320,384) x2 (bf16 pairs)
-constexpr uint32_t TB_A1 = 256, TB_A2 = 320;
+// [0,256) two accumulators | [256,384) x1, two row tiles of 64 columns |
+// [384,512) bf16x3: x2, likewise; fp16: a third accumulator
+constexpr uint32_t TB_TMEM_COLS = 512;
+constexpr uint32_t TB_A1 = 256, TB_A2 = 384, TB_ABUF = 64;
+__device__ __forceinline__ uint32_t tb_acc_col(uint32_t buf) { return buf < 2 ? buf * TN : 384u; }
 constexpr int TB_THREADS = 640;
-constexpr int TB_EPI_THREADS = 256;  // two epilogue warps per TMEM lane quarter, 64 columns of a tile each
+#ifndef TB_REG_CTRL
+// what the epilogue warpgroups gain, (EPI - 96) * 256, must be given back first by the others:
+// (96 - CTRL) * 128 + (96 - FIN) * 128  (the pool is per CTA)
+#define TB_REG_CTRL 48
+#define TB_REG_FIN 80
+#define TB_REG_EPI 128
+#endif
+// dev tracing (B2F_TC_TRACE=<file>): block 0 stamps clock64() at the hand-offs of its first TR_TILES row tiles
+constexpr int TR_TILES = 64, TR_SLOTS = 32, TR_ROLES = 12;  // mma | 8 epilogue warps | split | finish | B producer
+#define TR(role, slot)                                                                      \
+  do {                                                                                      \
+    if (TRACE && blockIdx.x == 0 && lane == 0 && it < (uint32_t)TR_TILES)                   \
+      trace[((role) * TR_TILES + it) * TR_SLOTS + (slot)] = (unsigned long long)clock64();  \
+  } while (0)
 // stage = 128 centres x 64 k: c1 atom + c2 atom (bf16x3), or the single scaled fp16 atom (fp16 filter)
 template <int MODE> __host__ __device__ constexpr int tb_stage_bytes() { return MODE == KM_FILTER_FP16 ? CHUNK_BYTES : 2 * CHUNK_BYTES; }
 // kind::f16, fp32 accumulate, A and B K-major, M = 128, N = TN; input format 1 = bf16, 0 = fp16
@@ -40,19 +59,24 @@ constexpr uint32_t IDESC_BF16 =
     (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 constexpr uint32_t IDESC_FP16 = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 
+// warp roles.  The scheduler prefers the higher warp ids, so the warps whose latency everybody else waits on (MMA
+// issuer, producers) get the top ids and the throughput-bound epilogue warps the bottom ones.
+constexpr int W_EPI0 = 0;    // warps 0-7   epilogue
+constexpr int W_SPLIT0 = 8;  // warps 8-11  split
+constexpr int W_FIN0 = 12;   // warps 12-15 finish
+constexpr int W_XPROD = 16, W_MMA = 17, W_BPROD = 18, W_ALLOC = 19;
+
 struct SmemB {
   uint64_t xs_full[4], xs_empty[4];  // fp32 staging, per 32-float chunk
-  uint64_t xa_full[2], xa_empty[2];  // TMEM operand, per 64-k atom
+  uint64_t xa_full[4], xa_empty[4];  // TMEM operand, per (row-tile buffer, 64-k atom)
   uint64_t b_full[8], b_empty[8];
-  uint64_t t_full[2], t_empty[2];
-  uint64_t a_full[2], a_empty[2];    // epilogue -> accumulate hand-off
-  uint64_t n_full[2];                // split -> epilogue: squared row norms of a tile
+  uint64_t t_full[3], t_empty[3];    // accumulators
+  uint64_t a_full[2], a_empty[2];    // epilogue -> finish hand-off
+  uint64_t n_full[4], n_empty[4];    // split -> finish: squared row norms of a tile
   uint32_t tmem_base;
-  int lab[2][TM];                    // certain label, or -1 for a row sent to the re-check list
-  float score[2][TM];
-  float xnorm2[2][TM];
-  float p_b1[2][TM], p_b2[2][TM];    // partial results of the second epilogue warp of each quarter
-  int p_i1[2][TM];
+  float xnorm2[4][TM];
+  float p_b1[2][2][TM], p_b2[2][2][TM];  // [slot][epilogue warp of the lane quarter][row]: best, second best
+  int p_i1[2][2][TM];                    // index of the best
 };
 
 struct TcbWs {  // header of the caller-provided workspace
@@ -74,20 +98,22 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, 
 
 }  // namespace
 
-template <int MODE>
+template <int MODE, bool TRACE>
 __global__ void __launch_bounds__(TB_THREADS, 1)
     km_tcb_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c1,
                   const __grid_constant__ CUtensorMap map_c2, const float* __restrict__ X, int64_t n, int d,
                   int64_t ld, const float* __restrict__ cn, const float* __restrict__ misc, float kappa2,
                   float kappa0, int k, int nstages, double* __restrict__ payload, float* __restrict__ rep,
                   unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels, int accumulate,
-                  TcbWs* __restrict__ ws, int32_t* __restrict__ amb_idx, int cap) {
+                  TcbWs* __restrict__ ws, int32_t* __restrict__ amb_idx, int cap,
+                  unsigned long long* __restrict__ trace) {
   constexpr int TB_STAGE_BYTES = tb_stage_bytes<MODE>();
   constexpr bool H16 = MODE == KM_FILTER_FP16;
+  constexpr uint32_t NBUF = H16 ? 3 : 2;  // accumulator buffers in tensor memory
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   if (smem_u32(smem_raw) & 1023u) __trap();
   const int KC = d / 32;  // fp32 staging chunks
-  const int KA = d / 64;  // 64-k atoms of the bf16 operands
+  const int KA = d / 64;  // 64-k atoms of the 16-bit operands
   uint8_t* xs = smem_raw;
   uint8_t* stages = xs + (size_t)KC * CHUNK_BYTES;
   SmemB* sm = reinterpret_cast<SmemB*>(stages + (size_t)nstages * TB_STAGE_BYTES);
@@ -100,15 +126,18 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     for (int c = 0; c < 4; ++c) {
       mbar_init(&sm->xs_full[c], 1);
       mbar_init(&sm->xs_empty[c], EPI_THREADS);
-    }
-    for (int c = 0; c < 2; ++c) {
       mbar_init(&sm->xa_full[c], EPI_THREADS);
       mbar_init(&sm->xa_empty[c], 1);
-      mbar_init(&sm->t_full[c], 1);
-      mbar_init(&sm->t_empty[c], TB_EPI_THREADS);
-      mbar_init(&sm->a_full[c], EPI_THREADS);
-      mbar_init(&sm->a_empty[c], EPI_THREADS);
       mbar_init(&sm->n_full[c], EPI_THREADS);
+      mbar_init(&sm->n_empty[c], EPI_THREADS);
+    }
+    for (int c = 0; c < 3; ++c) {
+      mbar_init(&sm->t_full[c], 1);
+      mbar_init(&sm->t_empty[c], EPI_THREADS);
+    }
+    for (int c = 0; c < 2; ++c) {
+      mbar_init(&sm->a_full[c], 2 * EPI_THREADS);
+      mbar_init(&sm->a_empty[c], EPI_THREADS);
     }
     for (int s = 0; s < 8; ++s) {
       mbar_init(&sm->b_full[s], 1);
@@ -116,7 +145,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 3) {
+  if (warp == W_ALLOC) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm->tmem_base)),
                  "r"(TB_TMEM_COLS)
                  : "memory");
@@ -127,26 +156,34 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   tc_fence_after();
   const uint32_t tmem_base = sm->tmem_base;
 
-  if (warp == 0) {
+  // Register budget (launch: 640 threads x 96).  The epilogue keeps 64 accumulator values in flight per thread; at
+  // 96 registers it spills its loop state to local memory, and with all of L1 carved out for shared memory each
+  // reload is an L2 round trip (~1000 idle cycles per centre tile in the hand-off trace).  The control and finish warpgroups
+  // give registers back, the two epilogue warpgroups take them (setmaxnreg works per 4-warp group).
+  if (warp >= W_XPROD) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_CTRL));
+  }
+  if (warp == W_XPROD) {
     // ===================== X producer =====================
     if (lane == 0) {
       uint32_t it = 0;
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         for (int kc = 0; kc < KC; ++kc) {
-          mbar_wait(&sm->xs_empty[kc], (it & 1) ^ 1);
+          mbar_wait_ns(&sm->xs_empty[kc], (it & 1) ^ 1, 128);
           mbar_expect_tx(&sm->xs_full[kc], (uint32_t)CHUNK_BYTES);
           tma_load_2d(xs + (size_t)kc * CHUNK_BYTES, &map_x, kc * 32, (int)(tile * TM), &sm->xs_full[kc]);
         }
       }
     }
-  } else if (warp == 2) {
+  } else if (warp == W_BPROD) {
     // ===================== B producer =====================
     if (lane == 0) {
-      uint32_t s = 0, ph = 0;
-      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      uint32_t s = 0, ph = 0, it = 0;
+      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         for (int nt = 0; nt < NT; ++nt) {
           for (int a = 0; a < KA; ++a) {
-            mbar_wait(&sm->b_empty[s], ph ^ 1);
+            mbar_wait_ns(&sm->b_empty[s], ph ^ 1, 64);
+            if (nt < 8) TR(11, 2 * nt + a);
             mbar_expect_tx(&sm->b_full[s], (uint32_t)TB_STAGE_BYTES);
             uint8_t* dst = stages + (size_t)s * TB_STAGE_BYTES;
             tma_load_2d(dst, &map_c1, a * 64, nt * TN, &sm->b_full[s]);
@@ -159,23 +196,25 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == W_MMA) {
     // ===================== MMA issuer: one batch (12 * KA or 4 * KA instructions) per centre tile ============
     const uint64_t desc_fixed = (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
     const uint32_t st_a = smem_u32(stages) >> 4;
     const uint32_t chunk16 = CHUNK_BYTES >> 4, stage16 = (uint32_t)TB_STAGE_BYTES >> 4;
-    uint32_t it = 0, acc_it = 0, stage = 0, bphase = 0;
+    uint32_t it = 0, buf = 0, round = 0, stage = 0, bphase = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      for (int nt = 0; nt < NT; ++nt, ++acc_it) {
-        const uint32_t buf = acc_it & 1;
-        mbar_wait(&sm->t_empty[buf], ((acc_it >> 1) & 1) ^ 1);
-        const uint32_t tmem_d = tmem_base + buf * TN;
+      const uint32_t xb = it & 1;  // row-tile buffer of the TMEM operand
+      for (int nt = 0; nt < NT; ++nt) {
+        if (nt < 8) TR(0, 3 * nt);
+        const uint32_t tmem_d = tmem_base + tb_acc_col(buf);
         uint32_t st_idx[2];
+        // operands first (they are ready long before), the accumulator last: its release by the epilogue is the
+        // event the issue has to follow as closely as possible
 #pragma unroll
         for (int a = 0; a < 2; ++a) {
           if (a < KA) {
-            if (nt == 0) mbar_wait(&sm->xa_full[a], it & 1);
-            mbar_wait(&sm->b_full[stage], bphase);
+            if (nt == 0) mbar_wait_ns(&sm->xa_full[xb * 2 + a], (it >> 1) & 1, 20);
+            mbar_wait_ns(&sm->b_full[stage], bphase, 20);
             st_idx[a] = stage;
             if (++stage == (uint32_t)nstages) {
               stage = 0;
@@ -183,13 +222,16 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             }
           }
         }
+        if (nt < 8) TR(0, 3 * nt + 1);
+        mbar_wait_ns(&sm->t_empty[buf], round ^ 1, 20);
         tc_fence_after();
+        if (nt < 8) TR(0, 24 + nt);
         if (elect_one()) {
 #pragma unroll
           for (int a = 0; a < 2; ++a) {
             if (a < KA) {
-              const uint32_t a1 = tmem_base + TB_A1 + a * 32;  // 32 columns = 64 bf16 of k per atom
-              const uint32_t a2 = tmem_base + TB_A2 + a * 32;
+              const uint32_t a1 = tmem_base + TB_A1 + xb * TB_ABUF + a * 32;  // 32 columns = 64 halves of k per atom
+              const uint32_t a2 = tmem_base + TB_A2 + xb * TB_ABUF + a * 32;
               const uint64_t b1 = desc_fixed | (uint64_t)(st_a + st_idx[a] * stage16);
               const uint64_t b2 = b1 + chunk16;
 #pragma unroll
@@ -203,43 +245,56 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
                 }
               }
               tc_commit(&sm->b_empty[st_idx[a]]);
-              if (nt == NT - 1) tc_commit(&sm->xa_empty[a]);
+              if (nt == NT - 1) tc_commit(&sm->xa_empty[xb * 2 + a]);
             }
           }
           tc_commit(&sm->t_full[buf]);
         }
         __syncwarp();
+        if (nt < 8) TR(0, 3 * nt + 2);
+        if (++buf == NBUF) {
+          buf = 0;
+          round ^= 1;
+        }
       }
     }
-  } else if (warp >= 4 && warp < 12) {
-    // ===================== epilogue: best / second best per row, certainty test =====================
-    // Two warps share a TMEM lane quarter; warp `half` scans columns [64*half, 64*half + 64) of every
-    // accumulator tile (two resident warps per scheduler hide the min/max dependency latency).
+  } else if (warp < W_SPLIT0) {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(TB_REG_EPI));
+    // ===================== epilogue: best / second best per row =====================
+    // Two warps share a TMEM lane quarter; warp `half` takes every other centre tile, whole, so the two warps of a
+    // scheduler run out of step and each one's TMEM-load and barrier latencies are covered by the other's arithmetic.
     const int q = warp & 3;
-    const int half = (warp - 4) >> 2;
+    const uint32_t half = (uint32_t)(warp - W_EPI0) >> 2;
     const int row_in_tile = q * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
-    const float cmax = misc[KM_MISC_CMAX];
-    // fp16 filter: the accumulator holds S^2 * (x . -2c); the extra term of the bound covers fp16 underflow
+    // fp16 filter: the accumulator holds S^2 * (x . -2c)
     const float inv = H16 ? misc[KM_MISC_INV_SCALE2] : 1.f;
-    const float tau0 = H16 ? kappa0 / misc[KM_MISC_SCALE] : 0.f;
-    uint32_t it = 0, acc_it = 0;
+    uint32_t it = 0, buf = 0, round = 0, par = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       float b1a = INFINITY, b2a = INFINITY, b1b = INFINITY, b2b = INFINITY;
       int i1a = 0, i1b = 1;
-      for (int nt = 0; nt < NT; ++nt, ++acc_it) {
-        const int buf = acc_it & 1;
-        mbar_wait(&sm->t_full[buf], (acc_it >> 1) & 1);
+      for (int nt = 0; nt < NT; ++nt) {
+        const uint32_t cbuf = buf, cround = round;
+        const bool mine = par == half;
+        par ^= 1;
+        if (++buf == NBUF) {
+          buf = 0;
+          round ^= 1;
+        }
+        if (!mine) continue;
+        if (nt < 8) TR(1 + warp, 3 * nt);
+        mbar_wait_ns(&sm->t_full[cbuf], cround, 20);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + lane_addr + (uint32_t)(buf * TN + half * 64);
+        if (nt < 8) TR(1 + warp, 3 * nt + 1);
+        const uint32_t taddr = tmem_base + lane_addr + tb_acc_col(cbuf);
         uint32_t v[2][32];
         tmem_ld32(taddr, v[0]);
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
+        for (int c = 0; c < 4; ++c) {
           tmem_ld_wait();
-          if (c + 1 < 2) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
-          const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + half * 64 + c * 32);
-          const int jbase = nt * TN + half * 64 + c * 32;
+          if (c + 1 < 4) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+          const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + c * 32);
+          const int jbase = nt * TN + c * 32;
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
             const float4 cv = __ldg(cn4 + j4);
@@ -255,63 +310,23 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           }
         }
         tc_fence_before();
-        mbar_arrive(&sm->t_empty[buf]);
+        mbar_arrive(&sm->t_empty[cbuf]);
+        if (nt < 8) TR(1 + warp, 3 * nt + 2);
       }
       // merge this thread's two chains: smaller score wins, equal scores keep the lower centre index
-      bool a_wins = (b1a < b1b) || (b1a == b1b && i1a < i1b);
-      float b1 = a_wins ? b1a : b1b;
-      int i1 = a_wins ? i1a : i1b;
-      float b2 = fminf(fmaxf(b1a, b1b), fminf(b2a, b2b));  // second smallest over both chains
-      // merge the two column halves (the upper-half warp hands its partial result over in smem)
-      const int nb = it & 1;
-      if (half == 1) {
-        sm->p_b1[nb][row_in_tile] = b1;
-        sm->p_b2[nb][row_in_tile] = b2;
-        sm->p_i1[nb][row_in_tile] = i1;
-      }
-      asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
-      if (half == 1) continue;
-      {
-        const float ob1 = sm->p_b1[nb][row_in_tile], ob2 = sm->p_b2[nb][row_in_tile];
-        const int oi1 = sm->p_i1[nb][row_in_tile];
-        const bool mine = (b1 < ob1) || (b1 == ob1 && i1 < oi1);
-        b2 = fminf(fmaxf(b1, ob1), fminf(b2, ob2));
-        i1 = mine ? i1 : oi1;
-        b1 = mine ? b1 : ob1;
-      }
-      mbar_wait(&sm->n_full[nb], (it >> 1) & 1);
-      const float xn = sm->xnorm2[nb][row_in_tile];
-      const float xl = sqrtf(xn);  // xn = +inf marks a row whose scaled entries overflow fp16: never certain
-      const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax);  // 2 * tau for this row
-      const int64_t row = tile * TM + row_in_tile;
-      const bool live = row < n;
-      const bool certain = (b2 - b1) > tau2;  // false for NaN as well
-      if (live) labels[row] = i1;             // provisional for uncertain rows (rewritten by the re-check)
-      // append uncertain rows to the re-check list (one atomic per warp)
-      const unsigned m = __ballot_sync(0xffffffffu, live && !certain);
-      if (m) {
-        int base = 0;
-        if (lane == (__ffs(m) - 1)) base = atomicAdd(&ws->count, __popc(m));
-        base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-        if (live && !certain) {
-          const int slot = base + __popc(m & ((1u << lane) - 1));
-          if (slot < cap) amb_idx[slot] = (int32_t)(row & 0x7fffffff);
-        }
-      }
-      if (accumulate) {
-        const int ab = it & 1;
-        mbar_wait(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1);
-        sm->lab[ab][row_in_tile] = (live && certain) ? i1 : -1;
-        // bf16x3: squared distance to the chosen centre.  fp16: ||x||^2 only -- the remaining part of the cost,
-        // sum_j (n_j ||c_j||^2 - 2 c_j . S_j), is added exactly from the sums (tcb_cost_terms_kernel)
-        sm->score[ab][row_in_tile] = H16 ? xn : fmaxf(xn + b1, 0.f);
-        mbar_arrive(&sm->a_full[ab]);
-      }
+      const bool a_wins = (b1a < b1b) || (b1a == b1b && i1a < i1b);
+      const uint32_t ab = it & 1;
+      mbar_wait_ns(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1, 64);
+      sm->p_b1[ab][half][row_in_tile] = a_wins ? b1a : b1b;
+      sm->p_i1[ab][half][row_in_tile] = a_wins ? i1a : i1b;
+      sm->p_b2[ab][half][row_in_tile] = fminf(fmaxf(b1a, b1b), fminf(b2a, b2b));  // second smallest over both chains
+      mbar_arrive(&sm->a_full[ab]);
+      TR(1 + warp, 31);
     }
-  } else if (warp >= 12 && warp < 16) {
+  } else if (warp < W_FIN0) {
     // ===================== split: fp32 row -> (x1, x2) bf16 pairs, or S * x as fp16 pairs, in tensor memory;
     // row norms
-    const int w4 = warp - 12;
+    const int w4 = warp - W_SPLIT0;
     const int r = w4 * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
     const float S = H16 ? misc[KM_MISC_SCALE] : 1.f;
@@ -319,12 +334,13 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       float xn = 0.f, amax = 0.f;
+      if (w4 == 0) TR(9, 0);
       for (int a = 0; a < KA; ++a) {
         uint32_t p1[32], p2[32];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int kc = 2 * a + h;
-          mbar_wait(&sm->xs_full[kc], it & 1);
+          mbar_wait_ns(&sm->xs_full[kc], it & 1, 64);
           const uint8_t* src = xs + (size_t)kc * CHUNK_BYTES + (size_t)r * 128;
 #pragma unroll
           for (int p = 0; p < 8; ++p) {
@@ -350,54 +366,100 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           }
           mbar_arrive(&sm->xs_empty[kc]);
         }
-        mbar_wait(&sm->xa_empty[a], (it & 1) ^ 1);  // previous tile's MMAs are done with this TMEM atom
+        const uint32_t xb = it & 1;
+        if (w4 == 0) TR(9, 1 + 3 * a);
+        mbar_wait_ns(&sm->xa_empty[xb * 2 + a], ((it >> 1) & 1) ^ 1, 128);  // MMAs of tile it-2 are done with this atom
         tc_fence_after();
-        tmem_st32(tmem_base + lane_addr + TB_A1 + a * 32, p1);
-        if (!H16) tmem_st32(tmem_base + lane_addr + TB_A2 + a * 32, p2);
+        if (w4 == 0) TR(9, 2 + 3 * a);
+        tmem_st32(tmem_base + lane_addr + TB_A1 + xb * TB_ABUF + a * 32, p1);
+        if (!H16) tmem_st32(tmem_base + lane_addr + TB_A2 + xb * TB_ABUF + a * 32, p2);
         tmem_st_wait();
         tc_fence_before();
-        mbar_arrive(&sm->xa_full[a]);
+        mbar_arrive(&sm->xa_full[xb * 2 + a]);
+        if (w4 == 0) TR(9, 3 + 3 * a);
       }
-      // the epilogue of tile `it` reads the norm only after the last centre tile: the slot written two
-      // tiles ago has long been consumed (its epilogue precedes the MMAs this split had to wait for)
-      sm->xnorm2[it & 1][r] = (H16 && !(amax <= xlim)) ? INFINITY : xn;
-      mbar_arrive(&sm->n_full[it & 1]);
+      // four slots: the split warps run up to two tiles ahead of the MMAs, which run ahead of the finish warps
+      mbar_wait_ns(&sm->n_empty[it & 3], ((it >> 2) & 1) ^ 1, 128);
+      sm->xnorm2[it & 3][r] = (H16 && !(amax <= xlim)) ? INFINITY : xn;
+      mbar_arrive(&sm->n_full[it & 3]);
     }
-  } else if (warp >= 16) {
-    // ===================== accumulate certain rows =====================
-    const int w4 = warp - 16;
+  } else if (warp < W_XPROD) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_FIN));
+    // ===================== finish: merge the two epilogue warps' results, certainty test, labels, re-check list,
+    // accumulation of certain rows (16-byte vector reductions), cost, counts.  Thread == row.
+    const int w4 = warp - W_FIN0;
+    const int row_in_tile = w4 * 32 + lane;
+    const float cmax = misc[KM_MISC_CMAX];
+    const float tau0 = H16 ? kappa0 / misc[KM_MISC_SCALE] : 0.f;  // fp16 underflow term of the bound
     double cost = 0.0;
     unsigned long long nrows = 0;
     float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
     uint32_t it = 0;
-    if (accumulate) {
-      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const int ab = it & 1;
-        mbar_wait(&sm->a_full[ab], (it >> 1) & 1);
-        const int my_lab = sm->lab[ab][w4 * 32 + lane];
-        const float my_sc = sm->score[ab][w4 * 32 + lane];
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const uint32_t ab = it & 1;
+      if (w4 == 0) TR(10, 0);
+      mbar_wait_ns(&sm->a_full[ab], (it >> 1) & 1, 128);
+      if (w4 == 0) TR(10, 1);
+      float b1 = sm->p_b1[ab][0][row_in_tile], b2 = sm->p_b2[ab][0][row_in_tile];
+      int i1 = sm->p_i1[ab][0][row_in_tile];
+      {
+        const float ob1 = sm->p_b1[ab][1][row_in_tile], ob2 = sm->p_b2[ab][1][row_in_tile];
+        const int oi1 = sm->p_i1[ab][1][row_in_tile];
         mbar_arrive(&sm->a_empty[ab]);
-        const int64_t r0 = tile * TM + w4 * 32;
-        for (int g = 0; g < 32; g += 8) {
-          float4 xv[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
-            xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (lbl >= 0 && lane * 4 < d) xv[u] = *reinterpret_cast<const float4*>(X + (r0 + g + u) * ld + lane * 4);
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
-            if (lbl >= 0 && lane * 4 < d) red_add_v4(myrep + (size_t)lbl * d + lane * 4, xv[u]);
-          }
-        }
-        if (my_lab >= 0) {
-          cost += (double)my_sc;
-          atomicAdd(cnt + my_lab, 1ull);
-          ++nrows;
+        const bool mine = (b1 < ob1) || (b1 == ob1 && i1 < oi1);
+        b2 = fminf(fmaxf(b1, ob1), fminf(b2, ob2));
+        i1 = mine ? i1 : oi1;
+        b1 = mine ? b1 : ob1;
+      }
+      mbar_wait_ns(&sm->n_full[it & 3], (it >> 2) & 1, 64);
+      const float xn = sm->xnorm2[it & 3][row_in_tile];
+      mbar_arrive(&sm->n_empty[it & 3]);
+      const float xl = sqrtf(xn);  // xn = +inf marks a row whose scaled entries overflow fp16: never certain
+      const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax);  // 2 * tau for this row
+      const int64_t row = tile * TM + row_in_tile;
+      const bool live = row < n;
+      const bool certain = (b2 - b1) > tau2;  // false for NaN as well
+      if (live) labels[row] = i1;             // provisional for uncertain rows (rewritten by the re-check)
+      // append uncertain rows to the re-check list (one atomic per warp)
+      const unsigned m = __ballot_sync(0xffffffffu, live && !certain);
+      if (m) {
+        int base = 0;
+        if (lane == (__ffs(m) - 1)) base = atomicAdd(&ws->count, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+        if (live && !certain) {
+          const int slot = base + __popc(m & ((1u << lane) - 1));
+          if (slot < cap) amb_idx[slot] = (int32_t)(row & 0x7fffffff);
         }
       }
+      if (w4 == 0) TR(10, 2);
+      if (!accumulate) continue;
+      const int my_lab = (live && certain) ? i1 : -1;
+      // bf16x3: squared distance to the chosen centre.  fp16: ||x||^2 only -- the remaining part of the cost,
+      // sum_j (n_j ||c_j||^2 - 2 c_j . S_j), is added exactly from the sums (tcb_cost_terms_kernel)
+      const float my_sc = H16 ? xn : fmaxf(xn + b1, 0.f);
+      const int64_t r0 = tile * TM + w4 * 32;
+      for (int g = 0; g < 32; g += 8) {
+        float4 xv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
+          xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (lbl >= 0 && lane * 4 < d) xv[u] = *reinterpret_cast<const float4*>(X + (r0 + g + u) * ld + lane * 4);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
+          if (lbl >= 0 && lane * 4 < d) red_add_v4(myrep + (size_t)lbl * d + lane * 4, xv[u]);
+        }
+      }
+      if (my_lab >= 0) {
+        cost += (double)my_sc;
+        atomicAdd(cnt + my_lab, 1ull);
+        ++nrows;
+      }
+      if (w4 == 0) TR(10, 3);
+    }
+    if (accumulate) {
       cost = warp_sum(cost);
       unsigned long long tot = nrows;
 #pragma unroll
@@ -410,7 +472,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 3) {
+  if (warp == W_ALLOC) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TB_TMEM_COLS)
                  : "memory");
   }
@@ -502,9 +564,13 @@ static int tcb_cap_from_bytes(size_t bytes, int d) {
 }
 
 static int km_tcb_stages(int d, int filter) {
-  const int left = 227 * 1024 - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES;
+  // fp16 filter: stay within the 196 KB shared-memory carve-out so that 32 KB of L1 remain for the ||c||^2 table,
+  // the row re-reads of the finish warps and the few spilled loop counters (else every one is an L2 round trip)
+  const int budget = (filter == KM_FILTER_FP16 ? 195 : 227) * 1024;
+  const int left = budget - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES;
   int s = left / (filter == KM_FILTER_FP16 ? tb_stage_bytes<KM_FILTER_FP16>() : tb_stage_bytes<KM_FILTER_BF16X3>());
-  return s > 8 ? 8 : s;
+  const int cap = getenv("B2F_TC_STAGES") ? atoi(getenv("B2F_TC_STAGES")) : 8;  // dev knob
+  return s > cap ? cap : s;
 }
 
 bool km_tcb_supported(int k, int d, int64_t ld) {
@@ -575,24 +641,40 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
+  unsigned long long* trace = nullptr;
+  const char* trace_path = getenv("B2F_TC_TRACE");  // dev knob: the only place this library allocates
+  const size_t trace_bytes = (size_t)TR_ROLES * TR_TILES * TR_SLOTS * sizeof(unsigned long long);
+  if (trace_path) {
+    B2F_CUDA(cudaMalloc(&trace, trace_bytes));
+    B2F_CUDA(cudaMemsetAsync(trace, 0, trace_bytes, stream));
+  }
   if (h16) {
     const double* c64 = reinterpret_cast<const double*>(pp + P.off_c64);
     const int cgrid = (k + 7) / 8;
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, -1.0);
-    B2F_CUDA(cudaFuncSetAttribute(km_tcb_kernel<KM_FILTER_FP16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    km_tcb_kernel<KM_FILTER_FP16><<<grid, TB_THREADS, smem, stream>>>(mx, m1, m1, X, n, d, ld, cn, misc, kappa2, kappa0,
-                                                                      k, nstages, payload, rep, cnt, labels,
-                                                                      acc_main ? 1 : 0, hdr, amb_idx, cap);
+    auto kern = trace ? km_tcb_kernel<KM_FILTER_FP16, true> : km_tcb_kernel<KM_FILTER_FP16, false>;
+    B2F_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m1, X, n, d, ld, cn, misc, kappa2, kappa0, k, nstages, payload, rep,
+                                             cnt, labels, acc_main ? 1 : 0, hdr, amb_idx, cap, trace);
     B2F_LAUNCH_CHECK();
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, 1.0);
   } else {
-    B2F_CUDA(cudaFuncSetAttribute(km_tcb_kernel<KM_FILTER_BF16X3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem));
-    km_tcb_kernel<KM_FILTER_BF16X3><<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, cn, misc, kappa2,
-                                                                        kappa0, k, nstages, payload, rep, cnt, labels,
-                                                                        acc_main ? 1 : 0, hdr, amb_idx, cap);
+    auto kern = trace ? km_tcb_kernel<KM_FILTER_BF16X3, true> : km_tcb_kernel<KM_FILTER_BF16X3, false>;
+    B2F_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, cn, misc, kappa2, kappa0, k, nstages, payload, rep,
+                                             cnt, labels, acc_main ? 1 : 0, hdr, amb_idx, cap, trace);
   }
   B2F_LAUNCH_CHECK();
+  if (trace) {
+    std::vector<unsigned long long> host(trace_bytes / sizeof(unsigned long long));
+    B2F_CUDA(cudaStreamSynchronize(stream));
+    B2F_CUDA(cudaMemcpy(host.data(), trace, trace_bytes, cudaMemcpyDeviceToHost));
+    B2F_CUDA(cudaFree(trace));
+    if (FILE* f = fopen(trace_path, "wb")) {
+      fwrite(host.data(), 1, trace_bytes, f);
+      fclose(f);
+    }
+  }
   tcb_gather_kernel<<<b2f_sm_count() * 4, 256, 0, stream>>>(X, ld, d, hdr, amb_idx, Xamb, cap);
   B2F_LAUNCH_CHECK();
   // 3xTF32 bound: dropped products 3 u^2 with u = 2^-11 on c' = -2c, plus 48 fp32 accumulation roundings

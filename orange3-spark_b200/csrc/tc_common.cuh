@@ -65,6 +65,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
   }
 }
+// Bounded wait that really sleeps between polls.  Measured (ncu source page of km_tcb_kernel): the suspend-time hint
+// of try_wait returns within a few cycles whenever ANY mbarrier of the CTA is signalled, so in a kernel with
+// constant barrier traffic mbar_wait() spins at ~7 instructions per 9 cycles and -- the scheduler prefers the
+// higher warp ids -- starves the warps doing the arithmetic.  Use this for every wait that has slack (a
+// double-buffered resource): the warp is not eligible for `ns` nanoseconds per failed poll.
+__device__ __forceinline__ void mbar_wait_ns(uint64_t* bar, uint32_t parity, uint32_t ns) {
+  if (mbar_try_wait(bar, parity)) return;
+  uint32_t tries = 0;
+  do {
+    __nanosleep(ns);
+    if (++tries > 20000000u) {
+      printf("b200fit: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  } while (!mbar_try_wait(bar, parity));
+}
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
