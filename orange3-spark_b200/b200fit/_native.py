@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200fit.so")
+# B2F_LIB_PATH: dev knob (kernel experiments built next to the product library), never a fallback
+LIB_PATH = os.environ.get("B2F_LIB_PATH") or os.path.join(_HERE, "libb200fit.so")
 
 # dtype codes (include/b200fit.h)
 F32, F64, I32, I64, U8 = 0, 1, 2, 3, 4

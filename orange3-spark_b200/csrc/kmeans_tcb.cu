@@ -37,6 +37,37 @@ namespace {
 constexpr uint32_t TB_TMEM_COLS = 512;
 constexpr uint32_t TB_A1 = 256, TB_A2 = 384, TB_ABUF = 64;
 __device__ __forceinline__ uint32_t tb_acc_col(uint32_t buf) { return buf < 2 ? buf * TN : 384u; }
+
+// fp16 filter epilogue works on INTEGER KEYS.  Per row, scores are scaled by a power of two `sc` such that
+// |score| * sc < 2^21 (|score| <= ||c||^2 + 2 ||x|| ||c||), and formed as  t = D * (inv * sc) + (cn_j * sc + 1.5 * 2^23):
+// the magic constant leaves round(score * sc) in the mantissa, so  key = (int)bits(t) * 129 + column  (wrapping
+// multiply; the window of possible products stays inside the int32 range) orders like (score, column) under SIGNED
+// compare, and best / second best need min/max only -- no compare + select for the index: 2.5 ALU-pipe operations
+// per score instead of 4.5; the multiply-adds, integer one included (hence 129, not a shift), run on the FMA pipe.
+// Each key is within 1 unit of score * sc; the certainty test pays for it with 2.5 units.
+constexpr float TB_MAGIC = 12582912.f;  // 1.5 * 2^23
+constexpr int TB_KEYMUL = 129;
+__device__ __forceinline__ int tb_key(float d, float arow, float cn, float sc, int col) {
+  return __float_as_int(fmaf(d, arow, fmaf(cn, sc, TB_MAGIC))) * TB_KEYMUL + col;
+}
+// value part of a key, relative to the key of score 0 (floor division of a possibly negative number)
+__device__ __forceinline__ int tb_key_value(int key) {
+  const int base = (int)(0x4B400000u * (uint32_t)TB_KEYMUL);  // wraps to a negative number
+  const int rel = key - base + (1 << 22) * TB_KEYMUL;         // >= 0: values span (-2^22, 2^22)
+  return rel / TB_KEYMUL;
+}
+__device__ __forceinline__ int tb_key_col(int key) {
+  const int base = (int)(0x4B400000u * (uint32_t)TB_KEYMUL);
+  const int rel = key - base + (1 << 22) * TB_KEYMUL;
+  return rel % TB_KEYMUL;
+}
+__device__ __forceinline__ float tb_row_scale(float xn, float cmax) {
+  const float R = fmaf(2.f * sqrtf(xn), cmax, cmax * cmax);  // +inf / NaN for rows flagged by the split warps
+  int e = (__float_as_int(R) >> 23) & 0xff;                  // R < 2^(e - 126)
+  e = 274 - e;                                               // biased exponent of 2^(21 - (e - 126))
+  e = max(1, min(254, e));
+  return __int_as_float(e << 23);
+}
 constexpr int TB_THREADS = 640;
 #ifndef TB_REG_CTRL
 // what the epilogue warpgroups gain, (EPI - 96) * 256, must be given back first by the others:
@@ -198,6 +229,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     }
   } else if (warp == W_MMA) {
     // ===================== MMA issuer: one batch (12 * KA or 4 * KA instructions) per centre tile ============
+    // ONE issuer on purpose.  The epilogue warps of a lane quarter take alternate centre tiles, and with three
+    // accumulators a buffer's consecutive uses go to different warps; their parity waits are only safe because
+    // centre tiles complete in issue order (a warp that has seen tile g+1 complete knows tile g has).  Two issuing
+    // warps break that order -- measured: no faster, and a stall-free epilogue (timing experiment) deadlocks.
     const uint64_t desc_fixed = (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
     const uint32_t st_a = smem_u32(stages) >> 4;
     const uint32_t chunk16 = CHUNK_BYTES >> 4, stage16 = (uint32_t)TB_STAGE_BYTES >> 4;
@@ -269,10 +304,21 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     // fp16 filter: the accumulator holds S^2 * (x . -2c)
     const float inv = H16 ? misc[KM_MISC_INV_SCALE2] : 1.f;
+    const float cmax_e = misc[KM_MISC_CMAX];
     uint32_t it = 0, buf = 0, round = 0, par = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       float b1a = INFINITY, b2a = INFINITY, b1b = INFINITY, b2b = INFINITY;
       int i1a = 0, i1b = 1;
+      // integer-key path (fp16 filter): running best / second best keys and the centre tile of the best
+      int B1 = 0x7fffffff, B2 = 0x7fffffff;
+      int T1 = 0;
+      float sc = 1.f, arow = 1.f;
+      if (H16) {
+        // the split warps finished this row tile before its first MMA could start: the norms are there
+        mbar_wait_ns(&sm->n_full[it & 3], (it >> 2) & 1, 32);
+        sc = tb_row_scale(sm->xnorm2[it & 3][row_in_tile], cmax_e);
+        arow = inv * sc;
+      }
       for (int nt = 0; nt < NT; ++nt) {
         const uint32_t cbuf = buf, cround = round;
         const bool mine = par == half;
@@ -289,6 +335,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         const uint32_t taddr = tmem_base + lane_addr + tb_acc_col(cbuf);
         uint32_t v[2][32];
         tmem_ld32(taddr, v[0]);
+        int k1a = 0x7fffffff, k2a = 0x7fffffff, k1b = 0x7fffffff, k2b = 0x7fffffff;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           tmem_ld_wait();
@@ -297,7 +344,27 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           const int jbase = nt * TN + c * 32;
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
+#ifdef TB_EXP_NOCN  // timing experiment: results invalid
+            const float4 cv = make_float4(1.f, 2.f, 3.f, 4.f);
+#else
             const float4 cv = __ldg(cn4 + j4);
+#endif
+#ifdef TB_EXP_NOMATH  // timing experiment: results invalid
+            if (j4 > 0) continue;
+#endif
+            if (H16) {
+              const int col = c * 32 + j4 * 4;
+              const int q0 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 0]), arow, cv.x, sc, col);
+              const int q1 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 1]), arow, cv.y, sc, col + 1);
+              const int q2 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 2]), arow, cv.z, sc, col + 2);
+              const int q3 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 3]), arow, cv.w, sc, col + 3);
+              const int loa = min(q0, q1), hia = max(q0, q1), lob = min(q2, q3), hib = max(q2, q3);
+              k2a = min(k2a, min(hia, max(k1a, loa)));
+              k1a = min(k1a, loa);
+              k2b = min(k2b, min(hib, max(k1b, lob)));
+              k1b = min(k1b, lob);
+              continue;
+            }
             const float s0 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 0]), inv, cv.x);  // inv is a power of two
             const float s1 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 1]), inv, cv.y);
             const float s2 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 2]), inv, cv.z);
@@ -311,15 +378,27 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         }
         tc_fence_before();
         mbar_arrive(&sm->t_empty[cbuf]);
+        if (H16) {  // fold the tile's two chains into the running pair; an earlier tile keeps equal keys
+          const int k1 = min(k1a, k1b), k2 = min(max(k1a, k1b), min(k2a, k2b));
+          B2 = min(max(B1, k1), min(B2, k2));
+          T1 = (k1 < B1) ? nt : T1;
+          B1 = min(B1, k1);
+        }
         if (nt < 8) TR(1 + warp, 3 * nt + 2);
       }
       // merge this thread's two chains: smaller score wins, equal scores keep the lower centre index
       const bool a_wins = (b1a < b1b) || (b1a == b1b && i1a < i1b);
       const uint32_t ab = it & 1;
       mbar_wait_ns(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1, 64);
-      sm->p_b1[ab][half][row_in_tile] = a_wins ? b1a : b1b;
-      sm->p_i1[ab][half][row_in_tile] = a_wins ? i1a : i1b;
-      sm->p_b2[ab][half][row_in_tile] = fminf(fmaxf(b1a, b1b), fminf(b2a, b2b));  // second smallest over both chains
+      if (H16) {
+        sm->p_b1[ab][half][row_in_tile] = __int_as_float(B1);
+        sm->p_b2[ab][half][row_in_tile] = __int_as_float(B2);
+        sm->p_i1[ab][half][row_in_tile] = T1 * TN + tb_key_col(B1);
+      } else {
+        sm->p_b1[ab][half][row_in_tile] = a_wins ? b1a : b1b;
+        sm->p_i1[ab][half][row_in_tile] = a_wins ? i1a : i1b;
+        sm->p_b2[ab][half][row_in_tile] = fminf(fmaxf(b1a, b1b), fminf(b2a, b2b));  // second smallest of both chains
+      }
       mbar_arrive(&sm->a_full[ab]);
       TR(1 + warp, 31);
     }
@@ -402,14 +481,25 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       if (w4 == 0) TR(10, 1);
       float b1 = sm->p_b1[ab][0][row_in_tile], b2 = sm->p_b2[ab][0][row_in_tile];
       int i1 = sm->p_i1[ab][0][row_in_tile];
+      float gap_units = 0.f;  // fp16 filter: second best - best in key units
       {
         const float ob1 = sm->p_b1[ab][1][row_in_tile], ob2 = sm->p_b2[ab][1][row_in_tile];
         const int oi1 = sm->p_i1[ab][1][row_in_tile];
         mbar_arrive(&sm->a_empty[ab]);
-        const bool mine = (b1 < ob1) || (b1 == ob1 && i1 < oi1);
-        b2 = fminf(fmaxf(b1, ob1), fminf(b2, ob2));
-        i1 = mine ? i1 : oi1;
-        b1 = mine ? b1 : ob1;
+        if (H16) {
+          const int B1 = __float_as_int(b1), B2 = __float_as_int(b2);
+          const int O1 = __float_as_int(ob1), O2 = __float_as_int(ob2);
+          const bool mine = (B1 < O1) || (B1 == O1 && i1 < oi1);
+          const int S2 = min(max(B1, O1), min(B2, O2)), S1 = min(B1, O1);
+          // (a warp without a centre tile hands over INT_MAX keys: at least one warp has real ones)
+          gap_units = (S2 == 0x7fffffff) ? 0.f : (float)(tb_key_value(S2) - tb_key_value(S1));
+          i1 = mine ? i1 : oi1;
+        } else {
+          const bool mine = (b1 < ob1) || (b1 == ob1 && i1 < oi1);
+          b2 = fminf(fmaxf(b1, ob1), fminf(b2, ob2));
+          i1 = mine ? i1 : oi1;
+          b1 = mine ? b1 : ob1;
+        }
       }
       mbar_wait_ns(&sm->n_full[it & 3], (it >> 2) & 1, 64);
       const float xn = sm->xnorm2[it & 3][row_in_tile];
@@ -418,7 +508,12 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax);  // 2 * tau for this row
       const int64_t row = tile * TM + row_in_tile;
       const bool live = row < n;
-      const bool certain = (b2 - b1) > tau2;  // false for NaN as well
+      bool certain = (b2 - b1) > tau2;  // false for NaN as well
+      if (H16) {
+        const float sc = tb_row_scale(xn, cmax);
+        const float arow = misc[KM_MISC_INV_SCALE2] * sc;
+        certain = gap_units > fmaf(tau2, sc, 2.5f) && arow > 0.f && arow < INFINITY;
+      }
       if (live) labels[row] = i1;             // provisional for uncertain rows (rewritten by the re-check)
       // append uncertain rows to the re-check list (one atomic per warp)
       const unsigned m = __ballot_sync(0xffffffffu, live && !certain);

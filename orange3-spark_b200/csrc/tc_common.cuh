@@ -76,7 +76,8 @@ __device__ __forceinline__ void mbar_wait_ns(uint64_t* bar, uint32_t parity, uin
   do {
     __nanosleep(ns);
     if (++tries > 20000000u) {
-      printf("b200fit: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+      printf("b200fit: mbarrier wait timed out (block %d thread %d, barrier at smem 0x%x, parity %u)\n", blockIdx.x,
+             threadIdx.x, smem_u32(bar), parity);
       __trap();
     }
   } while (!mbar_try_wait(bar, parity));

@@ -17,9 +17,8 @@ for w in range(8):
 ev = []
 for it in range(first, first + ntiles):
     for nt in range(8):
-        for r, lab in ((0, ("loop top", "operands ready", "issued")),):
-            for s in range(3):
-                ev.append((t[r, it, 3 * nt + s], "%-5s tile %d nt %d %s" % (names[r], it, nt, lab[s])))
+        for s, lab in enumerate(("loop top", "operands ready", "issued")):
+            ev.append((t[0, it, 3 * nt + s], "mma   tile %d nt %d %s" % (it, nt, lab)))
         ev.append((t[0, it, 24 + nt], "mma   tile %d nt %d accumulator free, issuing" % (it, nt)))
         for a in range(2):
             ev.append((t[11, it, 2 * nt + a], "bprod tile %d nt %d atom %d stage free, TMA issued" % (it, nt, a)))
@@ -38,8 +37,8 @@ ev = [(c - t0, s) for c, s in ev if c]
 ev.sort()
 for c, s in ev:
     print("%8d  %s" % (c, s))
-per_tile = np.diff(t[0, 8:TILES, 0]).mean()
-print("mean cycles per row tile (MMA warp, tiles 8..63): %.0f" % per_tile)
+per_tile = np.diff(t[1, 8:TILES, 31]).mean()
+print("mean cycles per row tile (epilogue warp 0 hand-offs, tiles 8..63): %.0f" % per_tile)
 for r in range(1, 9):
     busy = 0
     n = 0
@@ -51,6 +50,7 @@ for r in range(1, 9):
     print("%s: %.0f cycles per accumulator tile while holding it (%d tiles)" % (names[r], busy / max(n, 1), n))
     wait = sum(t[r, it, 3 * nt + 1] - t[r, it, 3 * nt] for it in range(8, TILES) for nt in range(8) if t[r, it, 3 * nt])
     print("%s: %.0f cycles waiting for t_full per accumulator tile" % (names[r], wait / max(n, 1)))
-mw = np.mean([t[0, it, 3 * nt + 1] - t[0, it, 3 * nt] for it in range(8, TILES) for nt in range(8)])
-mi = np.mean([t[0, it, 3 * nt + 2] - t[0, it, 3 * nt + 1] for it in range(8, TILES) for nt in range(8)])
+own = [(it, nt) for it in range(8, TILES) for nt in range(8) if t[0, it, 3 * nt]]
+mw = np.mean([t[0, it, 3 * nt + 1] - t[0, it, 3 * nt] for it, nt in own])
+mi = np.mean([t[0, it, 3 * nt + 2] - t[0, it, 3 * nt + 1] for it, nt in own])
 print("mma: %.0f cycles until operands ready, %.0f cycles waiting for the accumulator + issuing, per centre tile" % (mw, mi))
