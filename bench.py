@@ -227,7 +227,7 @@ def b200_arm(args):
     cost_after = float(eng.status_f64.cpu()[1].item())
     rows_after = eng.rows_counted(eng.payload)
     uncertain = int(eng.ws[:4].view(torch.int32).item()) if eng.use_ws else 0
-    algo_name = "bf16x3 filter + 3xTF32 re-check (B2F_KM_TCB)" if eng.use_ws else "algo %d" % args.algo
+    algo_name = ("fp16 filter + 3xTF32 re-check + fp64 tail (B2F_KM_TCH)" if eng.use_ws and args.algo in (0, 5) else "bf16x3 filter + 3xTF32 re-check (B2F_KM_TCB)" if eng.use_ws else "algo %d" % args.algo)
     value = 1e3 / ms_step
     flops = 2.0 * n * k * d
     achieved = flops / (kern_ms * 1e-3) / 1e12

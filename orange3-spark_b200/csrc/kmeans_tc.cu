@@ -238,7 +238,9 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         // (fp64) kernel instead of being accumulated here
         const float b2 = fminf(fmaxf(b1a, b1b), fminf(b2a, b2b));
         mbar_wait(&sm->n_full[it & 1], (it >> 1) & 1);
-        const float tau2 = rck.kappa2 * sqrtf(sm->xnorm2[it & 1][row_in_tile]) * (*rck.cmax);
+        // (second term: fp32 roundings of ||c||^2 and of the final add, relevant for rows near the origin)
+        const float cmx = *rck.cmax;
+        const float tau2 = rck.kappa2 * sqrtf(sm->xnorm2[it & 1][row_in_tile]) * cmx + 3.6e-7f * cmx * cmx;
         certain = (b2 - b1) > tau2;
         const bool list_it = row < n && !certain;
         const unsigned m = __ballot_sync(0xffffffffu, list_it);

@@ -1,27 +1,34 @@
-// K2 fused Lloyd kernel, bf16x3 filter pass + exact re-check (sm_100a only).
+// K2 fused Lloyd kernel: low-precision filter pass + exact re-check (sm_100a only).
 //
-// The 3xTF32 kernel (kmeans_tc.cu) is limited by the tensor pipe under the board power cap.  This
-// variant halves the tensor work: x = x1 + x2 (+ r), c' = -2c = c1 + c2 (+ r), all bf16, and
-//     score ~= x1.c1 + x1.c2 + x2.c1 + ||c||^2        (three kind::f16 MMAs, fp32 accumulation)
-// whose error is bounded per row by  tau = kappa * ||x|| * max_j ||c_j||  (dropped terms <= 3 u^2 per
-// operand pair with u = 2^-8, plus accumulation slack).  A row whose best and second-best scores are
-// more than 2 tau apart has a CERTAIN label; every other row is appended to a list, gathered into a
-// compact matrix and re-assigned by the 3xTF32 kernel, which also does its accumulation.  So labels,
-// sums and counts equal the 3xTF32 path's; only the cost of certain rows carries the bf16x3 error
-// (zero-mean, ~1e-4 relative per row).
+// The 3xTF32 kernel (kmeans_tc.cu) is limited by the tensor pipe under the board power cap.  Here the first pass
+// runs on cheap operands and only has to decide which rows it can label FOR CERTAIN:
+//   fp16 filter (B2F_KM_TCH, default):  score ~= (S x) . (S c') / S^2 + ||c||^2,  c' = -2c, both operands rounded
+//       once to fp16 after scaling by a power of two S taken from the centres: ONE kind::f16 MMA per product.
+//       |error| <= tau = kappa ||x|| max||c|| + underflow term,  kappa = 4 * 2^-11 (+ accumulation slack).
+//   bf16x3 filter (B2F_KM_TCB):  x = x1 + x2, c' = c1 + c2 (bf16), score ~= x1.c1 + x1.c2 + x2.c1 + ||c||^2: three
+//       MMAs, kappa = 6 * 2^-16.
+// A row whose best and second-best scores are more than 2 tau apart has a CERTAIN label and is accumulated here;
+// every other row goes to a list, is gathered into a compact matrix and re-assigned by the 3xTF32 kernel (which has
+// its own certainty test) and, failing that, by the fp64 kernel.  Labels, sums and counts therefore equal the exact
+// path's.  Cost: bf16x3 adds its (zero-mean) score error per certain row; the fp16 variant adds sum ||x||^2 only and
+// the centre-dependent remainder sum_j (n_j ||c_j||^2 - 2 c_j . S_j) exactly from the sums (tcb_cost_terms_kernel).
 //
 // Replaces MLlib's findClosest + axpy loop behind KMeans.fit;
 //   reference call site: orangecontrib/spark/base/spark_ml_estimator.py:22.
 //
-// CTA = 640 threads, persistent, one per SM:
-//   warp 0  X producer (TMA, fp32 staging chunks of 128 rows x 32 floats)
-//   warp 1  MMA issuer (one batch of 12*KA tcgen05.mma per centre tile, A operand from tensor memory)
-//   warp 2  B producer (TMA, stage = 128 centres x 64 k of c1 and of c2, bf16, 128B swizzle)
-//   warp 3  TMEM allocator
-//   warps 4-11  epilogue (two warps per TMEM lane quarter, 64 columns each): tcgen05.ld, + ||c||^2,
-//               running best / second best, certainty test
-//   warps 12-15 split: fp32 row -> x1, x2 bf16 pairs -> tcgen05.st into tensor memory; row norms
-//   warps 16-19 accumulate certain rows (16-byte vector reductions), cost, counts
+// CTA = 640 threads, persistent, one per SM.  The scheduler prefers the higher warp ids, so latency-critical roles
+// sit at the top:
+//   warps 0-7   epilogue: two per TMEM lane quarter, each takes every other centre tile whole; tcgen05.ld, running
+//               best / second best (fp16: on integer keys, min/max only), partial results to shared memory
+//   warps 8-11  split: fp32 row -> fp16 (or bf16 pair) operand -> tcgen05.st into tensor memory; row norms
+//   warps 12-15 finish (thread == row): merge the two epilogue partials, certainty test, labels, re-check list,
+//               accumulation of certain rows (16-byte vector reductions into 4 fp32 replicas), cost, counts
+//   warp 16     X producer (TMA, fp32 staging chunks of 128 rows x 32 floats)
+//   warp 17     MMA issuer (one batch of 4*KA or 12*KA tcgen05.mma per centre tile, A operand from tensor memory)
+//   warp 18     B producer (TMA, stage = one centre tile: 128 centres x d of the 16-bit operand plane(s))
+//   warp 19     TMEM allocator
+// Tensor memory: [0,256) two accumulators | [256,384) operand x1, two row tiles | [384,512) bf16x3: x2; fp16: a
+// third accumulator.  Registers are moved from the control / finish warpgroups to the epilogue (setmaxnreg).
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -99,8 +106,8 @@ constexpr int W_XPROD = 16, W_MMA = 17, W_BPROD = 18, W_ALLOC = 19;
 
 struct SmemB {
   uint64_t xs_full[4], xs_empty[4];  // fp32 staging, per 32-float chunk
-  uint64_t xa_full[4], xa_empty[4];  // TMEM operand, per (row-tile buffer, 64-k atom)
-  uint64_t b_full[8], b_empty[8];
+  uint64_t xa_full[2], xa_empty[2];  // TMEM operand, per row-tile buffer
+  uint64_t b_full[4], b_empty[4];    // centre-operand stages (a stage = one whole centre tile)
   uint64_t t_full[3], t_empty[3];    // accumulators
   uint64_t a_full[2], a_empty[2];    // epilogue -> finish hand-off
   uint64_t n_full[4], n_empty[4];    // split -> finish: squared row norms of a tile
@@ -147,7 +154,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   const int KA = d / 64;  // 64-k atoms of the 16-bit operands
   uint8_t* xs = smem_raw;
   uint8_t* stages = xs + (size_t)KC * CHUNK_BYTES;
-  SmemB* sm = reinterpret_cast<SmemB*>(stages + (size_t)nstages * TB_STAGE_BYTES);
+  SmemB* sm = reinterpret_cast<SmemB*>(stages + (size_t)nstages * 2 * TB_STAGE_BYTES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t ntiles = (n + TM - 1) / TM;
@@ -157,8 +164,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     for (int c = 0; c < 4; ++c) {
       mbar_init(&sm->xs_full[c], 1);
       mbar_init(&sm->xs_empty[c], EPI_THREADS);
-      mbar_init(&sm->xa_full[c], EPI_THREADS);
-      mbar_init(&sm->xa_empty[c], 1);
+      mbar_init(&sm->b_full[c], 1);
+      mbar_init(&sm->b_empty[c], 1);
       mbar_init(&sm->n_full[c], EPI_THREADS);
       mbar_init(&sm->n_empty[c], EPI_THREADS);
     }
@@ -167,12 +174,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_init(&sm->t_empty[c], EPI_THREADS);
     }
     for (int c = 0; c < 2; ++c) {
+      mbar_init(&sm->xa_full[c], EPI_THREADS);
+      mbar_init(&sm->xa_empty[c], 1);
       mbar_init(&sm->a_full[c], 2 * EPI_THREADS);
       mbar_init(&sm->a_empty[c], EPI_THREADS);
-    }
-    for (int s = 0; s < 8; ++s) {
-      mbar_init(&sm->b_full[s], 1);
-      mbar_init(&sm->b_empty[s], 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -212,17 +217,17 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       uint32_t s = 0, ph = 0, it = 0;
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         for (int nt = 0; nt < NT; ++nt) {
+          mbar_wait_ns(&sm->b_empty[s], ph ^ 1, 64);
+          if (nt < 8) TR(11, nt);
+          mbar_expect_tx(&sm->b_full[s], (uint32_t)(KA * TB_STAGE_BYTES));
           for (int a = 0; a < KA; ++a) {
-            mbar_wait_ns(&sm->b_empty[s], ph ^ 1, 64);
-            if (nt < 8) TR(11, 2 * nt + a);
-            mbar_expect_tx(&sm->b_full[s], (uint32_t)TB_STAGE_BYTES);
-            uint8_t* dst = stages + (size_t)s * TB_STAGE_BYTES;
+            uint8_t* dst = stages + (size_t)s * (2 * TB_STAGE_BYTES) + (size_t)a * TB_STAGE_BYTES;
             tma_load_2d(dst, &map_c1, a * 64, nt * TN, &sm->b_full[s]);
             if (!H16) tma_load_2d(dst + CHUNK_BYTES, &map_c2, a * 64, nt * TN, &sm->b_full[s]);
-            if (++s == (uint32_t)nstages) {
-              s = 0;
-              ph ^= 1;
-            }
+          }
+          if (++s == (uint32_t)nstages) {
+            s = 0;
+            ph ^= 1;
           }
         }
       }
@@ -239,54 +244,48 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     uint32_t it = 0, buf = 0, round = 0, stage = 0, bphase = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t xb = it & 1;  // row-tile buffer of the TMEM operand
+      mbar_wait_ns(&sm->xa_full[xb], (it >> 1) & 1, 20);
+      const uint32_t a1 = tmem_base + TB_A1 + xb * TB_ABUF;  // 32 columns = 64 halves of k per atom
+      const uint32_t a2 = tmem_base + TB_A2 + xb * TB_ABUF;
       for (int nt = 0; nt < NT; ++nt) {
         if (nt < 8) TR(0, 3 * nt);
-        const uint32_t tmem_d = tmem_base + tb_acc_col(buf);
-        uint32_t st_idx[2];
-        // operands first (they are ready long before), the accumulator last: its release by the epilogue is the
-        // event the issue has to follow as closely as possible
-#pragma unroll
-        for (int a = 0; a < 2; ++a) {
-          if (a < KA) {
-            if (nt == 0) mbar_wait_ns(&sm->xa_full[xb * 2 + a], (it >> 1) & 1, 20);
-            mbar_wait_ns(&sm->b_full[stage], bphase, 20);
-            st_idx[a] = stage;
-            if (++stage == (uint32_t)nstages) {
-              stage = 0;
-              bphase ^= 1;
-            }
-          }
-        }
+        // operand stage first (ready long before), the accumulator last: its release by the epilogue is the event
+        // the issue has to follow as closely as possible
+        mbar_wait_ns(&sm->b_full[stage], bphase, 20);
         if (nt < 8) TR(0, 3 * nt + 1);
         mbar_wait_ns(&sm->t_empty[buf], round ^ 1, 20);
         tc_fence_after();
         if (nt < 8) TR(0, 24 + nt);
         if (elect_one()) {
+          const uint32_t tmem_d = tmem_base + tb_acc_col(buf);
+          const uint64_t bd = desc_fixed | (uint64_t)(st_a + stage * (2 * stage16));
 #pragma unroll
           for (int a = 0; a < 2; ++a) {
             if (a < KA) {
-              const uint32_t a1 = tmem_base + TB_A1 + xb * TB_ABUF + a * 32;  // 32 columns = 64 halves of k per atom
-              const uint32_t a2 = tmem_base + TB_A2 + xb * TB_ABUF + a * 32;
-              const uint64_t b1 = desc_fixed | (uint64_t)(st_a + st_idx[a] * stage16);
+              const uint64_t b1 = bd + a * stage16;
               const uint64_t b2 = b1 + chunk16;
 #pragma unroll
               for (int s = 0; s < 4; ++s) {  // 16 halves of k = 32 bytes = 2 descriptor units, 8 TMEM columns
                 if (H16) {
-                  tc_mma_f16_ts(tmem_d, a1 + 8 * s, b1 + 2 * s, IDESC_FP16, (a | s) ? 1u : 0u);
+                  tc_mma_f16_ts(tmem_d, a1 + a * 32 + 8 * s, b1 + 2 * s, IDESC_FP16, (a | s) ? 1u : 0u);
                 } else {
-                  tc_mma_f16_ts(tmem_d, a1 + 8 * s, b1 + 2 * s, IDESC_BF16, (a | s) ? 1u : 0u);
-                  tc_mma_f16_ts(tmem_d, a1 + 8 * s, b2 + 2 * s, IDESC_BF16, 1u);
-                  tc_mma_f16_ts(tmem_d, a2 + 8 * s, b1 + 2 * s, IDESC_BF16, 1u);
+                  tc_mma_f16_ts(tmem_d, a1 + a * 32 + 8 * s, b1 + 2 * s, IDESC_BF16, (a | s) ? 1u : 0u);
+                  tc_mma_f16_ts(tmem_d, a1 + a * 32 + 8 * s, b2 + 2 * s, IDESC_BF16, 1u);
+                  tc_mma_f16_ts(tmem_d, a2 + a * 32 + 8 * s, b1 + 2 * s, IDESC_BF16, 1u);
                 }
               }
-              tc_commit(&sm->b_empty[st_idx[a]]);
-              if (nt == NT - 1) tc_commit(&sm->xa_empty[xb * 2 + a]);
             }
           }
+          tc_commit(&sm->b_empty[stage]);
+          if (nt == NT - 1) tc_commit(&sm->xa_empty[xb]);
           tc_commit(&sm->t_full[buf]);
         }
         __syncwarp();
         if (nt < 8) TR(0, 3 * nt + 2);
+        if (++stage == (uint32_t)nstages) {
+          stage = 0;
+          bphase ^= 1;
+        }
         if (++buf == NBUF) {
           buf = 0;
           round ^= 1;
@@ -447,14 +446,14 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         }
         const uint32_t xb = it & 1;
         if (w4 == 0) TR(9, 1 + 3 * a);
-        mbar_wait_ns(&sm->xa_empty[xb * 2 + a], ((it >> 1) & 1) ^ 1, 128);  // MMAs of tile it-2 are done with this atom
+        if (a == 0) mbar_wait_ns(&sm->xa_empty[xb], ((it >> 1) & 1) ^ 1, 128);  // MMAs of tile it-2 are done with it
         tc_fence_after();
         if (w4 == 0) TR(9, 2 + 3 * a);
         tmem_st32(tmem_base + lane_addr + TB_A1 + xb * TB_ABUF + a * 32, p1);
         if (!H16) tmem_st32(tmem_base + lane_addr + TB_A2 + xb * TB_ABUF + a * 32, p2);
         tmem_st_wait();
         tc_fence_before();
-        mbar_arrive(&sm->xa_full[xb * 2 + a]);
+        if (a == KA - 1) mbar_arrive(&sm->xa_full[xb]);
         if (w4 == 0) TR(9, 3 + 3 * a);
       }
       // four slots: the split warps run up to two tiles ahead of the MMAs, which run ahead of the finish warps
@@ -505,7 +504,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       const float xn = sm->xnorm2[it & 3][row_in_tile];
       mbar_arrive(&sm->n_empty[it & 3]);
       const float xl = sqrtf(xn);  // xn = +inf marks a row whose scaled entries overflow fp16: never certain
-      const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax);  // 2 * tau for this row
+      // 2 * tau for this row: operand rounding (~ ||x|| max||c||), fp16 underflow, and the fp32 roundings of ||c||^2
+      // itself and of the final add (~ max||c||^2: matters only for rows much closer to the origin than the centres)
+      const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax) + 3.6e-7f * cmax * cmax;
       const int64_t row = tile * TM + row_in_tile;
       const bool live = row < n;
       bool certain = (b2 - b1) > tau2;  // false for NaN as well
@@ -663,8 +664,9 @@ static int km_tcb_stages(int d, int filter) {
   // the row re-reads of the finish warps and the few spilled loop counters (else every one is an L2 round trip)
   const int budget = (filter == KM_FILTER_FP16 ? 195 : 227) * 1024;
   const int left = budget - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES;
-  int s = left / (filter == KM_FILTER_FP16 ? tb_stage_bytes<KM_FILTER_FP16>() : tb_stage_bytes<KM_FILTER_BF16X3>());
-  const int cap = getenv("B2F_TC_STAGES") ? atoi(getenv("B2F_TC_STAGES")) : 8;  // dev knob
+  // a stage holds one centre tile: two 64-k atoms (space for two even when d == 64)
+  int s = left / (2 * (filter == KM_FILTER_FP16 ? tb_stage_bytes<KM_FILTER_FP16>() : tb_stage_bytes<KM_FILTER_BF16X3>()));
+  const int cap = getenv("B2F_TC_STAGES") ? atoi(getenv("B2F_TC_STAGES")) : 4;  // dev knob
   return s > cap ? cap : s;
 }
 
@@ -672,7 +674,7 @@ bool km_tcb_supported(int k, int d, int64_t ld) {
   if (d != 64 && d != 128) return false;  // whole 64-k atoms, X hi/lo pairs fit the tensor memory budget
   if (k % TN != 0 || k < TN) return false;
   if (ld % 4 != 0) return false;
-  return km_tcb_stages(d, KM_FILTER_BF16X3) >= 2 * (d / 64) && km_tc_supported(k, d, ld);
+  return km_tcb_stages(d, KM_FILTER_BF16X3) >= 2 && km_tc_supported(k, d, ld);
 }
 
 size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
@@ -732,7 +734,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   const bool acc_main = accumulate && !(dbg & 4);
   B2F_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcbWs), stream));
   const size_t stage_bytes = h16 ? tb_stage_bytes<KM_FILTER_FP16>() : tb_stage_bytes<KM_FILTER_BF16X3>();
-  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * stage_bytes + sizeof(SmemB) + 64;
+  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * 2 * stage_bytes + sizeof(SmemB) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
   if ((int64_t)grid > ntiles) grid = (int)ntiles;

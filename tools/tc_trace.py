@@ -20,8 +20,7 @@ for it in range(first, first + ntiles):
         for s, lab in enumerate(("loop top", "operands ready", "issued")):
             ev.append((t[0, it, 3 * nt + s], "mma   tile %d nt %d %s" % (it, nt, lab)))
         ev.append((t[0, it, 24 + nt], "mma   tile %d nt %d accumulator free, issuing" % (it, nt)))
-        for a in range(2):
-            ev.append((t[11, it, 2 * nt + a], "bprod tile %d nt %d atom %d stage free, TMA issued" % (it, nt, a)))
+        ev.append((t[11, it, nt], "bprod tile %d nt %d stage free, TMA issued" % (it, nt)))
         for r in range(1, 9):
             if t[r, it, 3 * nt]:
                 for s, lab in enumerate(("wait t_full", "got accumulator", "released accumulator")):
