@@ -48,14 +48,19 @@ static inline size_t b2f_align_up(size_t x, size_t a) { return (x + a - 1) / a *
 //          CB2  bf16[k*d]    -2*c - CB1, rounded to bf16
 //          CH16 fp16[k*d]    -2*c * S rounded to fp16, S a power of two (operand of the fp16 filter kernel)
 //          CN64 double[k]    ||c||^2 in fp64 (exact re-check)
+//          CNH  fp16[k*64]   ||c||^2 * S^2 / 2^15 as three fp16 pieces in columns 0..2, zeros elsewhere: one more
+//                            k-block of the fp16 filter's centre operand (its x side is the constant 2^15), so the
+//                            tensor core adds ||c||^2 and the epilogue does not have to
 //          MISC float[64]    [0] = max_j ||c_j|| rounded up   [1] = max |c_jl|   (float bits, atomicMax)
 //                            [2] = S   [3] = 1 / S^2   (written by the second prepare kernel)            ]
+#define KM_CNH_COLS 64
+#define KM_CNH_E1 32768.f
 #define KM_MISC_CMAX 0
 #define KM_MISC_CABS 1
 #define KM_MISC_SCALE 2
 #define KM_MISC_INV_SCALE2 3
 struct KmPrepLayout {
-  size_t off_c32, off_ch, off_cl, off_cn, off_c64, off_cb1, off_cb2, off_ch16, off_cn64, off_misc, bytes;
+  size_t off_c32, off_ch, off_cl, off_cn, off_c64, off_cb1, off_cb2, off_ch16, off_cn64, off_cnh, off_misc, bytes;
 };
 static inline KmPrepLayout km_prep_layout(int k, int d) {
   KmPrepLayout L;
@@ -70,6 +75,7 @@ static inline KmPrepLayout km_prep_layout(int k, int d) {
   L.off_cb2 = o; o = b2f_align_up(o + kd * 2, 1024);
   L.off_ch16 = o; o = b2f_align_up(o + kd * 2, 1024);
   L.off_cn64 = o; o = b2f_align_up(o + (size_t)k * 8, 1024);
+  L.off_cnh = o;  o = b2f_align_up(o + (size_t)k * KM_CNH_COLS * 2, 1024);
   L.off_misc = o; o = b2f_align_up(o + 256, 1024);
   L.bytes = o;
   return L;

@@ -55,6 +55,7 @@ __global__ void km_prepare_kernel(const double* __restrict__ C, int k, int d, fl
 // max |-2 c_jl| * S lies in [2^11, 2^12]: centre entries keep full fp16 precision down to 2^-26 of the largest one
 // and data entries up to ~16x the largest |-2c| entry stay finite (rows beyond that are sent to the re-check).
 __global__ void km_prepare_h16_kernel(const double* __restrict__ C, int k, int d, __half* __restrict__ ch16,
+                                      const double* __restrict__ cn64, __half* __restrict__ cnh,
                                       float* __restrict__ misc) {
   const float cabs = misc[KM_MISC_CABS];
   int e = 0;
@@ -72,6 +73,22 @@ __global__ void km_prepare_h16_kernel(const double* __restrict__ C, int k, int d
   const size_t kd = (size_t)k * d;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < kd; i += (size_t)gridDim.x * blockDim.x)
     ch16[i] = __float2half_rn((float)(-2.0 * C[i]) * S);
+  // ||c||^2 * S^2 / 2^15 = h1 + h2 + h3 (fp16 pieces; |c_jl| S <= 2^11 and d <= 128 keep h below 2^14)
+  const double s2 = (double)S * (double)S / (double)KM_CNH_E1;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)k * KM_CNH_COLS;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int j = (int)(i / KM_CNH_COLS), c = (int)(i % KM_CNH_COLS);
+    __half out = __float2half_rn(0.f);
+    if (c < 3) {
+      const double h = cn64[j] * s2;
+      const __half h1 = __float2half_rn((float)h);
+      const double r1 = h - (double)__half2float(h1);
+      const __half h2 = __float2half_rn((float)r1);
+      const double r2 = r1 - (double)__half2float(h2);
+      out = c == 0 ? h1 : c == 1 ? h2 : __float2half_rn((float)r2);
+    }
+    cnh[i] = out;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -441,6 +458,8 @@ extern "C" int b2f_kmeans_prepare(const double* centers, int k, int d, void* pre
   B2F_LAUNCH_CHECK();
   km_prepare_h16_kernel<<<(int)(((size_t)k * d + 255) / 256 > 1184 ? 1184 : ((size_t)k * d + 255) / 256), 256, 0,
                           b2f_cs(stream)>>>(centers, k, d, reinterpret_cast<__half*>(p + L.off_ch16),
+                                            reinterpret_cast<const double*>(p + L.off_cn64),
+                                            reinterpret_cast<__half*>(p + L.off_cnh),
                                             reinterpret_cast<float*>(p + L.off_misc));
   B2F_LAUNCH_CHECK();
   return B2F_OK;

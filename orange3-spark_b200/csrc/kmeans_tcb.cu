@@ -24,9 +24,9 @@
 //   warps 12-15 finish (thread == row): merge the two epilogue partials, certainty test, labels, re-check list,
 //               accumulation of certain rows (16-byte vector reductions into 4 fp32 replicas), cost, counts
 //   warp 16     X producer (TMA, fp32 staging chunks of 128 rows x 32 floats)
-//   warp 17     MMA issuer (one batch of 4*KA or 12*KA tcgen05.mma per centre tile, A operand from tensor memory)
+//   warps 17,19 MMA issuers, alternate centre tiles in token order (one batch of 4*KA + 1 or 12*KA tcgen05.mma per
+//               centre tile, A operand from tensor memory); warp 19 also allocates the tensor memory
 //   warp 18     B producer (TMA, stage = one centre tile: 128 centres x d of the 16-bit operand plane(s))
-//   warp 19     TMEM allocator
 // Tensor memory: [0,256) two accumulators | [256,384) operand x1, two row tiles | [384,512) bf16x3: x2; fp16: a
 // third accumulator.  Registers are moved from the control / finish warpgroups to the epilogue (setmaxnreg).
 #include <cuda_bf16.h>
@@ -39,23 +39,26 @@
 
 namespace {
 
-// [0,256) two accumulators | [256,384) x1, two row tiles of 64 columns |
-// [384,512) bf16x3: x2, likewise; fp16: a third accumulator
 constexpr uint32_t TB_TMEM_COLS = 512;
-constexpr uint32_t TB_A1 = 256, TB_A2 = 384, TB_ABUF = 64;
-__device__ __forceinline__ uint32_t tb_acc_col(uint32_t buf) { return buf < 2 ? buf * TN : 384u; }
+// bf16x3: [0,256) two accumulators | [256,384) x1, two row tiles of 64 columns | [384,512) x2, likewise
+// fp16:   [0,384) three accumulators | [384,448) the operand, one row tile | [448,456) the constant k-block that
+//         multiplies the ||c||^2 pieces of the centre operand
+constexpr uint32_t TB_A1_BF = 256, TB_A2_BF = 384, TB_A1_H = 384, TB_AC_H = 448, TB_ABUF = 64;
+__device__ __forceinline__ uint32_t tb_acc_col(uint32_t buf) { return buf * TN; }
 
 // fp16 filter epilogue works on INTEGER KEYS.  Per row, scores are scaled by a power of two `sc` such that
-// |score| * sc < 2^21 (|score| <= ||c||^2 + 2 ||x|| ||c||), and formed as  t = D * (inv * sc) + (cn_j * sc + 1.5 * 2^23):
+// |score| * sc < 2^21 (|score| <= ||c||^2 + 2 ||x|| ||c||), and formed as  t = D * (inv * sc) + 1.5 * 2^23  (D holds
+// S^2 * score: the ||c||^2 term is added by the tensor core through one more k-block of the operands):
 // the magic constant leaves round(score * sc) in the mantissa, so  key = (int)bits(t) * 129 + column  (wrapping
 // multiply; the window of possible products stays inside the int32 range) orders like (score, column) under SIGNED
 // compare, and best / second best need min/max only -- no compare + select for the index: 2.5 ALU-pipe operations
-// per score instead of 4.5; the multiply-adds, integer one included (hence 129, not a shift), run on the FMA pipe.
+// per score instead of 4.5; the two multiply-adds, the integer one included (hence 129, not a shift), run on the FMA
+// pipe, and no ||c||^2 table is read.
 // Each key is within 1 unit of score * sc; the certainty test pays for it with 2.5 units.
 constexpr float TB_MAGIC = 12582912.f;  // 1.5 * 2^23
 constexpr int TB_KEYMUL = 129;
-__device__ __forceinline__ int tb_key(float d, float arow, float cn, float sc, int col) {
-  return __float_as_int(fmaf(d, arow, fmaf(cn, sc, TB_MAGIC))) * TB_KEYMUL + col;
+__device__ __forceinline__ int tb_key(float d, float arow, int col) {
+  return __float_as_int(fmaf(d, arow, TB_MAGIC)) * TB_KEYMUL + col;
 }
 // value part of a key, relative to the key of score 0 (floor division of a possibly negative number)
 __device__ __forceinline__ int tb_key_value(int key) {
@@ -102,7 +105,7 @@ constexpr uint32_t IDESC_FP16 = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint
 constexpr int W_EPI0 = 0;    // warps 0-7   epilogue
 constexpr int W_SPLIT0 = 8;  // warps 8-11  split
 constexpr int W_FIN0 = 12;   // warps 12-15 finish
-constexpr int W_XPROD = 16, W_MMA = 17, W_BPROD = 18, W_ALLOC = 19;
+constexpr int W_XPROD = 16, W_MMA = 17, W_BPROD = 18, W_ALLOC = 19;  // W_ALLOC: TMEM allocator + second MMA issuer
 
 struct SmemB {
   uint64_t xs_full[4], xs_empty[4];  // fp32 staging, per 32-float chunk
@@ -111,6 +114,7 @@ struct SmemB {
   uint64_t t_full[3], t_empty[3];    // accumulators
   uint64_t a_full[2], a_empty[2];    // epilogue -> finish hand-off
   uint64_t n_full[4], n_empty[4];    // split -> finish: squared row norms of a tile
+  uint64_t tok[2];                   // MMA issue token: warp p has put its batch into the tensor queue
   uint32_t tmem_base;
   float xnorm2[4][TM];
   float p_b1[2][2][TM], p_b2[2][2][TM];  // [slot][epilogue warp of the lane quarter][row]: best, second best
@@ -145,8 +149,11 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
                   unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels, int accumulate,
                   TcbWs* __restrict__ ws, int32_t* __restrict__ amb_idx, int cap,
                   unsigned long long* __restrict__ trace) {
-  constexpr int TB_STAGE_BYTES = tb_stage_bytes<MODE>();
+  constexpr int TB_STAGE_BYTES = tb_stage_bytes<MODE>();  // per 64-k atom
   constexpr bool H16 = MODE == KM_FILTER_FP16;
+  constexpr int TB_TILE_BYTES = 2 * TB_STAGE_BYTES + (H16 ? CHUNK_BYTES : 0);  // a stage: two atoms (+ ||c||^2 block)
+  constexpr uint32_t XBUFS = H16 ? 1 : 2;  // row-tile buffers of the TMEM operand
+  constexpr uint32_t TB_A1 = H16 ? TB_A1_H : TB_A1_BF, TB_A2 = TB_A2_BF;
   constexpr uint32_t NBUF = H16 ? 3 : 2;  // accumulator buffers in tensor memory
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   if (smem_u32(smem_raw) & 1023u) __trap();
@@ -154,7 +161,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   const int KA = d / 64;  // 64-k atoms of the 16-bit operands
   uint8_t* xs = smem_raw;
   uint8_t* stages = xs + (size_t)KC * CHUNK_BYTES;
-  SmemB* sm = reinterpret_cast<SmemB*>(stages + (size_t)nstages * 2 * TB_STAGE_BYTES);
+  SmemB* sm = reinterpret_cast<SmemB*>(stages + (size_t)nstages * TB_TILE_BYTES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t ntiles = (n + TM - 1) / TM;
@@ -174,6 +181,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_init(&sm->t_empty[c], EPI_THREADS);
     }
     for (int c = 0; c < 2; ++c) {
+      mbar_init(&sm->tok[c], 1);
       mbar_init(&sm->xa_full[c], EPI_THREADS);
       mbar_init(&sm->xa_empty[c], 1);
       mbar_init(&sm->a_full[c], 2 * EPI_THREADS);
@@ -219,12 +227,14 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         for (int nt = 0; nt < NT; ++nt) {
           mbar_wait_ns(&sm->b_empty[s], ph ^ 1, 64);
           if (nt < 8) TR(11, nt);
-          mbar_expect_tx(&sm->b_full[s], (uint32_t)(KA * TB_STAGE_BYTES));
+          mbar_expect_tx(&sm->b_full[s], (uint32_t)(KA * TB_STAGE_BYTES + (H16 ? CHUNK_BYTES : 0)));
           for (int a = 0; a < KA; ++a) {
-            uint8_t* dst = stages + (size_t)s * (2 * TB_STAGE_BYTES) + (size_t)a * TB_STAGE_BYTES;
+            uint8_t* dst = stages + (size_t)s * TB_TILE_BYTES + (size_t)a * TB_STAGE_BYTES;
             tma_load_2d(dst, &map_c1, a * 64, nt * TN, &sm->b_full[s]);
             if (!H16) tma_load_2d(dst + CHUNK_BYTES, &map_c2, a * 64, nt * TN, &sm->b_full[s]);
           }
+          // fp16: map_c2 is the ||c||^2 plane (64 halves per centre, three of them non-zero)
+          if (H16) tma_load_2d(stages + (size_t)s * TB_TILE_BYTES + 2 * TB_STAGE_BYTES, &map_c2, 0, nt * TN, &sm->b_full[s]);
           if (++s == (uint32_t)nstages) {
             s = 0;
             ph ^= 1;
@@ -232,33 +242,56 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         }
       }
     }
-  } else if (warp == W_MMA) {
-    // ===================== MMA issuer: one batch (12 * KA or 4 * KA instructions) per centre tile ============
-    // ONE issuer on purpose.  The epilogue warps of a lane quarter take alternate centre tiles, and with three
-    // accumulators a buffer's consecutive uses go to different warps; their parity waits are only safe because
-    // centre tiles complete in issue order (a warp that has seen tile g+1 complete knows tile g has).  Two issuing
-    // warps break that order -- measured: no faster, and a stall-free epilogue (timing experiment) deadlocks.
+  } else if (warp == W_MMA || warp == W_ALLOC) {
+    // ===================== MMA issuers: one batch (4*KA + 1 or 12*KA instructions) per centre tile ============
+    // An issuing warp sits in the (shallow) tensor queue for about as long as its batch executes, and only then can
+    // it look at the barriers of a next tile.  So TWO warps take alternate centre tiles: while one issues, the other
+    // has its operand stage and accumulator checked.  An issue token keeps the batches in tile order in the queue,
+    // hence completing in tile order: the epilogue warps' parity waits rely on that (a warp that has seen tile g+1
+    // complete must be able to conclude that tile g has), and a commit covers the other warp's earlier tiles too.
+    const uint32_t mp = (warp == W_MMA) ? 0u : 1u;
     const uint64_t desc_fixed = (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
     const uint32_t st_a = smem_u32(stages) >> 4;
     const uint32_t chunk16 = CHUNK_BYTES >> 4, stage16 = (uint32_t)TB_STAGE_BYTES >> 4;
-    uint32_t it = 0, buf = 0, round = 0, stage = 0, bphase = 0;
+    uint32_t it = 0, buf = 0, round = 0, stage = 0, bphase = 0, gpar = 0;
+    uint32_t mine_n = 0;  // centre tiles this warp has issued
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      const uint32_t xb = it & 1;  // row-tile buffer of the TMEM operand
-      mbar_wait_ns(&sm->xa_full[xb], (it >> 1) & 1, 20);
+      const uint32_t xb = it % XBUFS;  // row-tile buffer of the TMEM operand
       const uint32_t a1 = tmem_base + TB_A1 + xb * TB_ABUF;  // 32 columns = 64 halves of k per atom
       const uint32_t a2 = tmem_base + TB_A2 + xb * TB_ABUF;
+      bool first = true;
       for (int nt = 0; nt < NT; ++nt) {
-        if (nt < 8) TR(0, 3 * nt);
-        // operand stage first (ready long before), the accumulator last: its release by the epilogue is the event
-        // the issue has to follow as closely as possible
-        mbar_wait_ns(&sm->b_full[stage], bphase, 20);
-        if (nt < 8) TR(0, 3 * nt + 1);
-        mbar_wait_ns(&sm->t_empty[buf], round ^ 1, 20);
+        const bool mine = gpar == mp;
+        const bool very_first = (it == 0 && nt == 0);
+        gpar ^= 1u;
+        const uint32_t cbuf = buf, cround = round, cstage = stage, cbphase = bphase;
+        if (++stage == (uint32_t)nstages) {
+          stage = 0;
+          bphase ^= 1;
+        }
+        if (++buf == NBUF) {
+          buf = 0;
+          round ^= 1;
+        }
+        if (!mine) continue;
+        if (mp == 0 && nt < 8) TR(0, 3 * nt);
+        mbar_wait_ns(&sm->b_full[cstage], cbphase, 20);
+        if (mp == 0 && nt < 8) TR(0, 3 * nt + 1);
+        mbar_wait_ns(&sm->t_empty[cbuf], cround ^ 1, 20);
+        // the other warp has issued the previous centre tile: its k-th tile is global tile 2k + (1 - mp)
+        if (!very_first) mbar_wait_ns(&sm->tok[mp ^ 1u], (mp ? mine_n : mine_n - 1u) & 1u, 20);
+        // Only now the operand buffer: a warp that owns no tile of some row tile (k == 128) never looks at that row
+        // tile's phase of xa_full, and a parity wait is only meaningful one phase ahead of what the waiter has seen.
+        // After the token every earlier row tile's phase is known to be complete.  (The stage and accumulator
+        // barriers cannot be skipped that way: their previous use belongs to a tile at least two back, which the
+        // token chain has already ordered.)
+        if (first) mbar_wait_ns(&sm->xa_full[xb], (it / XBUFS) & 1, 20);
+        first = false;
         tc_fence_after();
-        if (nt < 8) TR(0, 24 + nt);
+        if (mp == 0 && nt < 8) TR(0, 24 + nt);
         if (elect_one()) {
-          const uint32_t tmem_d = tmem_base + tb_acc_col(buf);
-          const uint64_t bd = desc_fixed | (uint64_t)(st_a + stage * (2 * stage16));
+          const uint32_t tmem_d = tmem_base + tb_acc_col(cbuf);
+          const uint64_t bd = desc_fixed | (uint64_t)(st_a + cstage * ((uint32_t)TB_TILE_BYTES >> 4));
 #pragma unroll
           for (int a = 0; a < 2; ++a) {
             if (a < KA) {
@@ -276,20 +309,16 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
               }
             }
           }
-          tc_commit(&sm->b_empty[stage]);
+          // + ||c||^2:  (2^15, 2^15, 2^15, 0, ...) . (h1, h2, h3, 0, ...), the first 16-k slice of the third atom
+          if (H16) tc_mma_f16_ts(tmem_d, tmem_base + TB_AC_H, bd + 2 * stage16, IDESC_FP16, 1u);
+          mbar_arrive(&sm->tok[mp]);  // batch is in the queue: the other warp may issue the next tile
+          tc_commit(&sm->b_empty[cstage]);
           if (nt == NT - 1) tc_commit(&sm->xa_empty[xb]);
-          tc_commit(&sm->t_full[buf]);
+          tc_commit(&sm->t_full[cbuf]);
         }
         __syncwarp();
-        if (nt < 8) TR(0, 3 * nt + 2);
-        if (++stage == (uint32_t)nstages) {
-          stage = 0;
-          bphase ^= 1;
-        }
-        if (++buf == NBUF) {
-          buf = 0;
-          round ^= 1;
-        }
+        ++mine_n;
+        if (mp == 0 && nt < 8) TR(0, 3 * nt + 2);
       }
     }
   } else if (warp < W_SPLIT0) {
@@ -311,12 +340,11 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       // integer-key path (fp16 filter): running best / second best keys and the centre tile of the best
       int B1 = 0x7fffffff, B2 = 0x7fffffff;
       int T1 = 0;
-      float sc = 1.f, arow = 1.f;
+      float arow = 1.f;
       if (H16) {
         // the split warps finished this row tile before its first MMA could start: the norms are there
         mbar_wait_ns(&sm->n_full[it & 3], (it >> 2) & 1, 32);
-        sc = tb_row_scale(sm->xnorm2[it & 3][row_in_tile], cmax_e);
-        arow = inv * sc;
+        arow = inv * tb_row_scale(sm->xnorm2[it & 3][row_in_tile], cmax_e);
       }
       for (int nt = 0; nt < NT; ++nt) {
         const uint32_t cbuf = buf, cround = round;
@@ -343,20 +371,15 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           const int jbase = nt * TN + c * 32;
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
-#ifdef TB_EXP_NOCN  // timing experiment: results invalid
-            const float4 cv = make_float4(1.f, 2.f, 3.f, 4.f);
-#else
-            const float4 cv = __ldg(cn4 + j4);
-#endif
 #ifdef TB_EXP_NOMATH  // timing experiment: results invalid
             if (j4 > 0) continue;
 #endif
-            if (H16) {
+            if (H16) {  // the accumulator already holds S^2 (x . -2c + ||c||^2)
               const int col = c * 32 + j4 * 4;
-              const int q0 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 0]), arow, cv.x, sc, col);
-              const int q1 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 1]), arow, cv.y, sc, col + 1);
-              const int q2 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 2]), arow, cv.z, sc, col + 2);
-              const int q3 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 3]), arow, cv.w, sc, col + 3);
+              const int q0 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 0]), arow, col);
+              const int q1 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 1]), arow, col + 1);
+              const int q2 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 2]), arow, col + 2);
+              const int q3 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 3]), arow, col + 3);
               const int loa = min(q0, q1), hia = max(q0, q1), lob = min(q2, q3), hib = max(q2, q3);
               k2a = min(k2a, min(hia, max(k1a, loa)));
               k1a = min(k1a, loa);
@@ -364,6 +387,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
               k1b = min(k1b, lob);
               continue;
             }
+            const float4 cv = __ldg(cn4 + j4);
             const float s0 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 0]), inv, cv.x);  // inv is a power of two
             const float s1 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 1]), inv, cv.y);
             const float s2 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 2]), inv, cv.z);
@@ -409,6 +433,17 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
     const float S = H16 ? misc[KM_MISC_SCALE] : 1.f;
     const float xlim = 65504.f / S;  // entries beyond this overflow fp16 after scaling
+    if (H16) {  // the constant k-block: 16 halves (2^15, 2^15, 2^15, 0 ...) per row, written once
+      uint32_t cst[8];
+      const __half2 ee = __floats2half2_rn(KM_CNH_E1, KM_CNH_E1), e0 = __floats2half2_rn(KM_CNH_E1, 0.f);
+      cst[0] = *reinterpret_cast<const uint32_t*>(&ee);
+      cst[1] = *reinterpret_cast<const uint32_t*>(&e0);
+#pragma unroll
+      for (int i = 2; i < 8; ++i) cst[i] = 0u;
+      tmem_st8(tmem_base + lane_addr + TB_AC_H, cst);
+      tmem_st_wait();
+      tc_fence_before();  // ordered before the MMAs by the first xa_full arrive below
+    }
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       float xn = 0.f, amax = 0.f;
@@ -444,9 +479,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           }
           mbar_arrive(&sm->xs_empty[kc]);
         }
-        const uint32_t xb = it & 1;
+        const uint32_t xb = it % XBUFS;
         if (w4 == 0) TR(9, 1 + 3 * a);
-        if (a == 0) mbar_wait_ns(&sm->xa_empty[xb], ((it >> 1) & 1) ^ 1, 128);  // MMAs of tile it-2 are done with it
+        // the MMAs that read this buffer last (tile it - XBUFS) are done with it
+        if (a == 0) mbar_wait_ns(&sm->xa_empty[xb], ((it / XBUFS) & 1) ^ 1, 64);
         tc_fence_after();
         if (w4 == 0) TR(9, 2 + 3 * a);
         tmem_st32(tmem_base + lane_addr + TB_A1 + xb * TB_ABUF + a * 32, p1);
@@ -506,7 +542,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       const float xl = sqrtf(xn);  // xn = +inf marks a row whose scaled entries overflow fp16: never certain
       // 2 * tau for this row: operand rounding (~ ||x|| max||c||), fp16 underflow, and the fp32 roundings of ||c||^2
       // itself and of the final add (~ max||c||^2: matters only for rows much closer to the origin than the centres)
-      const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax) + 3.6e-7f * cmax * cmax;
+      // (fp16 filter: ||c||^2 enters as three fp16 pieces times 2^15; their underflow adds 3 * 2^-10 / S^2)
+      const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax) + 3.6e-7f * cmax * cmax +
+                         (H16 ? 5.9e-3f * misc[KM_MISC_INV_SCALE2] : 0.f);
       const int64_t row = tile * TM + row_in_tile;
       const bool live = row < n;
       bool certain = (b2 - b1) > tau2;  // false for NaN as well
@@ -662,10 +700,11 @@ static int tcb_cap_from_bytes(size_t bytes, int d) {
 static int km_tcb_stages(int d, int filter) {
   // fp16 filter: stay within the 196 KB shared-memory carve-out so that 32 KB of L1 remain for the ||c||^2 table,
   // the row re-reads of the finish warps and the few spilled loop counters (else every one is an L2 round trip)
-  const int budget = (filter == KM_FILTER_FP16 ? 195 : 227) * 1024;
+  const int budget = (filter != KM_FILTER_FP16 ? 227 : getenv("B2F_TC_SMEM_KB") ? atoi(getenv("B2F_TC_SMEM_KB"))  // dev knob
+                                                                                 : 195) * 1024;
   const int left = budget - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES;
-  // a stage holds one centre tile: two 64-k atoms (space for two even when d == 64)
-  int s = left / (2 * (filter == KM_FILTER_FP16 ? tb_stage_bytes<KM_FILTER_FP16>() : tb_stage_bytes<KM_FILTER_BF16X3>()));
+  // a stage holds one centre tile: two 64-k atoms (space for two even when d == 64), fp16: + the ||c||^2 block
+  int s = left / (filter == KM_FILTER_FP16 ? 3 * CHUNK_BYTES : 2 * tb_stage_bytes<KM_FILTER_BF16X3>());
   const int cap = getenv("B2F_TC_STAGES") ? atoi(getenv("B2F_TC_STAGES")) : 4;  // dev knob
   return s > cap ? cap : s;
 }
@@ -710,7 +749,10 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   // (the fp16 plane goes through a 16-bit map as well: the copy does not interpret the elements)
   if ((rc = make_map_bf16(&m1, pp + (h16 ? P.off_ch16 : P.off_cb1), (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK)
     return rc;
-  if ((rc = make_map_bf16(&m2, pp + P.off_cb2, (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK) return rc;
+  // second map: bf16x3 -> the low bf16 plane; fp16 -> the ||c||^2 plane (64 halves per centre)
+  if (h16) rc = make_map_bf16(&m2, pp + P.off_cnh, (uint64_t)k, (uint64_t)KM_CNH_COLS, (uint64_t)KM_CNH_COLS);
+  else rc = make_map_bf16(&m2, pp + P.off_cb2, (uint64_t)k, (uint64_t)d, (uint64_t)d);
+  if (rc != B2F_OK) return rc;
   double* payload = nullptr;
   float* rep = nullptr;
   unsigned long long* cnt = nullptr;
@@ -726,15 +768,15 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   // fp16 filter (one product, x and -2c each rounded once, u = 2^-11):  |error| <= (2u + u^2) |x||c'| = 4.01 u |x||c|
   // plus the accumulation slack for d products; operands below the fp16 normal range carry an absolute error of
   // eta = 2^-25 / S per entry instead:  + sqrt(d) eta (|c'| + |x|)  ->  kappa0 (divided by S in the kernel)
-  const float kappa = h16 ? 4.0f * 1.01f / 2048.0f + 2.0f * (d + 16.0f) / 8388608.0f
+  const float kappa = h16 ? 4.0f * 1.01f / 2048.0f + 2.0f * (d + 20.0f) / 8388608.0f
                           : 6.0f * 1.02f / 65536.0f + 2.0f * (3.0f * d + 16.0f) / 8388608.0f;
   const float kappa2 = 2.0f * kappa;
   const float kappa0 = h16 ? 2.0f * 1.01f * sqrtf((float)d) / 33554432.0f : 0.f;
   const int dbg = getenv("B2F_TC_DBG") ? atoi(getenv("B2F_TC_DBG")) : 0;  // dev knob, results invalid when set
   const bool acc_main = accumulate && !(dbg & 4);
   B2F_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcbWs), stream));
-  const size_t stage_bytes = h16 ? tb_stage_bytes<KM_FILTER_FP16>() : tb_stage_bytes<KM_FILTER_BF16X3>();
-  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * 2 * stage_bytes + sizeof(SmemB) + 64;
+  const size_t tile_bytes = h16 ? 3 * (size_t)CHUNK_BYTES : 2 * (size_t)tb_stage_bytes<KM_FILTER_BF16X3>();
+  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * tile_bytes + sizeof(SmemB) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
@@ -751,7 +793,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, -1.0);
     auto kern = trace ? km_tcb_kernel<KM_FILTER_FP16, true> : km_tcb_kernel<KM_FILTER_FP16, false>;
     B2F_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m1, X, n, d, ld, cn, misc, kappa2, kappa0, k, nstages, payload, rep,
+    kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, cn, misc, kappa2, kappa0, k, nstages, payload, rep,
                                              cnt, labels, acc_main ? 1 : 0, hdr, amb_idx, cap, trace);
     B2F_LAUNCH_CHECK();
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, 1.0);
