@@ -48,12 +48,12 @@ static inline size_t b2f_align_up(size_t x, size_t a) { return (x + a - 1) / a *
 //          CB2  bf16[k*d]    -2*c - CB1, rounded to bf16
 //          CH16 fp16[k*d]    -2*c * S rounded to fp16, S a power of two (operand of the fp16 filter kernel)
 //          CN64 double[k]    ||c||^2 in fp64 (exact re-check)
-//          CNH  fp16[k*64]   ||c||^2 * S^2 / 2^15 as three fp16 pieces in columns 0..2, zeros elsewhere: one more
+//          CNH  fp16[k*16]   ||c||^2 * S^2 / 2^15 as three fp16 pieces in columns 0..2, zeros elsewhere: one more
 //                            k-block of the fp16 filter's centre operand (its x side is the constant 2^15), so the
 //                            tensor core adds ||c||^2 and the epilogue does not have to
 //          MISC float[64]    [0] = max_j ||c_j|| rounded up   [1] = max |c_jl|   (float bits, atomicMax)
 //                            [2] = S   [3] = 1 / S^2   (written by the second prepare kernel)            ]
-#define KM_CNH_COLS 64
+#define KM_CNH_COLS 16
 #define KM_CNH_E1 32768.f
 #define KM_MISC_CMAX 0
 #define KM_MISC_CABS 1

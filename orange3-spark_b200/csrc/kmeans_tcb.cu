@@ -41,9 +41,9 @@ namespace {
 
 constexpr uint32_t TB_TMEM_COLS = 512;
 // bf16x3: [0,256) two accumulators | [256,384) x1, two row tiles of 64 columns | [384,512) x2, likewise
-// fp16:   [0,384) three accumulators | [384,448) the operand, one row tile | [448,456) the constant k-block that
-//         multiplies the ||c||^2 pieces of the centre operand
-constexpr uint32_t TB_A1_BF = 256, TB_A2_BF = 384, TB_A1_H = 384, TB_AC_H = 448, TB_ABUF = 64;
+// fp16:   [0,384) three accumulators | [384,512) the operand, two row tiles of 64 columns  (the constant k-block that
+//         multiplies the ||c||^2 pieces of the centre operand is read from shared memory)
+constexpr uint32_t TB_A1_BF = 256, TB_A2_BF = 384, TB_A1_H = 384, TB_ABUF = 64;
 __device__ __forceinline__ uint32_t tb_acc_col(uint32_t buf) { return buf * TN; }
 
 // fp16 filter epilogue works on INTEGER KEYS.  Per row, scores are scaled by a power of two `sc` such that
@@ -79,12 +79,15 @@ __device__ __forceinline__ float tb_row_scale(float xn, float cmax) {
   return __int_as_float(e << 23);
 }
 constexpr int TB_THREADS = 640;
+constexpr int TB_CN_BYTES = 128 * 32;  // the ||c||^2 k-block of a centre tile: 128 centres x 16 halves
 #ifndef TB_REG_CTRL
 // what the epilogue warpgroups gain, (EPI - 96) * 256, must be given back first by the others:
 // (96 - CTRL) * 128 + (96 - FIN) * 128  (the pool is per CTA)
 #define TB_REG_CTRL 48
 #define TB_REG_FIN 80
 #define TB_REG_EPI 128
+#define TB_FIN_ROWS 8
+#define TB_FX_ROWS 8
 #endif
 // dev tracing (B2F_TC_TRACE=<file>): block 0 stamps clock64() at the hand-offs of its first TR_TILES row tiles
 constexpr int TR_TILES = 64, TR_SLOTS = 32, TR_ROLES = 12;  // mma | 8 epilogue warps | split | finish | B producer
@@ -115,6 +118,7 @@ struct SmemB {
   uint64_t a_full[2], a_empty[2];    // epilogue -> finish hand-off
   uint64_t n_full[4], n_empty[4];    // split -> finish: squared row norms of a tile
   uint64_t tok[2];                   // MMA issue token: warp p has put its batch into the tensor queue
+  uint64_t fx_full[4][2];            // finish warps (fp16 filter): rows of a batch have landed in their slot
   uint32_t tmem_base;
   float xnorm2[4][TM];
   float p_b1[2][2][TM], p_b2[2][2][TM];  // [slot][epilogue warp of the lane quarter][row]: best, second best
@@ -128,6 +132,15 @@ struct TcbWs {  // header of the caller-provided workspace
   int pad[61];
 };
 
+__device__ __forceinline__ void tc_mma_f16_ss(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
                                               uint32_t accumulate) {
   asm volatile(
@@ -151,8 +164,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
                   unsigned long long* __restrict__ trace) {
   constexpr int TB_STAGE_BYTES = tb_stage_bytes<MODE>();  // per 64-k atom
   constexpr bool H16 = MODE == KM_FILTER_FP16;
-  constexpr int TB_TILE_BYTES = 2 * TB_STAGE_BYTES + (H16 ? CHUNK_BYTES : 0);  // a stage: two atoms (+ ||c||^2 block)
-  constexpr uint32_t XBUFS = H16 ? 1 : 2;  // row-tile buffers of the TMEM operand
+  constexpr int TB_TILE_BYTES = 2 * TB_STAGE_BYTES + (H16 ? TB_CN_BYTES : 0);  // a stage: two atoms (+ ||c||^2 block)
+  constexpr uint32_t XBUFS = 2;  // row-tile buffers of the TMEM operand
   constexpr uint32_t TB_A1 = H16 ? TB_A1_H : TB_A1_BF, TB_A2 = TB_A2_BF;
   constexpr uint32_t NBUF = H16 ? 3 : 2;  // accumulator buffers in tensor memory
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -161,7 +174,11 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   const int KA = d / 64;  // 64-k atoms of the 16-bit operands
   uint8_t* xs = smem_raw;
   uint8_t* stages = xs + (size_t)KC * CHUNK_BYTES;
-  SmemB* sm = reinterpret_cast<SmemB*>(stages + (size_t)nstages * TB_TILE_BYTES);
+  // fp16: constant x-side k-block (128 rows x 16 halves, 32-byte swizzle; halves 0..2 of every row = 2^15)
+  uint8_t* aconst = stages + (size_t)nstages * TB_TILE_BYTES;
+  // fp16: row buffers of the finish warps: 4 warps x 2 slots x TB_FX_ROWS rows of d floats
+  uint8_t* fxbuf = aconst + (H16 ? TB_CN_BYTES : 0);
+  SmemB* sm = reinterpret_cast<SmemB*>(fxbuf + (H16 ? 4 * 2 * TB_FX_ROWS * d * 4 : 0));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t ntiles = (n + TM - 1) / TM;
@@ -180,6 +197,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_init(&sm->t_full[c], 1);
       mbar_init(&sm->t_empty[c], EPI_THREADS);
     }
+    for (int c = 0; c < 8; ++c) mbar_init(&sm->fx_full[c >> 1][c & 1], 1);
     for (int c = 0; c < 2; ++c) {
       mbar_init(&sm->tok[c], 1);
       mbar_init(&sm->xa_full[c], EPI_THREADS);
@@ -188,6 +206,19 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_init(&sm->a_empty[c], EPI_THREADS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (H16) {
+    for (int i = threadIdx.x; i < TB_CN_BYTES / 16; i += TB_THREADS) {  // 16-byte chunks: row = i / 2
+      const int r = i >> 1, pc = i & 1;
+      uint4 val = make_uint4(0u, 0u, 0u, 0u);
+      if (pc == ((r >> 2) & 1)) {  // 32-byte swizzle: address bit 4 ^= bit 7, i.e. chunk ^= (row >> 2) & 1
+        const __half2 ee = __floats2half2_rn(KM_CNH_E1, KM_CNH_E1), e0 = __floats2half2_rn(KM_CNH_E1, 0.f);
+        val.x = *reinterpret_cast<const uint32_t*>(&ee);
+        val.y = *reinterpret_cast<const uint32_t*>(&e0);
+      }
+      reinterpret_cast<uint4*>(aconst)[i] = val;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> tensor-core reads
   }
   if (warp == W_ALLOC) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm->tmem_base)),
@@ -227,13 +258,13 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         for (int nt = 0; nt < NT; ++nt) {
           mbar_wait_ns(&sm->b_empty[s], ph ^ 1, 64);
           if (nt < 8) TR(11, nt);
-          mbar_expect_tx(&sm->b_full[s], (uint32_t)(KA * TB_STAGE_BYTES + (H16 ? CHUNK_BYTES : 0)));
+          mbar_expect_tx(&sm->b_full[s], (uint32_t)(KA * TB_STAGE_BYTES + (H16 ? TB_CN_BYTES : 0)));
           for (int a = 0; a < KA; ++a) {
             uint8_t* dst = stages + (size_t)s * TB_TILE_BYTES + (size_t)a * TB_STAGE_BYTES;
             tma_load_2d(dst, &map_c1, a * 64, nt * TN, &sm->b_full[s]);
             if (!H16) tma_load_2d(dst + CHUNK_BYTES, &map_c2, a * 64, nt * TN, &sm->b_full[s]);
           }
-          // fp16: map_c2 is the ||c||^2 plane (64 halves per centre, three of them non-zero)
+          // fp16: map_c2 is the ||c||^2 plane (16 halves per centre, three of them non-zero; 32-byte swizzle)
           if (H16) tma_load_2d(stages + (size_t)s * TB_TILE_BYTES + 2 * TB_STAGE_BYTES, &map_c2, 0, nt * TN, &sm->b_full[s]);
           if (++s == (uint32_t)nstages) {
             s = 0;
@@ -251,6 +282,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     // complete must be able to conclude that tile g has), and a commit covers the other warp's earlier tiles too.
     const uint32_t mp = (warp == W_MMA) ? 0u : 1u;
     const uint64_t desc_fixed = (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+    const uint64_t desc_sw32 = (1ull << 16) | (16ull << 32) | (1ull << 46) | (6ull << 61);
     const uint32_t st_a = smem_u32(stages) >> 4;
     const uint32_t chunk16 = CHUNK_BYTES >> 4, stage16 = (uint32_t)TB_STAGE_BYTES >> 4;
     uint32_t it = 0, buf = 0, round = 0, stage = 0, bphase = 0, gpar = 0;
@@ -310,7 +342,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             }
           }
           // + ||c||^2:  (2^15, 2^15, 2^15, 0, ...) . (h1, h2, h3, 0, ...), the first 16-k slice of the third atom
-          if (H16) tc_mma_f16_ts(tmem_d, tmem_base + TB_AC_H, bd + 2 * stage16, IDESC_FP16, 1u);
+          // (operands of this one: 128 x 16 halves, 32-byte swizzle, 8-row groups 256 B apart)
+          if (H16)
+            tc_mma_f16_ss(tmem_d, desc_sw32 | (uint64_t)(smem_u32(aconst) >> 4),
+                          desc_sw32 | (uint64_t)(st_a + cstage * ((uint32_t)TB_TILE_BYTES >> 4) + 2 * stage16), IDESC_FP16, 1u);
           mbar_arrive(&sm->tok[mp]);  // batch is in the queue: the other warp may issue the next tile
           tc_commit(&sm->b_empty[cstage]);
           if (nt == NT - 1) tc_commit(&sm->xa_empty[xb]);
@@ -433,17 +468,6 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
     const float S = H16 ? misc[KM_MISC_SCALE] : 1.f;
     const float xlim = 65504.f / S;  // entries beyond this overflow fp16 after scaling
-    if (H16) {  // the constant k-block: 16 halves (2^15, 2^15, 2^15, 0 ...) per row, written once
-      uint32_t cst[8];
-      const __half2 ee = __floats2half2_rn(KM_CNH_E1, KM_CNH_E1), e0 = __floats2half2_rn(KM_CNH_E1, 0.f);
-      cst[0] = *reinterpret_cast<const uint32_t*>(&ee);
-      cst[1] = *reinterpret_cast<const uint32_t*>(&e0);
-#pragma unroll
-      for (int i = 2; i < 8; ++i) cst[i] = 0u;
-      tmem_st8(tmem_base + lane_addr + TB_AC_H, cst);
-      tmem_st_wait();
-      tc_fence_before();  // ordered before the MMAs by the first xa_full arrive below
-    }
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       float xn = 0.f, amax = 0.f;
@@ -508,7 +532,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     double cost = 0.0;
     unsigned long long nrows = 0;
     float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
-    uint32_t it = 0;
+    uint32_t it = 0, fxc = 0;  // fxc: batches this warp has pushed through its row buffers
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t ab = it & 1;
       if (w4 == 0) TR(10, 0);
@@ -572,19 +596,64 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       // sum_j (n_j ||c_j||^2 - 2 c_j . S_j), is added exactly from the sums (tcb_cost_terms_kernel)
       const float my_sc = H16 ? xn : fmaxf(xn + b1, 0.f);
       const int64_t r0 = tile * TM + w4 * 32;
-      for (int g = 0; g < 32; g += 8) {
-        float4 xv[8];
+      if (H16) {
+        // Rows travel L2 -> shared memory -> L2 reduction entirely on the copy engine (bulk copy, then bulk
+        // reduce-add into the replica row of the label): no registers, no load latency in this warp, two batches in
+        // flight.  At 8 rows in flight through registers this loop set the pace of the whole kernel (hand-off trace).
+        const uint32_t rowbytes = (uint32_t)d * 4u;
+        uint8_t* mybuf = fxbuf + (size_t)w4 * 2 * TB_FX_ROWS * rowbytes;
+        const int u = lane & (TB_FX_ROWS - 1);
+        int lbl_b[32 / TB_FX_ROWS];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int b = 0; b < 32 / TB_FX_ROWS; ++b) lbl_b[b] = __shfl_sync(0xffffffffu, my_lab, b * TB_FX_ROWS + u);
+        auto issue_load = [&](int b, bool newest_may_pend) {
+          const uint32_t slot = (fxc + b) & 1u;
+          const bool act = lane < TB_FX_ROWS && lbl_b[b] >= 0;
+          const unsigned m = __ballot_sync(0xffffffffu, act);
+          // the reduction that read this slot two batches ago must be done with it
+          if (newest_may_pend) bulk_wait_read<1>();
+          else bulk_wait_read<0>();
+          if (lane == 0) {
+            if (m) mbar_expect_tx(&sm->fx_full[w4][slot], (uint32_t)__popc(m) * rowbytes);
+            else mbar_arrive(&sm->fx_full[w4][slot]);
+          }
+          __syncwarp();
+          if (act)
+            bulk_load(mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes, X + (r0 + b * TB_FX_ROWS + lane) * ld,
+                      rowbytes, &sm->fx_full[w4][slot]);
+        };
+        issue_load(0, true);
+        issue_load(1, false);
+#pragma unroll
+        for (int b = 0; b < 32 / TB_FX_ROWS; ++b) {
+          const uint32_t slot = (fxc + b) & 1u;
+          mbar_wait_ns(&sm->fx_full[w4][slot], ((fxc + b) >> 1) & 1u, 64);
+          if (lane < TB_FX_ROWS && lbl_b[b] >= 0)
+            bulk_reduce_add_f32(myrep + (size_t)lbl_b[b] * d, mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes,
+                                rowbytes);
+          bulk_commit();
+          if (b + 2 < 32 / TB_FX_ROWS) issue_load(b + 2, false);
+        }
+        fxc += 32 / TB_FX_ROWS;
+      }
+      // TB_FIN_ROWS rows in flight per warp: the re-reads come from L2 (~800 cycles each way under load) and this
+      // loop, not the epilogue, set the pace of the whole kernel at 8 rows in flight (hand-off trace)
+      for (int g = 0; g < (H16 ? 0 : 32); g += TB_FIN_ROWS) {
+        if (w4 == 0) TR(10, 4 + 3 * (g / TB_FIN_ROWS));
+        float4 xv[TB_FIN_ROWS];
+#pragma unroll
+        for (int u = 0; u < TB_FIN_ROWS; ++u) {
           const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
           xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
           if (lbl >= 0 && lane * 4 < d) xv[u] = *reinterpret_cast<const float4*>(X + (r0 + g + u) * ld + lane * 4);
         }
+        if (w4 == 0) TR(10, 5 + 3 * (g / TB_FIN_ROWS));
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < TB_FIN_ROWS; ++u) {
           const int lbl = __shfl_sync(0xffffffffu, my_lab, g + u);
           if (lbl >= 0 && lane * 4 < d) red_add_v4(myrep + (size_t)lbl * d + lane * 4, xv[u]);
         }
+        if (w4 == 0) TR(10, 6 + 3 * (g / TB_FIN_ROWS));
       }
       if (my_lab >= 0) {
         cost += (double)my_sc;
@@ -593,6 +662,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
       if (w4 == 0) TR(10, 3);
     }
+    if (H16) bulk_wait_all();  // the reductions read this CTA's shared memory
     if (accumulate) {
       cost = warp_sum(cost);
       unsigned long long tot = nrows;
@@ -698,13 +768,12 @@ static int tcb_cap_from_bytes(size_t bytes, int d) {
 }
 
 static int km_tcb_stages(int d, int filter) {
-  // fp16 filter: stay within the 196 KB shared-memory carve-out so that 32 KB of L1 remain for the ||c||^2 table,
-  // the row re-reads of the finish warps and the few spilled loop counters (else every one is an L2 round trip)
   const int budget = (filter != KM_FILTER_FP16 ? 227 : getenv("B2F_TC_SMEM_KB") ? atoi(getenv("B2F_TC_SMEM_KB"))  // dev knob
-                                                                                 : 195) * 1024;
-  const int left = budget - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES;
+                                                                                 : 227) * 1024;
+  const int left = budget - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES -
+                   (filter == KM_FILTER_FP16 ? TB_CN_BYTES + 4 * 2 * TB_FX_ROWS * d * 4 : 0);
   // a stage holds one centre tile: two 64-k atoms (space for two even when d == 64), fp16: + the ||c||^2 block
-  int s = left / (filter == KM_FILTER_FP16 ? 3 * CHUNK_BYTES : 2 * tb_stage_bytes<KM_FILTER_BF16X3>());
+  int s = left / (filter == KM_FILTER_FP16 ? 2 * CHUNK_BYTES + TB_CN_BYTES : 2 * tb_stage_bytes<KM_FILTER_BF16X3>());
   const int cap = getenv("B2F_TC_STAGES") ? atoi(getenv("B2F_TC_STAGES")) : 4;  // dev knob
   return s > cap ? cap : s;
 }
@@ -750,7 +819,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   if ((rc = make_map_bf16(&m1, pp + (h16 ? P.off_ch16 : P.off_cb1), (uint64_t)k, (uint64_t)d, (uint64_t)d)) != B2F_OK)
     return rc;
   // second map: bf16x3 -> the low bf16 plane; fp16 -> the ||c||^2 plane (64 halves per centre)
-  if (h16) rc = make_map_bf16(&m2, pp + P.off_cnh, (uint64_t)k, (uint64_t)KM_CNH_COLS, (uint64_t)KM_CNH_COLS);
+  if (h16) rc = make_map_b16_sw32(&m2, pp + P.off_cnh, (uint64_t)k, (uint64_t)KM_CNH_COLS, (uint64_t)KM_CNH_COLS);
   else rc = make_map_bf16(&m2, pp + P.off_cb2, (uint64_t)k, (uint64_t)d, (uint64_t)d);
   if (rc != B2F_OK) return rc;
   double* payload = nullptr;
@@ -775,8 +844,9 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
   const int dbg = getenv("B2F_TC_DBG") ? atoi(getenv("B2F_TC_DBG")) : 0;  // dev knob, results invalid when set
   const bool acc_main = accumulate && !(dbg & 4);
   B2F_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcbWs), stream));
-  const size_t tile_bytes = h16 ? 3 * (size_t)CHUNK_BYTES : 2 * (size_t)tb_stage_bytes<KM_FILTER_BF16X3>();
-  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * tile_bytes + sizeof(SmemB) + 64;
+  const size_t tile_bytes = h16 ? 2 * (size_t)CHUNK_BYTES + TB_CN_BYTES : 2 * (size_t)tb_stage_bytes<KM_FILTER_BF16X3>();
+  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * tile_bytes +
+                      (h16 ? TB_CN_BYTES + 4 * 2 * TB_FX_ROWS * (size_t)d * 4 : 0) + sizeof(SmemB) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
   if ((int64_t)grid > ntiles) grid = (int)ntiles;

@@ -89,6 +89,25 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
       "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
       : "memory");
 }
+// plain (non-tensor) bulk copy global -> shared, completion on an mbarrier; bulk reduction shared -> global
+// (element-wise fp32 add performed by the copy engine at L2), completion through the issuing thread's bulk groups
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_reduce_add_f32(float* dst, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst),
+               "r"(smem_u32(src_smem)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the newest N groups of this thread have finished READING their shared-memory source
+template <int N> __device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(
@@ -189,7 +208,7 @@ static inline EncodeTiledFn get_encode_fn() {
 
 // 2-D row-major [rows, cols] tensor (row pitch `pitch` ELEMENTS), box = 128 bytes x 128 rows, 128B swizzle
 static inline int make_map_2d(CUtensorMap* m, const void* base, CUtensorMapDataType dt, int elem_bytes, uint64_t rows,
-                              uint64_t cols, uint64_t pitch, uint32_t box_rows = (uint32_t)TM) {
+                              uint64_t cols, uint64_t pitch, uint32_t box_rows = (uint32_t)TM, int swizzle_bytes = 128) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     b2f_set_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -197,10 +216,11 @@ static inline int make_map_2d(CUtensorMap* m, const void* base, CUtensorMapDataT
   }
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {pitch * (uint64_t)elem_bytes};
-  cuuint32_t box[2] = {(cuuint32_t)(128 / elem_bytes), (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)(swizzle_bytes / elem_bytes), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     b2f_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%llu cols=%llu pitch=%llu)", (int)r,
                   (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)pitch);
@@ -213,4 +233,8 @@ static inline int make_map_f32(CUtensorMap* m, const float* base, uint64_t rows,
 }
 static inline int make_map_bf16(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch) {
   return make_map_2d(m, base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, rows, cols, pitch);
+}
+// 16-bit elements, boxes of 128 rows x 16 elements (32 bytes) in the 32-byte swizzle
+static inline int make_map_b16_sw32(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch) {
+  return make_map_2d(m, base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, rows, cols, pitch, (uint32_t)TM, 32);
 }

@@ -32,6 +32,9 @@ for it in range(first, first + ntiles):
         ev.append((t[9, it, s], "split tile %d %s" % (it, lab)))
     for s, lab in enumerate(("wait a_full", "got partial results", "labels + list done", "accumulated")):
         ev.append((t[10, it, s], "fin   tile %d %s" % (it, lab)))
+    for g in range(4):
+        for s, lab in enumerate(("batch start", "loads issued", "reductions issued")):
+            ev.append((t[10, it, 4 + 3 * g + s], "fin   tile %d batch %d %s" % (it, g, lab)))
 ev = [(c - t0, s) for c, s in ev if c]
 ev.sort()
 for c, s in ev:
