@@ -234,7 +234,9 @@ def b200_arm(args):
     line = {"metric": "kmeans_lloyd_iter_per_s", "value": value, "unit": "iter/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None,
-            "dtype": "bf16x3 filter + tf32x3 re-check -> f32 (sums/cost folded in f64)" if eng.use_ws else
+            "dtype": ("f16 filter + tf32x3 re-check + f64 tail -> f32 sums (folded in f64)"
+                      if eng.use_ws and args.algo in (0, 5) else
+                      "bf16x3 filter + tf32x3 re-check -> f32 (sums/cost folded in f64)") if eng.use_ws else
                      "tf32x3->f32 (sums/cost folded in f64)",
             "data": "synthetic", "config": workload_config(n_total, world), "gpu_launches": launches,
             "clocks": clk.summary(),

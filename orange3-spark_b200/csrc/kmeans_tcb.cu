@@ -246,7 +246,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         for (int kc = 0; kc < KC; ++kc) {
           mbar_wait_ns(&sm->xs_empty[kc], (it & 1) ^ 1, 128);
           mbar_expect_tx(&sm->xs_full[kc], (uint32_t)CHUNK_BYTES);
-          tma_load_2d(xs + (size_t)kc * CHUNK_BYTES, &map_x, kc * 32, (int)(tile * TM), &sm->xs_full[kc]);
+          // the finish warps read the tile again ~2 row tiles later: ask L2 to keep it until then
+          tma_load_2d_hint(xs + (size_t)kc * CHUNK_BYTES, &map_x, kc * 32, (int)(tile * TM), &sm->xs_full[kc],
+                           accumulate ? L2_EVICT_LAST : L2_EVICT_FIRST);
         }
       }
     }
@@ -619,8 +621,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           }
           __syncwarp();
           if (act)
-            bulk_load(mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes, X + (r0 + b * TB_FX_ROWS + lane) * ld,
-                      rowbytes, &sm->fx_full[w4][slot]);
+            bulk_load_hint(mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes,
+                           X + (r0 + b * TB_FX_ROWS + lane) * ld, rowbytes, &sm->fx_full[w4][slot], L2_EVICT_FIRST);
         };
         issue_load(0, true);
         issue_load(1, false);
