@@ -86,6 +86,12 @@ int b2f_pack_columns(const void* const* col_ptrs_dev, const int32_t* col_dtypes_
  * (fp64, accumulated with atomics: zero `out` first; `w` and `shift` may be NULL).       */
 int b2f_colstats(const float* X, int64_t n, int d, int64_t ld, const float* w, const float* shift,
                  double* out, b2f_stream_t stream);
+/* StandardScalerModel.transform (A.6): Y[i, c] = (X[i, c] - shift[c]) * scale[c] for c < d, 0 in the padding columns;
+ * scale / shift: device fp32[d], either may be NULL (1 / 0); Y may be X (in place).  One HBM pass.
+ *   reference: the scaler is listed by orangecontrib/spark/utils/ml_api_utils.py:65-67 and applied through
+ *   transform() at orangecontrib/spark/base/spark_ml_transformer.py:133 (BASELINE config 5)            */
+int b2f_scale_columns(const float* X, float* Y, int64_t n, int d, int64_t ld, const float* scale, const float* shift,
+                      b2f_stream_t stream);
 /* label histogram: hist[c] += sum of w over rows with y == c, c < n_bins (fp64, zero first) */
 int b2f_label_hist(const float* y, const float* w, int64_t n, int n_bins, double* hist, int32_t* bad_flag,
                    b2f_stream_t stream);
@@ -172,6 +178,21 @@ int b2f_lr_multinomial_lossgrad(const float* X, const float* y, const float* w, 
 int b2f_lr_predict(const float* X, int64_t n, int d, int64_t ld, int n_classes, const double* beta,
                    const double* icpt, double threshold, float* raw, float* prob, float* pred,
                    b2f_stream_t stream);
+
+/* ---- evaluators -------------------------------------
+ * Squared-Euclidean silhouette the way pyspark.ml.evaluation.ClusteringEvaluator computes it (per-cluster
+ * statistics, no pairwise distances).
+ *   reference call site: orangecontrib/spark/widgets/ml/spark_ml_evaluation.py:42-55 (module = evaluation, :7,19)
+ * stats: device fp64 [k][d + 2] = S_c | Psi_c | N_c, zeroed by the caller, ACCUMULATED here (fp64 atomics): with
+ * several GPUs every rank adds its shard and the buffer is all-reduced before the score pass.
+ * labels: int32[n] in [0, k); a label outside sets *bad_flag (may be NULL) and the row is skipped.
+ * score: out[0] += sum w s_i, out[1] += sum w over this shard (fp64, zero first); scratch of
+ * b2f_silhouette_scratch_bytes(k, d) bytes.  silhouette = out[0] / out[1] after the all-reduce.             */
+int b2f_silhouette_stats(const float* X, int64_t n, int d, int64_t ld, const int32_t* labels, const float* w, int k,
+                         double* stats, int32_t* bad_flag, b2f_stream_t stream);
+size_t b2f_silhouette_scratch_bytes(int k, int d);
+int b2f_silhouette_score(const float* X, int64_t n, int d, int64_t ld, const int32_t* labels, const float* w, int k,
+                         const double* stats, void* scratch, double* out, b2f_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -47,3 +47,4 @@ from .logreg import (  # noqa: F401
     lr_predict,
 )
 from .optim import LBFGS, OWLQN  # noqa: F401
+from .evaluate import area_under_pr, area_under_roc, multiclass_metrics, silhouette_sqeuclid  # noqa: F401

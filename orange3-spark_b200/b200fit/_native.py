@@ -26,6 +26,10 @@ PROTOTYPES = {
     "b2f_synth_logistic": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i64, _u64, _vp, _vp, _vp, _i32, _vp]),
     "b2f_pack_columns": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _i64, _vp, _vp]),
     "b2f_colstats": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _vp, _vp, _vp]),
+    "b2f_scale_columns": (C.c_int, [_vp, _vp, _i64, _i32, _i64, _vp, _vp, _vp]),
+    "b2f_silhouette_stats": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _vp, _i32, _vp, _vp, _vp]),
+    "b2f_silhouette_scratch_bytes": (_sz, [_i32, _i32]),
+    "b2f_silhouette_score": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _vp, _i32, _vp, _vp, _vp, _vp]),
     "b2f_label_hist": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp]),
     "b2f_kmeans_prep_bytes": (_sz, [_i32, _i32]),
     "b2f_kmeans_acc_bytes": (_sz, [_i32, _i32]),

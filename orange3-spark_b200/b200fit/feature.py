@@ -255,7 +255,10 @@ class StandardScalerModel(Model):
             scale[: X.d] = np.where(self.std != 0, 1.0 / np.where(self.std != 0, self.std, 1.0), 0.0)
         if self.getOrDefault("withMean"):
             shift[: X.d] = self.mean
-        sc = torch.from_numpy(scale.astype(np.float32)).to(X.data.device)
-        sh = torch.from_numpy(shift.astype(np.float32)).to(X.data.device)
-        Y = (X.data - sh) * sc if self.getOrDefault("withMean") else X.data * sc
+        sc = torch.from_numpy(scale[: X.d].astype(np.float32)).to(X.data.device)
+        sh = torch.from_numpy(shift[: X.d].astype(np.float32)).to(X.data.device) if self.getOrDefault("withMean") else None
+        Y = torch.empty_like(X.data)
+        N.check(N.lib().b2f_scale_columns(N.ptr(X.data), N.ptr(Y), X.n, X.d, X.ld, N.ptr(sc), N.ptr(sh),
+                                          N.stream_ptr()), "b2f_scale_columns")
+        torch.cuda.current_stream().synchronize()  # sc / sh are temporaries of this call
         return frame.withColumn(out, DeviceMatrix(Y, X.d, X.row0))

@@ -174,6 +174,45 @@ extern "C" int b2f_colstats(const float* X, int64_t n, int d, int64_t ld, const 
   return B2F_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// StandardScalerModel.transform (A.6): Y = (X - shift) * scale per column; one HBM pass, 16-byte accesses.
+// Y may be X itself.  Padding columns d..ld-1 are written as zeros.
+// ---------------------------------------------------------------------------------------------
+__global__ void scale_columns_kernel(const float* __restrict__ X, float* Y, int64_t n, int d, int64_t ld,
+                                     const float* __restrict__ scale, const float* __restrict__ shift) {
+  const int64_t ld4 = ld >> 2;
+  const int64_t total = n * ld4;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % ld4) * 4;
+    float4 v = reinterpret_cast<const float4*>(X)[i];
+    float sc[4], sh[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      sc[u] = (c + u < d) ? (scale ? __ldg(scale + c + u) : 1.f) : 0.f;
+      sh[u] = (shift && c + u < d) ? __ldg(shift + c + u) : 0.f;
+    }
+    v.x = (v.x - sh[0]) * sc[0];
+    v.y = (v.y - sh[1]) * sc[1];
+    v.z = (v.z - sh[2]) * sc[2];
+    v.w = (v.w - sh[3]) * sc[3];
+    reinterpret_cast<float4*>(Y)[i] = v;
+  }
+}
+
+extern "C" int b2f_scale_columns(const float* X, float* Y, int64_t n, int d, int64_t ld, const float* scale,
+                                 const float* shift, b2f_stream_t stream) {
+  B2F_REQUIRE(X && Y, "b2f_scale_columns: null pointer");
+  B2F_REQUIRE(d > 0 && n >= 0 && ld >= d && ld % 4 == 0, "b2f_scale_columns: need d > 0, ld >= d, ld %% 4 == 0");
+  B2F_REQUIRE(((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(Y)) & 15) == 0,
+              "b2f_scale_columns: X and Y must be 16-byte aligned");
+  if (n == 0) return B2F_OK;
+  const int64_t want = (n * (ld >> 2) + 255) / 256;
+  const int64_t cap = (int64_t)b2f_sm_count() * 16;
+  scale_columns_kernel<<<(unsigned)(want < cap ? want : cap), 256, 0, b2f_cs(stream)>>>(X, Y, n, d, ld, scale, shift);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
 extern "C" int b2f_label_hist(const float* y, const float* w, int64_t n, int n_bins, double* hist, int32_t* bad_flag,
                               b2f_stream_t stream) {
   B2F_REQUIRE(y && hist, "b2f_label_hist: null pointer");

@@ -85,3 +85,27 @@ def press_apply(cls, in_df, edits=None, objects=None):
     for pname, obj in (objects or {}).items():
         param_map[ForeignParam(inst, pname, "")] = obj
     return inst.fit(in_df, params=param_map)
+
+
+def list_evaluators(module):
+    """reference: orangecontrib/spark/utils/ml_api_utils.py:59-62"""
+    return {n: c for n, c in inspect.getmembers(module, inspect.isclass)
+            if "evaluate" in dir(c) and not inspect.isabstract(c)
+            and "java_model" not in inspect.getfullargspec(c).args and not n.startswith("Java") and n != "Evaluator"}
+
+
+def press_apply_evaluator(cls, in_df, edits=None):
+    """Simulates 'Apply' on the Evaluation widget (reference: orangecontrib/spark/widgets/ml/spark_ml_evaluation.py:42-55):
+    metric names come out of the metricName doc text, one call per metric with metricName overridden in the map."""
+    _, _, table = describe(cls)
+    metric_names = table["metricName"][2].split("(")[-1].replace(")", "").split("|")
+    inst = cls()
+    param_map = {}
+    for pname, meta in table.items():
+        text = str(meta[1]) if not edits or pname not in edits else str(edits[pname])
+        param_map[ForeignParam(inst, pname, "")] = text_to_value(text)
+    values = {}
+    for metric in metric_names:
+        param_map[ForeignParam(inst, "metricName", "")] = metric
+        values[metric] = inst.apply(in_df, param_map)
+    return values

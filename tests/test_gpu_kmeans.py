@@ -265,3 +265,25 @@ def test_standard_scaler_then_kmeans_pipeline_cfg5_shape():
     np.testing.assert_allclose(np.array(m.clusterCenters()), ref["centers"], rtol=1e-5, atol=1e-5 * sc)
     np.testing.assert_allclose(m.summary.costHistory, ref["cost_hist"], rtol=1e-5)
     assert m.summary.clusterSizes == [int(c) for c in ref["counts_hist"][-1]]
+
+
+@pytest.mark.parametrize("n,d", [(1, 1), (1000, 3), (4099, 64), (777, 130)])
+def test_scale_columns_matches_oracle_also_in_place(n, d):
+    """b2f_scale_columns (StandardScalerModel.transform, A.6): (x - shift) * scale, padding columns zero."""
+    N, G = _imports()
+    L = N.lib()
+    rng = np.random.default_rng(n + d)
+    Xh = (rng.normal(size=(n, d)) * 3 + 1).astype(np.float32)
+    X, _, ld = G.upload_matrix(Xh)
+    mean, std = oracle.standard_scaler_fit(Xh.astype(np.float64)) if n > 1 else (Xh[0].astype(np.float64), np.ones(d))
+    inv = np.where(std != 0, 1.0 / np.where(std != 0, std, 1.0), 0.0)
+    sc = torch.from_numpy(inv.astype(np.float32)).to(G.dev())
+    sh = torch.from_numpy(mean.astype(np.float32)).to(G.dev())
+    Y = torch.full_like(X, 7.0)
+    N.check(L.b2f_scale_columns(N.ptr(X), N.ptr(Y), n, d, ld, N.ptr(sc), None, G.stream()), "scale")
+    ref = Xh.astype(np.float64) * inv
+    np.testing.assert_allclose(Y.cpu().numpy()[:, :d], ref, rtol=2e-7, atol=1e-7)
+    assert (Y.cpu().numpy()[:, d:] == 0).all()
+    N.check(L.b2f_scale_columns(N.ptr(X), N.ptr(X), n, d, ld, N.ptr(sc), N.ptr(sh), G.stream()), "scale in place")
+    ref = (Xh.astype(np.float32) - mean.astype(np.float32)).astype(np.float64) * inv
+    np.testing.assert_allclose(X.cpu().numpy()[:, :d], ref, rtol=3e-7, atol=1e-6)

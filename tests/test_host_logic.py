@@ -53,6 +53,19 @@ def test_estimator_discovery_and_description():
     assert all(p.default is not inspect.Parameter.empty for p in sig.parameters.values())
 
 
+def test_evaluator_discovery_and_metric_names():
+    ev = fw.list_evaluators(b200fit.evaluation)
+    assert set(ev) == {"ClusteringEvaluator", "BinaryClassificationEvaluator", "MulticlassClassificationEvaluator"}
+    for cls, metrics in ((b200fit.evaluation.ClusteringEvaluator, ["silhouette"]),
+                         (b200fit.evaluation.BinaryClassificationEvaluator, ["areaUnderROC", "areaUnderPR"]),
+                         (b200fit.evaluation.MulticlassClassificationEvaluator,
+                          ["f1", "accuracy", "weightedPrecision", "weightedRecall"])):
+        _, doc, table = fw.describe(cls)
+        assert doc and all(len(v) == 3 and v[2] for v in table.values())
+        assert table["metricName"][2].split("(")[-1].replace(")", "").split("|") == metrics
+        assert hasattr(cls(), "apply") and cls().isLargerBetter()
+
+
 def test_text_coercion_matches_gui_rules():
     assert fw.text_to_value("None") is None and fw.text_to_value("") is None
     assert fw.text_to_value("True") is True and fw.text_to_value("False") is False

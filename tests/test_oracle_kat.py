@@ -135,3 +135,29 @@ def test_assemble_and_scaler():
     T = oracle.standard_scaler_transform(Z, mean, std)
     np.testing.assert_allclose(T[:, 0], Z[:, 0] / std[0])
     assert (T[:, 1] == 0).all()
+
+
+
+def test_evaluator_restatements_against_scikit_learn():
+    """Pins oracle/evaluate.py: Spark's statistics form of the squared-Euclidean silhouette equals the pairwise
+    definition; exact ROC area and the weighted multiclass metrics equal scikit-learn's."""
+    from sklearn.metrics import (accuracy_score, f1_score, precision_score, recall_score, roc_auc_score,
+                                 silhouette_score)
+
+    rng = np.random.default_rng(0)
+    lab = rng.integers(0, 5, 600)
+    X = rng.normal(size=(600, 7)) + lab[:, None] * 1.5
+    assert oracle.silhouette_sqeuclid(X, lab) == pytest.approx(silhouette_score(X, lab, metric="sqeuclidean"), rel=1e-12)
+    y = (rng.uniform(size=600) < 0.4).astype(float)
+    sc = np.round(y * 0.8 + rng.normal(size=600), 1)  # many tied scores
+    assert oracle.area_under_roc(sc, y) == pytest.approx(roc_auc_score(y, sc), rel=1e-12)
+    w = rng.uniform(0.5, 2.0, 600)
+    assert oracle.area_under_roc(sc, y, w) == pytest.approx(roc_auc_score(y, sc, sample_weight=w), rel=1e-12)
+    # PR area: hand-checked 4-point case, curve (0,1) (0.5,1) (0.5,0.5) (1,2/3) (1,0.5)
+    assert oracle.area_under_pr([0.9, 0.8, 0.7, 0.6], [1, 0, 1, 0]) == pytest.approx(0.5 * 1.0 + 0.5 * (0.5 + 2 / 3) / 2)
+    p, t = rng.integers(0, 4, 600), rng.integers(0, 4, 600)
+    m = oracle.multiclass_metrics(p, t)
+    assert m["accuracy"] == pytest.approx(accuracy_score(t, p))
+    assert m["f1"] == pytest.approx(f1_score(t, p, average="weighted"))
+    assert m["weightedPrecision"] == pytest.approx(precision_score(t, p, average="weighted"))
+    assert m["weightedRecall"] == pytest.approx(recall_score(t, p, average="weighted"))
