@@ -111,8 +111,10 @@ def test_tc_rejects_unsupported_shapes():
         G.kmeans_step_raw(X[:, :32].contiguous(), 100, 32, 32, np.zeros((100, 32)), N.KM_TC3)
 
 
+# (k / 128 odd: the two MMA issuers, the two epilogue warps per quarter and the three accumulators then fall out of
+# step with the row tiles; 45000 rows = 352 row tiles: several per CTA)
 TCB_SHAPES = [(128, 64, 128), (1000, 64, 128), (5000, 128, 256), (4099, 128, 1024), (20000, 128, 128),
-              (30000, 64, 256)]
+              (30000, 64, 256), (3000, 64, 384), (45000, 128, 640), (40000, 64, 128)]
 
 
 FILTERS = ["TCB", "TCH"]  # bf16x3 filter (three MMAs per product) / fp16 filter (one MMA, scaled operands)
