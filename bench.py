@@ -265,6 +265,9 @@ def b200_arm(args):
     if not args.no_lr:
         line["lr_multinomial"] = lrm_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, DeviceMatrix,
                                          shard_bounds, max_over_ranks, sync_all)
+    if not args.no_lr:
+        line["pipeline_cfg5"] = cfg5_leg(args, torch, N, L, comm, rank, world, dev, pk, DeviceMatrix, ColumnarFrame,
+                                         shard_bounds, max_over_ranks, sync_all)
     if rank == 0 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(n_total)
     if rank == 0:
@@ -357,6 +360,75 @@ def lr_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, Devi
                          "traffic": measured_traffic("lr_binary_kernel", n), "kernel": "lr_binary_kernel", "algorithmic_bytes_per_launch": bytes_pass,
                          "peak_source": pk["src"]},
             "check": {"loss": float(p[d + 1] / p[d + 2]), "weight_sum": float(p[d + 2])}}
+
+
+def cfg5_leg(args, torch, N, L, comm, rank, world, dev, pk, DeviceMatrix, ColumnarFrame, shard_bounds, max_over_ranks,
+             sync_all):
+    """BASELINE configs[4]: StandardScaler -> KMeans k=256 on 200M x 64 (row-sharded): the scaler's two HBM passes
+    (column statistics, x / sigma) timed once each, then Lloyd iterations on the scaled matrix."""
+    import numpy as np
+
+    from b200fit._kmeans_init import init_random
+    from b200fit.clustering import CudaLloydEngine
+    from b200fit.feature import StandardScaler
+
+    n_total = 200_000_000 if not args.rows else max(args.rows, 1)
+    d, k = 64, 256
+    lo, hi = shard_bounds(n_total, rank, world)
+    n = hi - lo
+    rng = np.random.default_rng(SEED + 5)
+    col_scale = np.exp(rng.uniform(np.log(0.1), np.log(10.0), size=d)).astype(np.float32)
+    cs_d = torch.from_numpy(col_scale).to(dev)  # keep alive across the call
+    Xt = torch.empty((n, d), dtype=torch.float32, device=dev)
+    N.check(L.b2f_synth_mixture(N.ptr(Xt), n, lo, d, d, SEED + 5, k, 2.0, N.ptr(cs_d), N.stream_ptr()),
+            "b2f_synth_mixture")
+    torch.cuda.synchronize()
+    frame = ColumnarFrame({"raw": DeviceMatrix(Xt, d, lo)})
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    sync_all()
+    ev[0].record()
+    sm = StandardScaler(inputCol="raw", outputCol="features").fit(frame)
+    ev[1].record()
+    scaled = sm.transform(frame)
+    ev[2].record()
+    sync_all()
+    fit_ms, tr_ms = max_over_ranks(ev[0].elapsed_time(ev[1])), max_over_ranks(ev[1].elapsed_time(ev[2]))
+    del Xt, frame
+    torch.cuda.empty_cache()
+    X = scaled.col("features")
+    C0 = init_random(X, n_total, k, SEED + 5, comm)
+    eng = CudaLloydEngine(X, k)
+    eng.set_centers(C0)
+
+    def iteration():
+        payload = eng.step()
+        comm.all_reduce_sum(payload)
+        eng.finalize_async(payload, 0.0)
+
+    for _ in range(args.warmup):
+        iteration()
+    sync_all()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(args.steps):
+        iteration()
+    t1.record()
+    sync_all()
+    ms = max_over_ranks(t0.elapsed_time(t1)) / args.steps
+    flops = 2.0 * n * k * d
+    achieved = flops / (ms * 1e-3) / 1e12
+    rows_after = eng.rows_counted(eng.payload)
+    return {"metric": "kmeans_lloyd_iter_per_s", "value": 1e3 / ms, "unit": "iter/s", "ms_per_step": ms,
+            "config": {"workload": "StandardScaler -> KMeans k=256 on synthetic %dx64 fp32 (BASELINE configs[4])"
+                                   % n_total, "rows": n_total, "d": d, "k": k},
+            "scaler": {"fit_ms": fit_ms, "transform_ms": tr_ms,
+                       "fit_gbs": n * d * 4.0 / (fit_ms * 1e-3) / 1e9, "transform_gbs": n * d * 8.0 / (tr_ms * 1e-3) / 1e9,
+                       "note": "fit = column statistics pass (+ host sync), transform = b2f_scale_columns"},
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": pk["tensor"], "unit": "TFLOP/s",
+                         "frac": achieved / pk["tensor"], "traffic": None, "kernel": "b2f_kmeans_step_ws (whole step)",
+                         "algorithmic_flops_per_launch": flops, "peak_source": pk["src"] + " bf16 sustained"},
+            "check": {"rows_accumulated_last_iter": rows_after, "std_first_cols": [float(v) for v in sm.std[:3]],
+                      "col_scale_first_cols": [float(v) for v in col_scale[:3]]}}
 
 
 def lrm_leg(args, torch, N, L, comm, rank, world, dev, pk, CudaLogRegEngine, DeviceMatrix, shard_bounds,
