@@ -67,59 +67,93 @@ __global__ void __launch_bounds__(256) pack_columns_kernel(const void* const* __
   if (bad_flag && bad) atomicExch(bad_flag, 1);
 }
 
-// grid.y = chunks of 256 columns; CTA = 256 threads = 64 float4 column groups x 4 row lanes.
+// grid.y = chunks of 256 columns.  A CTA's 256 threads are laid out as RL row lanes x G float4 column groups, with
+// G = the number of column groups this chunk really has (16 at d = 64) and RL = 256 / G: every thread has a column
+// to read whatever d is (with a fixed 64 x 4 layout three quarters of the threads idled at d = 64 and the pass ran
+// at 12 % of the HBM peak).  Four rows in flight per thread.
 __global__ void __launch_bounds__(256) colstats_kernel(const float* __restrict__ X, int64_t n, int d, int64_t ld,
                                                        const float* __restrict__ w, const float* __restrict__ shift,
                                                        double* __restrict__ out) {
-  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
-  const int c = (blockIdx.y * 64 + tx) * 4;
-  const bool active = c < d;
+  const int col0 = blockIdx.y * 256;
+  const int G = min(64, (d - col0 + 3) >> 2);
+  const int RL = 256 / G;
+  const int tx = threadIdx.x % G, ty = threadIdx.x / G;
+  const int c = col0 + tx * 4;
+  const bool active = ty < RL;
   float sh[4] = {0.f, 0.f, 0.f, 0.f};
   if (active && shift)
     for (int j = 0; j < 4; ++j)
       if (c + j < d) sh[j] = shift[c + j];
   double s1[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0}, sw = 0, sw2 = 0;
-  for (int64_t r = (int64_t)blockIdx.x * 4 + ty; r < n; r += (int64_t)gridDim.x * 4) {
-    const float wi = w ? w[r] : 1.f;
-    if (active) {
-      const float4 v = ldg_stream(reinterpret_cast<const float4*>(X + r * ld + c));
-      const float xs[4] = {v.x, v.y, v.z, v.w};
+  const int64_t stride = (int64_t)gridDim.x * RL;
+  if (active) {
+    for (int64_t r0 = (int64_t)blockIdx.x * RL + ty; r0 < n; r0 += 4 * stride) {
+      float4 v[4];
+      float wi[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const double t = (double)xs[j] - (double)sh[j];
-        const double wt = (double)wi * t;
-        s1[j] += wt;
-        s2[j] += wt * t;
+      for (int u = 0; u < 4; ++u) {
+        const int64_t r = r0 + u * stride;
+        v[u] = make_float4(sh[0], sh[1], sh[2], sh[3]);  // contributes exactly zero
+        wi[u] = 0.f;
+        if (r < n) {
+          v[u] = ldg_stream(reinterpret_cast<const float4*>(X + r * ld + c));
+          wi[u] = w ? w[r] : 1.f;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float xs[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const double t = (double)xs[j] - (double)sh[j];
+          const double wt = (double)wi[u] * t;
+          s1[j] += wt;
+          s2[j] += wt * t;
+        }
+        if (blockIdx.y == 0 && tx == 0) {
+          sw += (double)wi[u];
+          sw2 += (double)wi[u] * (double)wi[u];
+        }
       }
     }
-    if (blockIdx.y == 0 && tx == 0) {
-      sw += (double)wi;
-      sw2 += (double)wi * (double)wi;
+  }
+  __shared__ double red[256][8];  // [ty * G + tx]
+  __shared__ double redw[256][2];
+  if (active) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      red[ty * G + tx][j] = s1[j];
+      red[ty * G + tx][4 + j] = s2[j];
+    }
+    if (tx == 0) {
+      redw[ty][0] = sw;
+      redw[ty][1] = sw2;
     }
   }
-  __shared__ double red[4][64][8];
-  __shared__ double redw[4][2];
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    red[ty][tx][j] = s1[j];
-    red[ty][tx][4 + j] = s2[j];
-  }
-  if (tx == 0) {
-    redw[ty][0] = sw;
-    redw[ty][1] = sw2;
-  }
   __syncthreads();
-  if (ty == 0 && active) {
+  if (ty == 0) {
+    double t1[4] = {0, 0, 0, 0}, t2[4] = {0, 0, 0, 0};
+    for (int y = 0; y < RL; ++y)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        t1[j] += red[y * G + tx][j];
+        t2[j] += red[y * G + tx][4 + j];
+      }
 #pragma unroll
     for (int j = 0; j < 4; ++j)
       if (c + j < d) {
-        atomicAdd(out + c + j, red[0][tx][j] + red[1][tx][j] + red[2][tx][j] + red[3][tx][j]);
-        atomicAdd(out + d + c + j, red[0][tx][4 + j] + red[1][tx][4 + j] + red[2][tx][4 + j] + red[3][tx][4 + j]);
+        atomicAdd(out + c + j, t1[j]);
+        atomicAdd(out + d + c + j, t2[j]);
       }
   }
   if (blockIdx.y == 0 && threadIdx.x == 0) {
-    atomicAdd(out + 2 * d, redw[0][0] + redw[1][0] + redw[2][0] + redw[3][0]);
-    atomicAdd(out + 2 * d + 1, redw[0][1] + redw[1][1] + redw[2][1] + redw[3][1]);
+    double a = 0, q = 0;
+    for (int y = 0; y < RL; ++y) {
+      a += redw[y][0];
+      q += redw[y][1];
+    }
+    atomicAdd(out + 2 * d, a);
+    atomicAdd(out + 2 * d + 1, q);
   }
 }
 
@@ -166,7 +200,9 @@ extern "C" int b2f_colstats(const float* X, int64_t n, int d, int64_t ld, const 
   if (n == 0) return B2F_OK;
   dim3 grid;
   grid.y = (d + 255) / 256;
-  int64_t want = (n + 3) / 4;
+  const int g0 = d >= 256 ? 64 : (d + 3) / 4;        // column groups of the first chunk -> row lanes per CTA
+  const int rows_per_sweep = (256 / g0) * 4;          // four rows in flight per thread
+  int64_t want = (n + rows_per_sweep - 1) / rows_per_sweep;
   int64_t cap = (int64_t)b2f_sm_count() * 8 / grid.y + 1;
   grid.x = (unsigned)(want < cap ? want : cap);
   colstats_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(X, n, d, ld, w, shift, out);
