@@ -119,7 +119,7 @@ int b2f_kmeans_step(const float* X, int64_t n, int d, int64_t ld, const float* w
                     void* acc, int32_t* labels, int algo, b2f_stream_t stream);
 /* Same pass with a caller-provided workspace (b2f_kmeans_ws_bytes(n, k, d) bytes, 256-byte aligned),
  * which enables B2F_KM_TCB / B2F_KM_TCH: rows whose label the low-precision filter pass cannot certify
- * are listed in the workspace, gathered and re-assigned by the 3xTF32 kernel.  The list holds n/8 rows; if
+ * are listed in the workspace, gathered and re-assigned by the 3xTF32 kernel.  The list holds n/5 rows; if
  * more rows are uncertain the excess is DROPPED and the payload's row count (last entry) comes out below
  * n -- the caller must then redo the pass with B2F_KM_TC3.  B2F_KM_AUTO picks TCH when the shape allows it
  * and labels / ws are given, else behaves like b2f_kmeans_step.  Same reference call site as above.    */

@@ -755,7 +755,7 @@ static TcbWsLayout tcb_ws_layout(int cap, int d) {
   return L;
 }
 static int tcb_cap_for_rows(int64_t n) {
-  int64_t c = (n / 8 + TM - 1) / TM * TM;  // room for 1 row in 8
+  int64_t c = (n / 5 + TM - 1) / TM * TM;  // room for 1 row in 5 (cfg 2 lists 5-9.5 % with random initial centres)
   if (c < 4096) c = 4096;
   if (c > (1 << 30)) c = 1 << 30;
   return (int)c;
