@@ -610,17 +610,24 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         for (int b = 0; b < 32 / TB_FX_ROWS; ++b) lbl_b[b] = __shfl_sync(0xffffffffu, my_lab, b * TB_FX_ROWS + u);
         auto issue_load = [&](int b, bool newest_may_pend) {
           const uint32_t slot = (fxc + b) & 1u;
+          const bool merged = ld == d;  // the batch's rows are one contiguous block: one copy instead of eight
+          const int64_t rb = r0 + b * TB_FX_ROWS;
+          const int nlive = (int)max((int64_t)0, min((int64_t)TB_FX_ROWS, n - rb));
           const bool act = lane < TB_FX_ROWS && lbl_b[b] >= 0;
           const unsigned m = __ballot_sync(0xffffffffu, act);
           // the reduction that read this slot two batches ago must be done with it
           if (newest_may_pend) bulk_wait_read<1>();
           else bulk_wait_read<0>();
           if (lane == 0) {
-            if (m) mbar_expect_tx(&sm->fx_full[w4][slot], (uint32_t)__popc(m) * rowbytes);
+            const uint32_t bytes = merged ? (m ? (uint32_t)nlive * rowbytes : 0u) : (uint32_t)__popc(m) * rowbytes;
+            if (bytes) mbar_expect_tx(&sm->fx_full[w4][slot], bytes);
             else mbar_arrive(&sm->fx_full[w4][slot]);
+            if (merged && bytes)
+              bulk_load_hint(mybuf + (size_t)slot * TB_FX_ROWS * rowbytes, X + rb * ld, bytes, &sm->fx_full[w4][slot],
+                             L2_EVICT_FIRST);
           }
           __syncwarp();
-          if (act)
+          if (act && !merged)
             bulk_load_hint(mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes,
                            X + (r0 + b * TB_FX_ROWS + lane) * ld, rowbytes, &sm->fx_full[w4][slot], L2_EVICT_FIRST);
         };
