@@ -5,14 +5,19 @@
 //   softmax / loss / (P - Y) per row (thread == row), written to shared memory as bf16 pairs
 //   GEMM2  G^T[d x 32]       += X_tile^T[d x 128] . (P - Y)[128 x 32]   tcgen05 kind::f16, bf16x3,
 //                                                                 A = X^T read MN-major from smem
+//          as x1 . [p1 | p2] (one N = 64 instruction, so x1 is read from shared memory once) + x2 . p1
 // X is streamed from HBM once (GEMM1) and re-read from L2 for GEMM2; G^T stays in tensor memory for the
-// CTA's lifetime.  Replaces the treeAggregate of MultinomialLogisticBlockAggregator;
+// CTA's lifetime.
+// What bounds it (hand-off trace, tools/lr_trace.py): shared-memory bandwidth.  Per 128 x 512 tile the shared
+// memory moves ~1.8 MB (TMA writes 512 KB for the two passes, split-warp loads 512 KB, bf16 stores 256 KB, GEMM2
+// operand reads 256 + 96 KB, GEMM1 W reads 192 KB) = 14 600 cycles at 128 B/clk of the 18 600 measured per tile.  Replaces the treeAggregate of MultinomialLogisticBlockAggregator;
 //   reference call site: orangecontrib/spark/base/spark_ml_estimator.py:22 with module = classification
 //   (orangecontrib/spark/widgets/ml/spark_ml_classification.py:15).
 //
 // CTA = 512 threads, persistent, one per SM:
-//   warp 0  X producer (TMA chunks of 128 rows x 32 floats): GEMM1 chunks of tile t+1, then GEMM2 chunks of t
-//   warp 1  MMA issuer (software pipelined: GEMM1(t+1) is issued before GEMM2(t))
+//   warp 0  X producer (TMA chunks of 128 rows x 32 floats): GEMM1 chunks of tile t+1 and GEMM2 chunks of t,
+//           in the order lt_phase() fixes for all three of producer, split warps and MMA issuer
+//   warp 1  MMA issuer (software pipelined: GEMM1(t+1) is issued before / between the blocks of GEMM2(t))
 //   warp 2  W producer (TMA, [32 classes x 32 k] of W_hi and W_lo per chunk)
 //   warp 3  TMEM allocator
 //   warps 4-7   softmax epilogue (thread == row)
@@ -20,13 +25,24 @@
 //               shared-memory operand tile (GEMM2); two groups of 4 warps (thread == row) alternate chunks
 #include <cuda_bf16.h>
 
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
 #include "tc_common.cuh"
 
 namespace {
 
 constexpr int LT_THREADS = 512;
 constexpr int LT_SPLIT_THREADS = 256;
-constexpr bool LT_PIPELINED = true;  // true: issue GEMM1(t+1) before GEMM2(t) (keeps two tiles per SM alive in L2)
+// Both switches are on in the product; -DLT_INTERLEAVE=0 / -DLT_PCAT=0 rebuild the earlier kernel for comparison
+// (20M x 512, 20 classes: 12.97 ms with both off, 11.68 interleave only, 12.95 [p1|p2] only, 10.84 with both).
+#ifndef LT_INTERLEAVE
+#define LT_INTERLEAVE 1  // the last 2 (FB - 1) GEMM1 chunks of tile t+1 go between the GEMM2 blocks of tile t (see lt_phase)
+#endif
+#ifndef LT_PCAT
+#define LT_PCAT 1        // GEMM2 reads x1 once against [p1 | p2] (N = 64) instead of twice (N = 32 each)
+#endif
 constexpr int LT_NP = 32;          // classes padded to the MMA N
 constexpr int LT_XS = 6;           // X staging slots (16 KB each); must stay a multiple of the number of split groups (2):
                                    // a slot is then always consumed by the same group and its parity waits cannot alias
@@ -35,12 +51,21 @@ constexpr int LT_WSTAGE = 2 * LT_NP * 128;
 // tensor memory columns
 constexpr uint32_t LT_TMEM_COLS = 512;
 constexpr uint32_t LT_D1 = 0;      // margins, 2 buffers x 32 columns
-constexpr uint32_t LT_A1 = 64;     // GEMM1 operand ring: 4 slots x (32 hi + 32 lo) columns
-constexpr uint32_t LT_G = 320;     // G^T: d/128 blocks x 32 columns (features on lanes)
+constexpr uint32_t LT_A1 = 64;     // GEMM1 operand ring: LT_A1_SLOTS slots x (32 hi + 32 lo) columns
+constexpr uint32_t LT_A1_SLOTS = LT_PCAT ? 3 : 4;
+constexpr uint32_t LT_G = LT_A1 + LT_A1_SLOTS * 64;  // G^T: d/128 blocks x LT_GW columns (features on lanes)
+constexpr uint32_t LT_GW = LT_PCAT ? 64 : 32;        // LT_PCAT: columns 0-31 = x1.p1 + x2.p1, columns 32-63 = x1.p2
+static_assert(LT_G + 4 * LT_GW <= LT_TMEM_COLS, "tensor memory budget");
+// (P - Y) operand tile in shared memory, per buffer 16 KB: bf16 pieces p1, p2, each two K atoms (64 rows of X) of
+// 32 class rows x 128 B.  LT_PCAT puts p2's class rows right behind p1's inside an atom so that one N = 64 operand
+// covers both
+constexpr uint32_t LT_PY_ATOM = LT_PCAT ? 8192 : 4096;  // bytes between the two K atoms of one piece
+constexpr uint32_t LT_PY_P2 = LT_PCAT ? 4096 : 8192;    // byte offset of p2 relative to p1
 // GEMM1: kind::tf32, A (TMEM) and B K-major, M = 128, N = 32
 constexpr uint32_t IDESC_G1 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(LT_NP >> 3) << 17) | (8u << 24);
 // GEMM2: kind::f16 bf16, A MN-major (bit 15), B K-major, M = 128, N = 32
 constexpr uint32_t IDESC_G2 = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | ((uint32_t)(LT_NP >> 3) << 17) | (8u << 24);
+constexpr uint32_t IDESC_G2_N64 = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | ((uint32_t)(64 >> 3) << 17) | (8u << 24);
 
 struct SmemL {
   uint64_t xs_full[LT_XS], xs_empty[LT_XS];
@@ -62,14 +87,47 @@ __device__ __forceinline__ void mma_tf32_ts(uint32_t d, uint32_t a, uint64_t b, 
       "r"(a), "l"(b), "r"(IDESC_G1), "r"(acc)
       : "memory");
 }
-__device__ __forceinline__ void mma_bf16_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t acc) {
+__device__ __forceinline__ void mma_bf16_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
   asm volatile(
       "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
-      "l"(a), "l"(b), "r"(IDESC_G2), "r"(acc)
+      "l"(a), "l"(b), "r"(idesc), "r"(acc)
       : "memory");
 }
+// Work order of one phase, shared by the X producer, the split warps and the MMA issuer: the GEMM1 chunks of one
+// tile (has_g1) and the GEMM2 blocks of the tile before it (has_g2).  Plain order: all chunks, then all blocks.
+// LT_INTERLEAVE: the last 2 (FB - 1) chunks are held back and issued two at a time after each block but the last, so
+// that the split warps have work while a block's MMAs drain (the operand tile of GEMM2 is single-buffered), and the
+// softmax of the GEMM1 tile still has the whole last block plus the next phase's leading chunks to hide behind.
+template <class F1, class F2>
+__device__ __forceinline__ void lt_phase(int KC, int FB, bool has_g1, bool has_g2, F1&& g1_chunk, F2&& g2_block) {
+  const int pre = (LT_INTERLEAVE && has_g1 && has_g2) ? KC - 2 * (FB - 1) : KC;
+  int c = 0;
+  if (has_g1)
+    for (; c < pre; ++c) g1_chunk(c);
+  if (has_g2)
+    for (int fb = 0; fb < FB; ++fb) {
+      g2_block(fb);
+      if (has_g1)
+        for (int e = 0; e < 2 && c < KC; ++e, ++c) g1_chunk(c);
+    }
+}
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// dev tracing (build with -DLT_TRACE, run with B2F_LR_TRACE=<file>; tools/lr_trace.py prints it): block 0 stamps
+// clock64() at the hand-offs of its first LTR_TILES row tiles.  Compiled out of the product library.
+#ifdef LT_TRACE
+constexpr int LTR_TILES = 48, LTR_SLOTS = 16, LTR_ROLES = 6;  // mma | softmax warp 4 | split group 0 | split group 1 | X producer | inside a chunk (warp 8)
+__device__ unsigned long long lt_trace[LTR_ROLES * LTR_TILES * LTR_SLOTS];
+#define LTR(role, it, slot)                                                                       \
+  do {                                                                                            \
+    if (blockIdx.x == 0 && lane == 0 && (it) >= 0 && (it) < LTR_TILES)                            \
+      lt_trace[((role) * LTR_TILES + (it)) * LTR_SLOTS + (slot)] = (unsigned long long)clock64(); \
+    asm volatile("" ::: "memory");                                                                \
+  } while (0)
+#else
+#define LTR(role, it, slot) do {} while (0)
+#endif
 
 }  // namespace
 
@@ -129,8 +187,9 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
   tc_fence_after();
   const uint32_t tmem_base = sm->tmem_base;
 
-  // Work order shared by the producer, the split warps and the MMA issuer:
-  //   G1(0), then for t = 0 .. my_tiles-1:  G1(t+1) (if any), G2(t)
+  // Work order shared by the producer, the split warps and the MMA issuer (lt_phase):
+  //   G1(0), then for t = 0 .. my_tiles-1:  G1(t+1) (if any) and G2(t)
+  // GEMM1 of the next tile is issued before GEMM2 of this one, so two tiles per SM are alive in L2
   if (warp == 0) {
     // ===================== X producer =====================
     if (lane == 0) {
@@ -144,16 +203,20 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
         tma_load_2d_hint(xs + (size_t)slot * CHUNK_BYTES, &map_x, col0, (int)(tile * TM), &sm->xs_full[slot], policy);
         ++g;
       };
-      for (int t = (LT_PIPELINED ? -1 : 0); t < my_tiles; ++t) {
-        const int t1 = LT_PIPELINED ? t + 1 : t;
-        if (t1 < my_tiles) {
-          const int64_t tile = blockIdx.x + (int64_t)t1 * gridDim.x;
-          for (int c = 0; c < KC; ++c) load_chunk(tile, c * 32, L2_EVICT_LAST);
-        }
-        if (t >= 0) {
-          const int64_t tile = blockIdx.x + (int64_t)t * gridDim.x;
-          for (int c = 0; c < KC; ++c) load_chunk(tile, c * 32, L2_EVICT_FIRST);
-        }
+      for (int t = -1; t < my_tiles; ++t) {
+        const int64_t tile1 = blockIdx.x + (int64_t)(t + 1) * gridDim.x, tile2 = blockIdx.x + (int64_t)t * gridDim.x;
+        lt_phase(
+            KC, FB, t + 1 < my_tiles, t >= 0,
+            [&](int c) {
+              if (c == 0) LTR(4, t + 1, 0);
+              load_chunk(tile1, c * 32, L2_EVICT_LAST);
+              if (c == KC - 1) LTR(4, t + 1, 1);
+            },
+            [&](int fb) {
+              if (fb == 0) LTR(4, t, 2);
+              for (int kc = 0; kc < 4; ++kc) load_chunk(tile2, (fb * 4 + kc) * 32, L2_EVICT_FIRST);
+              if (fb == FB - 1) LTR(4, t, 3);
+            });
       }
     }
   } else if (warp == 2) {
@@ -179,68 +242,75 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     const uint32_t w_a = smem_u32(wst) >> 4, a2_a = smem_u32(a2) >> 4, py_a = smem_u32(py) >> 4;
     uint32_t g1 = 0;  // GEMM1 chunk counter (operand ring slot g1 % 4, W stage g1 % LT_WS)
     uint32_t g2 = 0;  // GEMM2 block counter (a2 phase)
-    auto gemm1 = [&](int t) {
+    auto gemm1 = [&](int t, int c) {  // one 32-feature chunk of the margins of tile t
       const uint32_t buf = t & 1;
-      mbar_wait(&sm->d1_empty[buf], ((t >> 1) & 1) ^ 1);
       const uint32_t dd = tmem_base + LT_D1 + buf * LT_NP;
-      for (int c = 0; c < KC; ++c, ++g1) {
-        const uint32_t slot = g1 & 3, ph = (g1 >> 2) & 1;
-        const uint32_t ws = g1 % LT_WS, wph = (g1 / LT_WS) & 1;
-        mbar_wait(&sm->a1_full[slot], ph);
-        mbar_wait(&sm->w_full[ws], wph);
-        tc_fence_after();
-        if (elect_one()) {
-          const uint32_t ah = tmem_base + LT_A1 + slot * 64, al = ah + 32;
-          const uint64_t bh = kdesc | (uint64_t)(w_a + ws * (LT_WSTAGE >> 4));
-          const uint64_t bl = bh + ((LT_NP * 128) >> 4);
-#pragma unroll
-          for (int s = 0; s < 4; ++s) {
-            mma_tf32_ts(dd, ah + 8 * s, bh + 2 * s, (c | s) ? 1u : 0u);
-            mma_tf32_ts(dd, ah + 8 * s, bl + 2 * s, 1u);
-            mma_tf32_ts(dd, al + 8 * s, bh + 2 * s, 1u);
-          }
-          tc_commit(&sm->a1_empty[slot]);
-          tc_commit(&sm->w_empty[ws]);
-          if (c == KC - 1) tc_commit(&sm->d1_full[buf]);
-        }
-        __syncwarp();
+      if (c == 0) {
+        LTR(0, t, 0);
+        mbar_wait(&sm->d1_empty[buf], ((t >> 1) & 1) ^ 1);
+        LTR(0, t, 1);
       }
+      const uint32_t slot = g1 % LT_A1_SLOTS, ph = (g1 / LT_A1_SLOTS) & 1;
+      const uint32_t ws = g1 % LT_WS, wph = (g1 / LT_WS) & 1;
+      mbar_wait(&sm->a1_full[slot], ph);
+      mbar_wait(&sm->w_full[ws], wph);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t ah = tmem_base + LT_A1 + slot * 64, al = ah + 32;
+        const uint64_t bh = kdesc | (uint64_t)(w_a + ws * (LT_WSTAGE >> 4));
+        const uint64_t bl = bh + ((LT_NP * 128) >> 4);
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          mma_tf32_ts(dd, ah + 8 * s, bh + 2 * s, (c | s) ? 1u : 0u);
+          mma_tf32_ts(dd, ah + 8 * s, bl + 2 * s, 1u);
+          mma_tf32_ts(dd, al + 8 * s, bh + 2 * s, 1u);
+        }
+        tc_commit(&sm->a1_empty[slot]);
+        tc_commit(&sm->w_empty[ws]);
+        if (c == KC - 1) tc_commit(&sm->d1_full[buf]);
+      }
+      __syncwarp();
+      ++g1;
+      if (c == KC - 1) LTR(0, t, 2);
     };
-    auto gemm2 = [&](int t) {
+    auto gemm2 = [&](int t, int fb) {  // one 128-feature block of the gradient of tile t
       const uint32_t buf = t & 1;
-      mbar_wait(&sm->py_full[buf], (t >> 1) & 1);
-      for (int fb = 0; fb < FB; ++fb, ++g2) {
-        mbar_wait(&sm->a2_full, g2 & 1);
-        tc_fence_after();
-        if (elect_one()) {
-          const uint32_t dg = tmem_base + LT_G + fb * LT_NP;
-          const uint64_t ax1 = mndesc | (uint64_t)a2_a;                       // x1: atoms 0, 1
-          const uint64_t ax2 = mndesc | (uint64_t)(a2_a + 2 * (CHUNK_BYTES >> 4));  // x2: atoms 2, 3
-          const uint64_t bp1 = kdesc | (uint64_t)(py_a + buf * (16384 >> 4));
-          const uint64_t bp2 = bp1 + (8192 >> 4);
+      if (fb == 0) {
+        LTR(0, t, 3);
+        mbar_wait(&sm->py_full[buf], (t >> 1) & 1);
+        LTR(0, t, 4);
+      }
+      mbar_wait(&sm->a2_full, g2 & 1);
+      LTR(0, t, 5 + fb);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t dg = tmem_base + LT_G + fb * LT_GW;
+        const uint64_t ax1 = mndesc | (uint64_t)a2_a;                             // x1: atoms 0, 1
+        const uint64_t ax2 = mndesc | (uint64_t)(a2_a + 2 * (CHUNK_BYTES >> 4));  // x2: atoms 2, 3
+        const uint64_t bp1 = kdesc | (uint64_t)(py_a + buf * (16384 >> 4));
+        const uint64_t bp2 = bp1 + (LT_PY_P2 >> 4);
 #pragma unroll
-          for (int s = 0; s < 8; ++s) {  // 16 rows of K per instruction
-            const uint32_t aoff = (uint32_t)s * (2048 >> 4);                       // 16 rows x 128 B
-            const uint32_t boff = (uint32_t)(s >> 2) * (4096 >> 4) + (s & 3) * 2;  // atom of 64 rows, 32 B steps
-            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, (t | s) ? 1u : 0u);
-            mma_bf16_ss(dg, ax1 + aoff, bp2 + boff, 1u);
-            mma_bf16_ss(dg, ax2 + aoff, bp1 + boff, 1u);
+        for (int s = 0; s < 8; ++s) {  // 16 rows of K per instruction
+          const uint32_t aoff = (uint32_t)s * (2048 >> 4);                            // 16 rows x 128 B
+          const uint32_t boff = (uint32_t)(s >> 2) * (LT_PY_ATOM >> 4) + (s & 3) * 2;  // atom of 64 rows, 32 B steps
+          if (LT_PCAT) {
+            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, IDESC_G2_N64, (t | s) ? 1u : 0u);  // x1 . [p1 | p2]
+            mma_bf16_ss(dg, ax2 + aoff, bp1 + boff, IDESC_G2, 1u);                     // x2 . p1
+          } else {
+            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, IDESC_G2, (t | s) ? 1u : 0u);
+            mma_bf16_ss(dg, ax1 + aoff, bp2 + boff, IDESC_G2, 1u);
+            mma_bf16_ss(dg, ax2 + aoff, bp1 + boff, IDESC_G2, 1u);
           }
-          tc_commit(&sm->a2_empty);
-          if (fb == FB - 1) tc_commit(&sm->py_empty[buf]);
         }
-        __syncwarp();
+        tc_commit(&sm->a2_empty);
+        if (fb == FB - 1) tc_commit(&sm->py_empty[buf]);
       }
+      __syncwarp();
+      ++g2;
+      if (fb == FB - 1) LTR(0, t, 9);
     };
-    if (LT_PIPELINED && my_tiles > 0) gemm1(0);
-    for (int t = 0; t < my_tiles; ++t) {
-      if (LT_PIPELINED) {
-        if (t + 1 < my_tiles) gemm1(t + 1);
-      } else {
-        gemm1(t);
-      }
-      gemm2(t);
-    }
+    for (int t = -1; t < my_tiles; ++t)
+      lt_phase(KC, FB, t + 1 < my_tiles, t >= 0, [&](int c) { gemm1(t + 1, c); }, [&](int fb) { gemm2(t, fb); });
     if (elect_one()) tc_commit(&sm->g_done);
     __syncwarp();
   } else if (warp >= 4 && warp < 8) {
@@ -258,13 +328,16 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
       const bool live = row < n;
       const float wi = live ? (w ? w[row] : 1.f) : 0.f;
       const int yi = live ? (int)y[row] : 0;
+      if (warp == 4) LTR(1, t, 0);
       mbar_wait(&sm->d1_full[buf], (t >> 1) & 1);
+      if (warp == 4) LTR(1, t, 1);
       tc_fence_after();
       uint32_t v[32];
       tmem_ld32(tmem_base + lane_addr + LT_D1 + buf * LT_NP, v);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&sm->d1_empty[buf]);
+      if (warp == 4) LTR(1, t, 2);
       float m[LT_NP];
       float mx = 0.f;  // "subtract max if > 0"
 #pragma unroll
@@ -286,8 +359,10 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
       }
       // (P - Y) * w as bf16 pairs p1 + p2 into the GEMM2 B operand: [32 classes x 128 rows], K-major,
       // 2 atoms of 64 rows (128 B per class row), 128B swizzle
+      if (warp == 4) LTR(1, t, 3);
       mbar_wait(&sm->py_empty[buf], ((t >> 1) & 1) ^ 1);
-      uint8_t* pbase = py + (size_t)buf * 16384 + (size_t)(r >> 6) * 4096;
+      if (warp == 4) LTR(1, t, 4);
+      uint8_t* pbase = py + (size_t)buf * 16384 + (size_t)(r >> 6) * LT_PY_ATOM;
       const int cb = (r & 63) * 2;  // byte column of this row inside the 128-byte class row
 #pragma unroll
       for (int k = 0; k < LT_NP; ++k) {
@@ -298,25 +373,13 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
         const __nv_bfloat16 h2 = __float2bfloat16_rn(val - __bfloat162float(h1));
         const int off = k * 128 + ((((cb >> 4) ^ (k & 7)) << 4) | (cb & 15));
         *reinterpret_cast<__nv_bfloat16*>(pbase + off) = h1;
-        *reinterpret_cast<__nv_bfloat16*>(pbase + 8192 + off) = h2;
+        *reinterpret_cast<__nv_bfloat16*>(pbase + LT_PY_P2 + off) = h2;
       }
       fence_async_smem();
       mbar_arrive(&sm->py_full[buf]);
+      if (warp == 4) LTR(1, t, 5);
     }
-    // ---- final: G^T from tensor memory, intercept gradient, loss
-    mbar_wait(&sm->g_done, 0);
-    tc_fence_after();
-    const int plen = K * d + K + 2;
-    double* part = partials + (size_t)blockIdx.x * plen;
-    for (int fb = 0; fb < FB; ++fb) {
-      uint32_t v[32];
-      tmem_ld32(tmem_base + lane_addr + LT_G + fb * LT_NP, v);
-      tmem_ld_wait();
-      const int f = fb * 128 + r;  // lane == feature
-#pragma unroll
-      for (int k = 0; k < LT_NP; ++k)
-        if (k < K) part[(size_t)k * d + f] = (my_tiles > 0) ? (double)__uint_as_float(v[k]) : 0.0;
-    }
+    // ---- final: G^T from tensor memory, intercept gradient, loss (the row sums first: their registers are dead by the read-out)
 #pragma unroll
     for (int k = 0; k < LT_NP; ++k) {
       const double t = warp_sum((double)gb[k]);
@@ -327,6 +390,26 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     if (lane == 0) {
       sm->red[q][LT_NP] = loss;
       sm->red[q][LT_NP + 1] = sw;
+    }
+    mbar_wait(&sm->g_done, 0);
+    tc_fence_after();
+    const int plen = K * d + K + 2;
+    double* part = partials + (size_t)blockIdx.x * plen;
+    for (int fb = 0; fb < FB; ++fb) {
+      uint32_t v[32];
+      tmem_ld32(tmem_base + lane_addr + LT_G + fb * LT_GW, v);
+      tmem_ld_wait();
+      const int f = fb * 128 + r;  // lane == feature
+      if (LT_PCAT) {
+        uint32_t v2[32];
+        tmem_ld32(tmem_base + lane_addr + LT_G + fb * LT_GW + 32, v2);
+        tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < LT_NP; ++k) v[k] = __float_as_uint(__uint_as_float(v[k]) + __uint_as_float(v2[k]));
+      }
+#pragma unroll
+      for (int k = 0; k < LT_NP; ++k)
+        if (k < K) part[(size_t)k * d + f] = (my_tiles > 0) ? (double)__uint_as_float(v[k]) : 0.0;
     }
     asm volatile("bar.sync 1, 128;" ::: "memory");
     if (r < K + 2) {
@@ -344,11 +427,13 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     uint32_t g = 0;   // staging chunk counter (same order as the producer); this group takes g % 2 == grp
     uint32_t g1 = 0;  // GEMM1 operand ring counter
     uint32_t g2 = 0;  // GEMM2 block counter
-    auto split1 = [&]() {  // one tile of GEMM1: KC chunks -> tf32 hi / lo into tensor memory
-      for (int c = 0; c < KC; ++c, ++g, ++g1) {
-        if ((g & 1u) != (uint32_t)grp) continue;
+    auto split1 = [&](int tt, int c) {  // one GEMM1 chunk of tile tt -> tf32 hi / lo into tensor memory
+      if (q == 0 && c == 0) LTR(2 + grp, tt, 0);
+      if ((g & 1u) == (uint32_t)grp) {
         const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
+        if (w8 == 0) LTR(5, tt, 0);
         mbar_wait(&sm->xs_full[slot], ph);
+        if (w8 == 0) LTR(5, tt, 1);
         const uint8_t* src = xs + (size_t)slot * CHUNK_BYTES + (size_t)r * 128;
         uint32_t hi[32], lo[32];
 #pragma unroll
@@ -364,63 +449,68 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
           lo[p * 4 + 2] = __float_as_uint(v.z - __uint_as_float(h2)); lo[p * 4 + 3] = __float_as_uint(v.w - __uint_as_float(h3));
         }
         mbar_arrive(&sm->xs_empty[slot]);
-        const uint32_t aslot = g1 & 3, aph = (g1 >> 2) & 1;
+        if (w8 == 0) LTR(5, tt, 2);
+        const uint32_t aslot = g1 % LT_A1_SLOTS, aph = (g1 / LT_A1_SLOTS) & 1;
         mbar_wait(&sm->a1_empty[aslot], aph ^ 1);
+        if (w8 == 0) LTR(5, tt, 3);
         tc_fence_after();
         tmem_st32(tmem_base + lane_addr + LT_A1 + aslot * 64, hi);
         tmem_st32(tmem_base + lane_addr + LT_A1 + aslot * 64 + 32, lo);
         tmem_st_wait();
+        if (w8 == 0) LTR(5, tt, 4);
         tc_fence_before();
         mbar_arrive(&sm->a1_full[aslot]);
+        if (w8 == 0) LTR(5, tt, 5);
       }
+      ++g;
+      ++g1;
+      if (q == 0 && c == KC - 1) LTR(2 + grp, tt, 1);
     };
-    auto split2 = [&]() {  // one tile of GEMM2: FB blocks of 4 chunks -> bf16 x1 / x2, MN-major smem tile
-      for (int fb = 0; fb < FB; ++fb, ++g2) {
-        mbar_wait(&sm->a2_empty, (g2 & 1) ^ 1);
-        for (int kc = 0; kc < 4; ++kc, ++g) {
-          if ((g & 1u) != (uint32_t)grp) continue;
-          const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
-          mbar_wait(&sm->xs_full[slot], ph);
-          const uint8_t* src = xs + (size_t)slot * CHUNK_BYTES + (size_t)r * 128;
-          // features kc*32 .. +31 of this block -> atom kc/2, 16-byte chunks (kc%2)*4 + {0..3} of the row
-          uint8_t* d1 = a2 + (size_t)(kc >> 1) * CHUNK_BYTES + (size_t)r * 128;
-          uint8_t* d2 = d1 + 2 * CHUNK_BYTES;
+    auto split2 = [&](int tt, int fb) {  // one GEMM2 block of tile tt: 4 chunks -> bf16 x1 / x2, MN-major smem tile
+      if (q == 0 && fb == 0) LTR(2 + grp, tt, 2);
+      mbar_wait(&sm->a2_empty, (g2 & 1) ^ 1);
+      if (q == 0) LTR(2 + grp, tt, 3 + fb);
+      for (int kc = 0; kc < 4; ++kc, ++g) {
+        if ((g & 1u) != (uint32_t)grp) continue;
+        const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
+        if (w8 == 0) LTR(5, tt, 6);
+        mbar_wait(&sm->xs_full[slot], ph);
+        if (w8 == 0) LTR(5, tt, 7);
+        const uint8_t* src = xs + (size_t)slot * CHUNK_BYTES + (size_t)r * 128;
+        // features kc*32 .. +31 of this block -> atom kc/2, 16-byte chunks (kc%2)*4 + {0..3} of the row
+        uint8_t* d1 = a2 + (size_t)(kc >> 1) * CHUNK_BYTES + (size_t)r * 128;
+        uint8_t* d2 = d1 + 2 * CHUNK_BYTES;
 #pragma unroll
-          for (int hh = 0; hh < 4; ++hh) {
-            const float4 va = *reinterpret_cast<const float4*>(src + (((2 * hh) ^ (r & 7)) << 4));
-            const float4 vb = *reinterpret_cast<const float4*>(src + (((2 * hh + 1) ^ (r & 7)) << 4));
-            const float f[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
-            uint32_t o1[4], o2[4];
+        for (int hh = 0; hh < 4; ++hh) {
+          const float4 va = *reinterpret_cast<const float4*>(src + (((2 * hh) ^ (r & 7)) << 4));
+          const float4 vb = *reinterpret_cast<const float4*>(src + (((2 * hh + 1) ^ (r & 7)) << 4));
+          const float f[8] = {va.x, va.y, va.z, va.w, vb.x, vb.y, vb.z, vb.w};
+          uint32_t o1[4], o2[4];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              // x1 = x rounded to bf16 (nearest, ties away) and x2 = (x - x1) truncated to bf16, with
-              // full-rate integer ops; __byte_perm packs the two high halves (even k in the low 16 bits)
-              const uint32_t ra = (__float_as_uint(f[2 * e]) + 0x8000u) & 0xFFFF0000u;
-              const uint32_t rb = (__float_as_uint(f[2 * e + 1]) + 0x8000u) & 0xFFFF0000u;
-              const uint32_t la = __float_as_uint(f[2 * e] - __uint_as_float(ra));
-              const uint32_t lb = __float_as_uint(f[2 * e + 1] - __uint_as_float(rb));
-              o1[e] = __byte_perm(ra, rb, 0x7632);
-              o2[e] = __byte_perm(la, lb, 0x7632);
-            }
-            const int off = (((kc & 1) * 4 + hh) ^ (r & 7)) << 4;
-            *reinterpret_cast<uint4*>(d1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
-            *reinterpret_cast<uint4*>(d2 + off) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+          for (int e = 0; e < 4; ++e) {
+            // x1 = x rounded to bf16 (nearest, ties away) and x2 = (x - x1) truncated to bf16, with
+            // full-rate integer ops; __byte_perm packs the two high halves (even k in the low 16 bits)
+            const uint32_t ra = (__float_as_uint(f[2 * e]) + 0x8000u) & 0xFFFF0000u;
+            const uint32_t rb = (__float_as_uint(f[2 * e + 1]) + 0x8000u) & 0xFFFF0000u;
+            const uint32_t la = __float_as_uint(f[2 * e] - __uint_as_float(ra));
+            const uint32_t lb = __float_as_uint(f[2 * e + 1] - __uint_as_float(rb));
+            o1[e] = __byte_perm(ra, rb, 0x7632);
+            o2[e] = __byte_perm(la, lb, 0x7632);
           }
-          mbar_arrive(&sm->xs_empty[slot]);
+          const int off = (((kc & 1) * 4 + hh) ^ (r & 7)) << 4;
+          *reinterpret_cast<uint4*>(d1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+          *reinterpret_cast<uint4*>(d2 + off) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
         }
-        fence_async_smem();
-        mbar_arrive(&sm->a2_full);
+        mbar_arrive(&sm->xs_empty[slot]);
+        if (w8 == 0) LTR(5, tt, 8);
       }
+      fence_async_smem();
+      mbar_arrive(&sm->a2_full);
+      ++g2;
+      if (q == 0) LTR(2 + grp, tt, 7 + fb);
     };
-    if (LT_PIPELINED && my_tiles > 0) split1();
-    for (int t = 0; t < my_tiles; ++t) {
-      if (LT_PIPELINED) {
-        if (t + 1 < my_tiles) split1();
-      } else {
-        split1();
-      }
-      split2();
-    }
+    for (int t = -1; t < my_tiles; ++t)
+      lt_phase(KC, FB, t + 1 < my_tiles, t >= 0, [&](int c) { split1(t + 1, c); }, [&](int fb) { split2(t, fb); });
   }
   tc_fence_before();
   __syncthreads();
@@ -469,5 +559,16 @@ int lr_mn_tc_launch(const float* X, const float* y, const float* w, int64_t n, i
   B2F_CUDA(cudaFuncSetAttribute(lr_mn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   lr_mn_tc_kernel<<<grid, LT_THREADS, smem, st>>>(mx, mh, ml, y, w, n, d, K, icpt, partials);
   B2F_LAUNCH_CHECK();
+#ifdef LT_TRACE
+  if (const char* path = getenv("B2F_LR_TRACE")) {
+    std::vector<unsigned long long> host(LTR_ROLES * LTR_TILES * LTR_SLOTS);
+    B2F_CUDA(cudaStreamSynchronize(st));
+    B2F_CUDA(cudaMemcpyFromSymbol(host.data(), lt_trace, host.size() * sizeof(unsigned long long)));
+    if (FILE* f = fopen(path, "wb")) {
+      fwrite(host.data(), sizeof(unsigned long long), host.size(), f);
+      fclose(f);
+    }
+  }
+#endif
   return B2F_OK;
 }
