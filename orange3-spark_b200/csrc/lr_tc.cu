@@ -38,7 +38,11 @@ constexpr int LT_SPLIT_THREADS = 256;
 // Both switches are on in the product; -DLT_INTERLEAVE=0 / -DLT_PCAT=0 rebuild the earlier kernel for comparison
 // (20M x 512, 20 classes: 12.97 ms with both off, 11.68 interleave only, 12.95 [p1|p2] only, 10.84 with both).
 #ifndef LT_INTERLEAVE
-#define LT_INTERLEAVE 1  // the last 2 (FB - 1) GEMM1 chunks of tile t+1 go between the GEMM2 blocks of tile t (see lt_phase)
+#define LT_INTERLEAVE 1  // the last LT_BETWEEN (FB - 1) GEMM1 chunks of tile t+1 go between the GEMM2 blocks of tile t (lt_phase)
+#endif
+#ifndef LT_BETWEEN
+#define LT_BETWEEN 3     // GEMM1 chunks issued after each GEMM2 block but the last (same box, d = 512: 1 -> +10%, 2 -> +2.5%,
+                         // 4 -> +1.5% time relative to 3)
 #endif
 #ifndef LT_PCAT
 #define LT_PCAT 1        // GEMM2 reads x1 once against [p1 | p2] (N = 64) instead of twice (N = 32 each)
@@ -96,12 +100,12 @@ __device__ __forceinline__ void mma_bf16_ss(uint32_t d, uint64_t a, uint64_t b, 
 }
 // Work order of one phase, shared by the X producer, the split warps and the MMA issuer: the GEMM1 chunks of one
 // tile (has_g1) and the GEMM2 blocks of the tile before it (has_g2).  Plain order: all chunks, then all blocks.
-// LT_INTERLEAVE: the last 2 (FB - 1) chunks are held back and issued two at a time after each block but the last, so
+// LT_INTERLEAVE: the last LT_BETWEEN (FB - 1) chunks are held back and issued LT_BETWEEN at a time after each block but the last, so
 // that the split warps have work while a block's MMAs drain (the operand tile of GEMM2 is single-buffered), and the
 // softmax of the GEMM1 tile still has the whole last block plus the next phase's leading chunks to hide behind.
 template <class F1, class F2>
 __device__ __forceinline__ void lt_phase(int KC, int FB, bool has_g1, bool has_g2, F1&& g1_chunk, F2&& g2_block) {
-  const int pre = (LT_INTERLEAVE && has_g1 && has_g2) ? KC - 2 * (FB - 1) : KC;
+  const int pre = (LT_INTERLEAVE && has_g1 && has_g2) ? KC - LT_BETWEEN * (FB - 1) : KC;
   int c = 0;
   if (has_g1)
     for (; c < pre; ++c) g1_chunk(c);
@@ -109,7 +113,7 @@ __device__ __forceinline__ void lt_phase(int KC, int FB, bool has_g1, bool has_g
     for (int fb = 0; fb < FB; ++fb) {
       g2_block(fb);
       if (has_g1)
-        for (int e = 0; e < 2 && c < KC; ++e, ++c) g1_chunk(c);
+        for (int e = 0; e < LT_BETWEEN && c < KC; ++e, ++c) g1_chunk(c);
     }
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
