@@ -129,8 +129,23 @@ __device__ unsigned long long lt_trace[LTR_ROLES * LTR_TILES * LTR_SLOTS];
       lt_trace[((role) * LTR_TILES + (it)) * LTR_SLOTS + (slot)] = (unsigned long long)clock64(); \
     asm volatile("" ::: "memory");                                                                \
   } while (0)
+// LTW(k, stmt): run stmt and add the cycles it took to wait-sum k (warp 8 only); LTW_FLUSH writes the sums of a phase
+#define LTW(k, stmt)                                  \
+  do {                                                \
+    const long long c0_ = clock64();                  \
+    stmt;                                             \
+    if (w8 == 0) ltw[k] += clock64() - c0_;           \
+  } while (0)
+#define LTW_FLUSH(it)                                                                              \
+  do {                                                                                             \
+    if (w8 == 0 && blockIdx.x == 0 && lane == 0 && (it) >= 0 && (it) < LTR_TILES)                  \
+      for (int k_ = 0; k_ < 4; ++k_) lt_trace[(5 * LTR_TILES + (it)) * LTR_SLOTS + 9 + k_] = (unsigned long long)ltw[k_]; \
+    for (int k_ = 0; k_ < 4; ++k_) ltw[k_] = 0;                                                    \
+  } while (0)
 #else
 #define LTR(role, it, slot) do {} while (0)
+#define LTW(k, stmt) stmt
+#define LTW_FLUSH(it) do {} while (0)
 #endif
 
 }  // namespace
@@ -431,12 +446,15 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     uint32_t g = 0;   // staging chunk counter (same order as the producer); this group takes g % 2 == grp
     uint32_t g1 = 0;  // GEMM1 operand ring counter
     uint32_t g2 = 0;  // GEMM2 block counter
+#ifdef LT_TRACE
+    long long ltw[4] = {0, 0, 0, 0};  // cycles warp 8 waited in a phase: xs_full (G1) | a1_empty | a2_empty | xs_full (G2)
+#endif
     auto split1 = [&](int tt, int c) {  // one GEMM1 chunk of tile tt -> tf32 hi / lo into tensor memory
       if (q == 0 && c == 0) LTR(2 + grp, tt, 0);
       if ((g & 1u) == (uint32_t)grp) {
         const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
         if (w8 == 0) LTR(5, tt, 0);
-        mbar_wait(&sm->xs_full[slot], ph);
+        LTW(0, mbar_wait(&sm->xs_full[slot], ph));
         if (w8 == 0) LTR(5, tt, 1);
         const uint8_t* src = xs + (size_t)slot * CHUNK_BYTES + (size_t)r * 128;
         uint32_t hi[32], lo[32];
@@ -455,7 +473,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
         mbar_arrive(&sm->xs_empty[slot]);
         if (w8 == 0) LTR(5, tt, 2);
         const uint32_t aslot = g1 % LT_A1_SLOTS, aph = (g1 / LT_A1_SLOTS) & 1;
-        mbar_wait(&sm->a1_empty[aslot], aph ^ 1);
+        LTW(1, mbar_wait(&sm->a1_empty[aslot], aph ^ 1));
         if (w8 == 0) LTR(5, tt, 3);
         tc_fence_after();
         tmem_st32(tmem_base + lane_addr + LT_A1 + aslot * 64, hi);
@@ -472,13 +490,13 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     };
     auto split2 = [&](int tt, int fb) {  // one GEMM2 block of tile tt: 4 chunks -> bf16 x1 / x2, MN-major smem tile
       if (q == 0 && fb == 0) LTR(2 + grp, tt, 2);
-      mbar_wait(&sm->a2_empty, (g2 & 1) ^ 1);
+      LTW(2, mbar_wait(&sm->a2_empty, (g2 & 1) ^ 1));
       if (q == 0) LTR(2 + grp, tt, 3 + fb);
       for (int kc = 0; kc < 4; ++kc, ++g) {
         if ((g & 1u) != (uint32_t)grp) continue;
         const uint32_t slot = g % LT_XS, ph = (g / LT_XS) & 1;
         if (w8 == 0) LTR(5, tt, 6);
-        mbar_wait(&sm->xs_full[slot], ph);
+        LTW(3, mbar_wait(&sm->xs_full[slot], ph));
         if (w8 == 0) LTR(5, tt, 7);
         const uint8_t* src = xs + (size_t)slot * CHUNK_BYTES + (size_t)r * 128;
         // features kc*32 .. +31 of this block -> atom kc/2, 16-byte chunks (kc%2)*4 + {0..3} of the row
@@ -513,8 +531,10 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
       ++g2;
       if (q == 0) LTR(2 + grp, tt, 7 + fb);
     };
-    for (int t = -1; t < my_tiles; ++t)
+    for (int t = -1; t < my_tiles; ++t) {
       lt_phase(KC, FB, t + 1 < my_tiles, t >= 0, [&](int c) { split1(t + 1, c); }, [&](int fb) { split2(t, fb); });
+      LTW_FLUSH(t);
+    }
   }
   tc_fence_before();
   __syncthreads();

@@ -64,3 +64,5 @@ print("inside the last G1 chunk of a tile (warp 8): wait xs_full %.0f | load + c
       "fence + arrive %.0f" % tuple((c[:, i + 1] - c[:, i]).mean() for i in range(5)))
 print("inside the last G2 chunk of a tile (warp 8): wait xs_full %.0f | load + convert + store %.0f" % (
     (c[:, 7] - c[:, 6]).mean(), (c[:, 8] - c[:, 7]).mean()))
+print("warp 8, cycles waited per tile phase: xs_full in G1 chunks %.0f | a1_empty %.0f | a2_empty %.0f | xs_full in G2 chunks %.0f" %
+      tuple(c[:, 9 + k].mean() for k in range(4)))
