@@ -11,7 +11,8 @@
  *   - every function returns 0 on success, a negative B2F_E* code otherwise;
  *     b2f_last_error() returns a thread-local message for the last failure;
  *   - all pointers are DEVICE pointers unless the name ends in _host;
- *   - the caller owns every buffer (the library never allocates device memory)
+ *   - the caller owns every buffer (the library never allocates device memory; its development
+ *     tracers, which did, are compiled in only with -DB2F_DEV)
  *     and passes the CUDA stream as an opaque pointer (cudaStream_t; NULL = the
  *     legacy default stream);
  *   - calls are asynchronous on `stream`; nothing here synchronises the device;
@@ -76,7 +77,9 @@ int b2f_synth_logistic(float* X, float* y, int64_t n, int64_t row0, int d, int64
  * col_ptrs_dev[d]  : device array of device pointers, one per ordered input column
  * col_dtypes_dev[d]: device array of B2F_* dtype codes
  * X[n, ld]         : fp32 row-major output (padding columns d..ld-1 are zeroed)
- * bad_flag         : device int32, set to 1 if any value is NaN/Inf (NULL to skip) */
+ * bad_flag         : device int32, set to 1 if any value is NaN (NULL to skip).  Infinities pass: MLlib's
+ *                    VectorAssembler throws "Encountered NaN while assembling a row" under
+ *                    handleInvalid = "error" for NaN (and null) only.                       */
 int b2f_pack_columns(const void* const* col_ptrs_dev, const int32_t* col_dtypes_dev, int d, int64_t n,
                      float* X, int64_t ld, int32_t* bad_flag, b2f_stream_t stream);
 
@@ -121,11 +124,26 @@ int b2f_kmeans_step(const float* X, int64_t n, int d, int64_t ld, const float* w
  * which enables B2F_KM_TCB / B2F_KM_TCH: rows whose label the low-precision filter pass cannot certify
  * are listed in the workspace, gathered and re-assigned by the 3xTF32 kernel.  The list holds n/5 rows; if
  * more rows are uncertain the excess is DROPPED and the payload's row count (last entry) comes out below
- * n -- the caller must then redo the pass with B2F_KM_TC3.  B2F_KM_AUTO picks TCH when the shape allows it
+ * n -- the caller must then redo the pass with B2F_KM_TC3 and the same workspace (see below).  B2F_KM_AUTO picks TCH when the shape allows it
  * and labels / ws are given, else behaves like b2f_kmeans_step.  Same reference call site as above.    */
 size_t b2f_kmeans_ws_bytes(int64_t n, int k, int d);
 int b2f_kmeans_step_ws(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep, int k,
                        void* acc, int32_t* labels, void* ws, size_t ws_bytes, int algo, b2f_stream_t stream);
+/* With a workspace, B2F_KM_TC3 means: 3xTF32 scores over every row WITH the certainty test, rows inside its (narrow)
+ * uncertainty band to the fp64 kernel -- labels equal to fp64 except fp64-level ties.  It is the fallback of the
+ * filter pipeline; its list lives in the same workspace and holds every row when the workspace has the standard size.
+ * After any of these calls the first four int32 of the workspace read
+ *   [0] rows the filter pass listed for the 3xTF32 re-check   [1] rows re-checked (= min([0], [3]))
+ *   [2] rows listed for the fp64 kernel                       [3] capacity of each list
+ * so max(0, [0] - [3]) + max(0, [2] - [3]) rows were dropped (0 in any sane run).                      */
+/* The same pass over the rows x * col_scale (element-wise per column, fp32[d] on the device, 16-byte aligned)
+ * WITHOUT a scaled copy of X: StandardScalerModel.transform folded into the Lloyd pass (BASELINE config 5).
+ * The operand conversion multiplies by the factor, the accumulated raw row sums are scaled once per pass;
+ * payload, labels and cost are those of the scaled data.  Shapes as B2F_KM_TCH (b2f_kmeans_scaled_supported).
+ *   reference: orangecontrib/spark/base/spark_ml_transformer.py:133 followed by spark_ml_estimator.py:22  */
+int b2f_kmeans_scaled_supported(int k, int d, int64_t ld);
+int b2f_kmeans_step_scaled(const float* X, int64_t n, int d, int64_t ld, const float* col_scale, const void* prep,
+                           int k, void* acc, int32_t* labels, void* ws, size_t ws_bytes, b2f_stream_t stream);
 /* folds scratch replicas / partials into the fp64 payload at the head of acc */
 int b2f_kmeans_fold(void* acc, int k, int d, b2f_stream_t stream);
 /* centre update from the (all-reduced) payload: centres with count > 0 move to sums/count,
@@ -138,6 +156,13 @@ int b2f_kmeans_finalize(const double* payload, int k, int d, double tol, double*
  *   reference: orangecontrib/spark/widgets/ml/spark_ml_model.py:53                            */
 int b2f_kmeans_predict(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, int32_t* labels,
                        float* dist2, int algo, b2f_stream_t stream);
+/* The same with a workspace (b2f_kmeans_ws_bytes): labels then come from the certainty pipeline of
+ * b2f_kmeans_step_ws (filter pass, pair check, 3xTF32 re-check, fp64 tail) wherever the shape allows it, i.e. they
+ * equal the fp64 assignment except for fp64-level ties; dist2 is the fp32 direct-form distance to the labelled
+ * centre.  col_scale (may be NULL) as in b2f_kmeans_step_scaled.  Same reference call site.            */
+int b2f_kmeans_predict_ws(const float* X, int64_t n, int d, int64_t ld, const float* col_scale, const void* prep,
+                          int k, int32_t* labels, float* dist2, void* ws, size_t ws_bytes, int algo,
+                          b2f_stream_t stream);
 
 /* ---- K3 / K4 LogisticRegression loss + gradient passes --------------------
  * replaces the treeAggregate of LogisticAggregator inside RDDLossFunction.calculate

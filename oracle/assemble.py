@@ -9,10 +9,15 @@ orangecontrib/spark/widgets/ml/spark_ml_dataset.py:569-582 (commit):
 import numpy as np
 
 
-def assemble(columns):
+def assemble(columns, handle_invalid="error"):
     """A.1: concatenate the ordered scalar numeric/boolean columns, each cast to
-    double, into one dense row vector per row.  Null (None) is an error
-    (handleInvalid='error'); NaN passes through."""
+    double, into one dense row vector per row.  handleInvalid (VectorAssembler.scala,
+    `assemble(..., keepInvalid)`): 'error' (the default) rejects null AND NaN
+    ("Encountered NaN while assembling a row with handleInvalid = "error""), 'keep' lets
+    NaN through; infinities are ordinary values in both modes.  ('skip', which drops
+    rows, is not restated: the reference never sets it.)"""
+    if handle_invalid not in ("error", "keep"):
+        raise ValueError("handle_invalid must be 'error' or 'keep'")
     cols = []
     n = None
     for c in columns:
@@ -29,7 +34,10 @@ def assemble(columns):
             n = a.shape[0]
         elif a.shape[0] != n:
             raise ValueError("VectorAssembler: ragged columns")
-        cols.append(a.astype(np.float64))
+        a = a.astype(np.float64)
+        if handle_invalid == "error" and np.isnan(a).any():
+            raise ValueError("VectorAssembler: encountered NaN while assembling a row with handleInvalid='error'")
+        cols.append(a)
     if not cols:
         return np.zeros((0, 0))
     return np.concatenate(cols, axis=1)

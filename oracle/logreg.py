@@ -96,6 +96,20 @@ def lr_fit(X, y, w=None, max_iter=100, reg_param=0.0, elastic_net=0.0, tol=1e-6,
     if binomial and num_classes > 2:
         raise ValueError("Binomial family only supports 1 or 2 outcome classes but found %d" % num_classes)
     K = 1 if binomial else max(num_classes, 2)
+    if fit_intercept and np.count_nonzero(hist) == 1:
+        # A.3 / LogisticRegression.scala: "All labels are the same value and fitIntercept=true, so the coefficients
+        # will be zeros. Training is not needed."  Intercept +inf on the constant class (binomial: +inf when the
+        # label is always 1 -- numClasses == 2 -- and -inf when it is always 0); empty objective history.
+        j = int(np.argmax(hist))
+        if binomial:
+            icpt = np.inf if num_classes == 2 else -np.inf
+            coef = np.zeros(d)
+        else:
+            icpt = np.zeros(K)
+            icpt[j] = np.inf
+            coef = np.zeros((K, d))
+        return {"coefficients": coef, "intercept": icpt, "objectiveHistory": [], "totalIterations": 0,
+                "numClasses": 2 if binomial else K, "binomial": binomial, "mean": mean, "std": std, "evals": 0}
     inv_std = np.where(std != 0.0, 1.0 / np.where(std != 0.0, std, 1.0), 0.0)
     lam2 = reg_param * (1.0 - elastic_net)
     lam1 = reg_param * elastic_net

@@ -27,7 +27,7 @@ def gather_rows(X, local_idx, comm):
     out = torch.zeros((total, X.d), dtype=torch.float64, device=dev)
     off = int(cnt_h[: comm.rank].sum())
     if local_idx.numel():
-        out[off: off + local_idx.numel()] = X.data[local_idx.long(), : X.d].double()
+        out[off: off + local_idx.numel()] = X.rows(local_idx.long()).double()
     comm.all_reduce_sum(out)
     return out.cpu().numpy()
 

@@ -39,6 +39,9 @@ PROTOTYPES = {
     "b2f_kmeans_step": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _vp, _i32, _vp, _vp, _i32, _vp]),
     "b2f_kmeans_ws_bytes": (_sz, [_i64, _i32, _i32]),
     "b2f_kmeans_step_ws": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _i32, _vp]),
+    "b2f_kmeans_scaled_supported": (C.c_int, [_i32, _i32, _i64]),
+    "b2f_kmeans_step_scaled": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "b2f_kmeans_predict_ws": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _vp, _i32, _vp, _vp, _vp, _sz, _i32, _vp]),
     "b2f_kmeans_fold": (C.c_int, [_vp, _i32, _i32, _vp]),
     "b2f_kmeans_finalize": (C.c_int, [_vp, _i32, _i32, _f64, _vp, _vp, _vp, _vp]),
     "b2f_kmeans_predict": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _i32, _vp, _vp, _i32, _vp]),

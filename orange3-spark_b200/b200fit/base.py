@@ -11,11 +11,17 @@
 Calls are synchronous (the widget calls them on the Qt thread), exceptions
 propagate as plain Python exceptions, models are immutable after fit.
 """
+from abc import ABCMeta, abstractmethod
+
 from .param import Params
 
 
-class Transformer(Params):
-    def _transform(self, dataset):  # pragma: no cover - abstract
+# The bases are ABCs, as in pyspark: the reference's discovery lists every class of the module with a `fit` /
+# `transform` that is NOT abstract (orangecontrib/spark/utils/ml_api_utils.py:53-72, inspect.isabstract), and the
+# bases are imported into clustering / classification / feature.
+class Transformer(Params, metaclass=ABCMeta):
+    @abstractmethod
+    def _transform(self, dataset):
         raise NotImplementedError
 
     def transform(self, dataset, params=None):
@@ -24,8 +30,9 @@ class Transformer(Params):
         return self._transform(dataset)
 
 
-class Estimator(Params):
-    def _fit(self, dataset):  # pragma: no cover - abstract
+class Estimator(Params, metaclass=ABCMeta):
+    @abstractmethod
+    def _fit(self, dataset):
         raise NotImplementedError
 
     def fit(self, dataset, params=None):
@@ -36,9 +43,15 @@ class Estimator(Params):
         return self._fit(dataset)
 
 
-class Model(Transformer):
-    """Fitted model.  Registered as a virtual subclass of pyspark.ml.Model when pyspark is
-    importable so Orange's dynamic channel check isinstance(obj, pyspark.ml.Model) passes."""
+class Model(Transformer, metaclass=ABCMeta):
+    """Fitted model (abstract: `_transform` comes from the concrete model).  Registered as a virtual subclass of
+    pyspark.ml.Model when pyspark is importable so Orange's dynamic channel check isinstance(obj, pyspark.ml.Model)
+    passes."""
+
+    def transform(self, dataset, params=None):
+        from .frame import return_like
+
+        return return_like(dataset, super().transform(dataset, params))
 
 
 def _register_with_pyspark():

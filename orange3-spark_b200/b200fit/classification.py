@@ -87,6 +87,25 @@ def make_objective(engine, comm, K, d, inv_std, l2w, fit_intercept, active):
     return f
 
 
+def _parse_thresholds(th):
+    """`thresholds` as a list of floats.  The widget hands every non-numeric entry over as the STRING the user
+    typed (orangecontrib/spark/utils/gui_utils.py:78-94), e.g. "[0.5, 0.5]" or "0.3,0.7"."""
+    if th is None:
+        return None
+    if isinstance(th, str):
+        txt = th.strip().strip("[]()")
+        if not txt or txt == "None":
+            return None
+        try:
+            th = [float(v) for v in txt.replace(";", ",").split(",") if v.strip()]
+        except ValueError:
+            raise ValueError("thresholds: cannot read %r as a list of numbers" % th)
+    out = [float(v) for v in th]
+    if any(v < 0 for v in out) or sum(1 for v in out if v == 0) > 1:
+        raise ValueError("thresholds must be >= 0 with at most one zero, got %r" % (out,))
+    return out
+
+
 _LR_PARAMS = (
     ("featuresCol", "features column name.", TC.toString),
     ("labelCol", "label column name.", TC.toString),
@@ -191,9 +210,9 @@ class LogisticRegressionModel(Model):
         N.check(L.b2f_lr_predict(N.ptr(X.data), X.n, X.d, X.ld, nc, N.ptr(beta), N.ptr(icpt),
                                  float(self.getOrDefault("threshold")), N.ptr(raw), N.ptr(prob), N.ptr(pred),
                                  N.stream_ptr()), "b2f_lr_predict")
-        th = self.getOrDefault("thresholds")
+        th = _parse_thresholds(self.getOrDefault("thresholds"))
         if th is not None:  # argmax of p_k / t_k (A.3)
-            t = torch.tensor([float(v) for v in th], dtype=torch.float32, device=dev)
+            t = torch.tensor(th, dtype=torch.float32, device=dev)
             if t.numel() != nc:
                 raise ValueError("thresholds must have length %d" % nc)
             pred = torch.argmax(prob / t[None, :], dim=1).to(torch.float32)
@@ -262,6 +281,7 @@ class LogisticRegression(Estimator):
         N.check(L.b2f_label_hist(N.ptr(y), N.ptr(w), X.n, nb, N.ptr(hist_t), N.ptr(bad), N.stream_ptr()),
                 "b2f_label_hist")
         comm.all_reduce_sum(hist_t)
+        comm.all_reduce_max(bad)  # a bad label in ONE shard must raise on every rank, not strand the others
         if int(bad.item()):
             raise ValueError("LogisticRegression: labels must be non-negative integers (as doubles)")
         hist = hist_t.cpu().numpy()
@@ -271,6 +291,23 @@ class LogisticRegression(Estimator):
         K = 1 if binomial else nb
         if not binomial and K > 32:
             raise NotImplementedError("LogisticRegression: at most 32 classes are supported, got %d" % K)
+        if fit_icpt and np.count_nonzero(hist) == 1:
+            # MLlib: all labels equal and fitIntercept -> no training; zero coefficients, infinite intercept
+            # (+inf on the constant class; binomial: +inf when every label is 1, -inf when every label is 0)
+            j = int(np.argmax(hist))
+            if binomial:
+                b = np.array([np.inf if num_classes == 2 else -np.inf])
+            else:
+                b = np.zeros(K)
+                b[j] = np.inf
+            summ = LogisticRegressionSummary([], 0, 0)
+            summ.iterates, summ.passesAtState = [], []
+            summ.featuresStd, summ.featuresMean, summ.weightSum, summ.histogram = std, mean, W, hist
+            model = LogisticRegressionModel(np.zeros((K, d)), b, 2 if binomial else K, summ)
+            model._set(featuresCol=g("featuresCol"), labelCol=g("labelCol"), predictionCol=g("predictionCol"),
+                       threshold=g("threshold"), thresholds=g("thresholds"), probabilityCol=g("probabilityCol"),
+                       rawPredictionCol=g("rawPredictionCol"))
+            return model
         active = (std != 0.0).astype(np.float64)
         inv_std = np.where(std != 0.0, 1.0 / np.where(std != 0.0, std, 1.0), 0.0)
         lam2, lam1 = reg * (1.0 - alpha), reg * alpha

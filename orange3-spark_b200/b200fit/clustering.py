@@ -43,12 +43,16 @@ class CudaLloydEngine:
         self.status_f64 = torch.zeros(2, dtype=torch.float64, device=dev)
         self.launches = 0
         self.fallbacks = 0
-        # low-precision filter pass + 3xTF32 re-check (B2F_KM_TCH fp16 / B2F_KM_TCB bf16x3; AUTO = TCH) needs a
-        # labels buffer and a workspace
+        # low-precision filter pass + pair check + 3xTF32 re-check (B2F_KM_TCH fp16 / B2F_KM_TCB bf16x3; AUTO = TCH)
+        # needs a labels buffer and a workspace.  Decided from the SHAPE only (never from this rank's row count):
+        # every rank must take the same branches between collectives, also one whose shard is empty.
         self.use_ws = (algo in (N.KM_AUTO, N.KM_TCB, N.KM_TCH) and w is None and self.d in (64, 128)
-                       and self.k % 128 == 0 and X.ld % 4 == 0 and X.n > 0)
+                       and self.k % 128 == 0 and X.ld % 4 == 0)
         if algo in (N.KM_TCB, N.KM_TCH) and not self.use_ws:
             raise ValueError("B2F_KM_TCB / B2F_KM_TCH need d in {64, 128}, k % 128 == 0 and no row weights")
+        self.col_scale = getattr(X, "col_scale", None)
+        if self.col_scale is not None and not (self.use_ws and algo in (N.KM_AUTO, N.KM_TCH)):
+            raise ValueError("a scaled view needs the fp16 filter pipeline; materialise it first")
         if self.use_ws:
             self.ws_bytes = int(self.L.b2f_kmeans_ws_bytes(X.n, self.k, self.d))
             self.ws = torch.zeros(self.ws_bytes, dtype=torch.uint8, device=dev)
@@ -69,23 +73,38 @@ class CudaLloydEngine:
 
     def step(self, labels=None, exact=False, events=None):
         """Zero accumulators, assign + accumulate this shard, fold -> fp64 payload (device).
-        exact=True forces the 3xTF32 kernel (used when the re-check list of the filter pass overflowed)."""
+        exact=True (used when a list of the filter pass overflowed): 3xTF32 over every row WITH its certainty
+        test and the fp64 tail -- the same label guarantee as the filter pipeline, just slower."""
         s = N.stream_ptr()
         X = self.X
         N.check(self.L.b2f_kmeans_acc_zero(N.ptr(self.acc), self.k, self.d, s), "b2f_kmeans_acc_zero")
         if events:
             events[0].record()
-        if self.use_ws and not exact:
+        if self.use_ws:
             lab = labels if labels is not None else self.labels_buf
-            N.check(self.L.b2f_kmeans_step_ws(N.ptr(X.data), X.n, X.d, X.ld, None, N.ptr(self.prep), self.k,
-                                              N.ptr(self.acc), N.ptr(lab), N.ptr(self.ws), self.ws_bytes, self.algo,
-                                              s), "b2f_kmeans_step_ws")
-            # filter kernel, gather, 3xTF32 re-check, scatter, exact tail (+ 2 cost-term kernels around the fp16 filter)
-            self.launches += 5 if self.algo == N.KM_TCB else 7
+            if exact and self.col_scale is not None:
+                # rare path (list overflow on a scaled view): run it on the materialised copy
+                Xm = X.materialized()
+                N.check(self.L.b2f_kmeans_step_ws(N.ptr(Xm.data), Xm.n, Xm.d, Xm.ld, None, N.ptr(self.prep), self.k,
+                                                  N.ptr(self.acc), N.ptr(lab), N.ptr(self.ws), self.ws_bytes,
+                                                  N.KM_TC3, s), "b2f_kmeans_step_ws")
+                self.launches += 3
+            elif self.col_scale is not None:
+                N.check(self.L.b2f_kmeans_step_scaled(N.ptr(X.data), X.n, X.d, X.ld, N.ptr(self.col_scale),
+                                                      N.ptr(self.prep), self.k, N.ptr(self.acc), N.ptr(lab),
+                                                      N.ptr(self.ws), self.ws_bytes, s), "b2f_kmeans_step_scaled")
+                self.launches += 10  # as below + the two folds around the filter kernel
+            else:
+                algo = N.KM_TC3 if exact else self.algo
+                N.check(self.L.b2f_kmeans_step_ws(N.ptr(X.data), X.n, X.d, X.ld, None, N.ptr(self.prep), self.k,
+                                                  N.ptr(self.acc), N.ptr(lab), N.ptr(self.ws), self.ws_bytes, algo,
+                                                  s), "b2f_kmeans_step_ws")
+                # TCH: 2 cost-term kernels + filter + pair check + gather + 3xTF32 re-check + scatter + exact tail;
+                # TCB: filter + gather + re-check + scatter + exact tail; exact: set-cap + 3xTF32 + exact tail
+                self.launches += 3 if exact else (5 if self.algo == N.KM_TCB else 8)
         else:
-            algo = N.KM_TC3 if (exact or self.algo in (N.KM_TCB, N.KM_TCH)) else self.algo
             N.check(self.L.b2f_kmeans_step(N.ptr(X.data), X.n, X.d, X.ld, N.ptr(self.w), N.ptr(self.prep), self.k,
-                                           N.ptr(self.acc), N.ptr(labels), algo, s), "b2f_kmeans_step")
+                                           N.ptr(self.acc), N.ptr(labels), self.algo, s), "b2f_kmeans_step")
             self.launches += 1
         if events:
             events[1].record()
@@ -120,35 +139,47 @@ class CudaLloydEngine:
         return payload[kd: kd + self.k].cpu().numpy().copy()
 
 
-def lloyd(engine, comm, max_iter, tol):
+def lloyd(engine, comm, max_iter, tol, n_total=None):
     """A.2 iteration loop: stop at maxIter or when every moved centre moved <= tol; the final
-    model holds the updated centres; trainingCost is the cost of the LAST assignment step."""
+    model holds the updated centres; trainingCost is the cost of the LAST assignment step.
+    Every branch that precedes a collective is taken on all-reduced values, so all ranks stay in step."""
     it, converged, costs = 0, False, []
     payload = None
-    n_total = None
+    use_ws = bool(getattr(engine, "use_ws", False))  # shape-derived: identical on every rank
+    if use_ws and n_total is None:
+        import torch
+
+        t = torch.tensor([float(engine.X.n)], dtype=torch.float64, device=engine.dev)
+        comm.all_reduce_sum(t)
+        n_total = float(t.item())
     while it < max_iter and not converged:
         payload = engine.step()
         comm.all_reduce_sum(payload)
-        if getattr(engine, "use_ws", False):
-            rows = engine.rows_counted(payload)
-            if n_total is None:
-                import torch
-
-                t = torch.tensor([float(engine.X.n)], dtype=torch.float64, device=payload.device)
-                comm.all_reduce_sum(t)
-                n_total = float(t.item())
-            if rows != n_total:  # some rank dropped uncertain rows: redo this pass with the 3xTF32 kernel
-                engine.fallbacks += 1
-                payload = engine.step(exact=True)
-                comm.all_reduce_sum(payload)
+        if use_ws and engine.rows_counted(payload) != n_total:
+            # some rank dropped uncertain rows (a list of the filter pass overflowed): redo the pass on every rank
+            # with 3xTF32 + certainty test + fp64 tail, whose list has room for every row
+            engine.fallbacks += 1
+            payload = engine.step(exact=True)
+            comm.all_reduce_sum(payload)
+            if engine.rows_counted(payload) != n_total:
+                raise RuntimeError("KMeans: %d of %d rows were not assigned (workspace smaller than "
+                                   "b2f_kmeans_ws_bytes?)" % (n_total - engine.rows_counted(payload), n_total))
         converged, cost = engine.finalize(payload, tol)
         costs.append(cost)
         it += 1
     return it, costs, converged, payload
 
 
-def predict_labels(X, centers, want_dist=False, algo=N.KM_AUTO):
-    """Assignment only (KMeansModel.transform / computeCost / initialisers)."""
+def ws_dropped(ws):
+    """Rows a b2f_kmeans_*_ws call could not place in its lists (header of the workspace, include/b200fit.h)."""
+    h = ws[:16].view(_torch().int32).cpu().numpy()
+    return max(0, int(h[0]) - int(h[3])) + max(0, int(h[2]) - int(h[3]))
+
+
+def predict_labels(X, centers, want_dist=False, algo=N.KM_AUTO, info=None):
+    """Assignment only (KMeansModel.transform / computeCost / initialisers).  Where the shape allows it the labels
+    come from the same certainty pipeline as the fit (filter pass, pair check, 3xTF32 re-check, fp64 tail), so they
+    equal the fp64 assignment except for fp64-level ties; distances are those to the labelled centre."""
     N.require_cuda()
     torch = _torch()
     L = N.lib()
@@ -162,8 +193,28 @@ def predict_labels(X, centers, want_dist=False, algo=N.KM_AUTO):
     N.check(L.b2f_kmeans_prepare(N.ptr(cdev), k, d, N.ptr(prep), N.stream_ptr()), "b2f_kmeans_prepare")
     labels = torch.empty(X.n, dtype=torch.int32, device=dev)
     dist = torch.empty(X.n, dtype=torch.float32, device=dev) if want_dist else None
-    N.check(L.b2f_kmeans_predict(N.ptr(X.data), X.n, d, X.ld, N.ptr(prep), k, N.ptr(labels), N.ptr(dist), algo,
-                                 N.stream_ptr()), "b2f_kmeans_predict")
+    tc_shape = d % 32 == 0 and 32 <= d <= 128 and k % 128 == 0 and X.ld % 4 == 0
+    scale = getattr(X, "col_scale", None)
+    if scale is not None and not (tc_shape and d in (64, 128) and algo in (N.KM_AUTO, N.KM_TCH)):
+        X, scale = X.materialized(), None
+    if not tc_shape or algo in (N.KM_GENERIC, N.KM_TC1) or X.n == 0:
+        N.check(L.b2f_kmeans_predict(N.ptr(X.data), X.n, d, X.ld, N.ptr(prep), k, N.ptr(labels), N.ptr(dist), algo,
+                                     N.stream_ptr()), "b2f_kmeans_predict")
+        return (labels, dist) if want_dist else labels
+    ws_bytes = int(L.b2f_kmeans_ws_bytes(X.n, k, d))
+    ws = torch.zeros(ws_bytes, dtype=torch.uint8, device=dev)
+    N.check(L.b2f_kmeans_predict_ws(N.ptr(X.data), X.n, d, X.ld, N.ptr(scale), N.ptr(prep), k, N.ptr(labels),
+                                    N.ptr(dist), N.ptr(ws), ws_bytes, algo, N.stream_ptr()), "b2f_kmeans_predict_ws")
+    dropped = ws_dropped(ws)
+    if info is not None:
+        info["dropped_first_pass"] = dropped
+    if dropped:  # a list overflowed: 3xTF32 over every row with its certainty test + fp64 tail (room for all rows)
+        Xm = X.materialized() if scale is not None else X
+        N.check(L.b2f_kmeans_predict_ws(N.ptr(Xm.data), Xm.n, d, Xm.ld, None, N.ptr(prep), k, N.ptr(labels),
+                                        N.ptr(dist), N.ptr(ws), ws_bytes, N.KM_TC3, N.stream_ptr()),
+                "b2f_kmeans_predict_ws")
+        if ws_dropped(ws):
+            raise RuntimeError("KMeans predict: rows left unassigned after the exact fallback")
     return (labels, dist) if want_dist else labels
 
 
@@ -229,7 +280,7 @@ class KMeansModel(Model):
 
     def _transform(self, dataset):
         frame = as_frame(dataset)
-        X = to_device_matrix(frame.col(self.getOrDefault("featuresCol")))
+        X = to_device_matrix(frame.col(self.getOrDefault("featuresCol")), allow_scaled=True)
         labels = predict_labels(X, self._centers)
         return frame.withColumn(self.getOrDefault("predictionCol"), labels)
 
@@ -239,7 +290,7 @@ class KMeansModel(Model):
 
     def computeCost(self, dataset):
         frame = as_frame(dataset)
-        X = to_device_matrix(frame.col(self.getOrDefault("featuresCol")))
+        X = to_device_matrix(frame.col(self.getOrDefault("featuresCol")), allow_scaled=True)
         _, dist = predict_labels(X, self._centers, want_dist=True)
         c = dist.double().sum().reshape(1)
         Comm().all_reduce_sum(c)
@@ -282,9 +333,13 @@ class KMeans(Estimator):
         if g("distanceMeasure") != "euclidean":
             raise ValueError("KMeans: only distanceMeasure='euclidean' is supported, got %r" % g("distanceMeasure"))
         frame = as_frame(dataset)
-        X = to_device_matrix(frame.col(g("featuresCol")))
+        X = to_device_matrix(frame.col(g("featuresCol")), allow_scaled=True)
         wcol = g("weightCol")
         w = to_device_vector(frame.col(wcol), X.n) if wcol else None
+        if getattr(X, "col_scale", None) is not None and not (
+                w is None and self._algo in (N.KM_AUTO, N.KM_TCH)
+                and N.lib().b2f_kmeans_scaled_supported(int(k), X.d, X.ld)):
+            X = X.materialized()  # shapes the fused scaled pass does not take: write the scaled copy once
         comm = Comm()
         nt = torch.tensor([X.n], dtype=torch.int64, device=X.data.device)
         comm.all_reduce_sum(nt)
@@ -305,7 +360,7 @@ class KMeans(Estimator):
             raise ValueError("KMeans: unsupported initMode %r" % g("initMode"))
         eng = CudaLloydEngine(X, k, w=w, algo=self._algo)
         eng.set_centers(C0)
-        it, costs, converged, payload = lloyd(eng, comm, max_iter, tol)
+        it, costs, converged, payload = lloyd(eng, comm, max_iter, tol, float(n_total))
         sizes = eng.get_counts(payload) if payload is not None else np.zeros(k)
         model = KMeansModel(eng.get_centers(),
                             KMeansSummary(k, it, costs[-1] if costs else float("nan"), sizes, costs, converged))

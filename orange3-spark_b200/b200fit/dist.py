@@ -43,6 +43,20 @@ class Comm:
             self._dist.broadcast(t, src=src, group=self.group)
         return t
 
+    def any_rank(self, flag, device=None):
+        """True on EVERY rank iff `flag` is true on at least one.  Error conditions found in one rank's shard (a bad
+        label, a ragged column) are tested through this before raising: a rank that raises alone leaves the others
+        blocked in the next collective."""
+        if not (self.active and self.world > 1):
+            return bool(flag)
+        import torch
+
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else "cpu"
+        t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=device)
+        self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX, group=self.group)
+        return bool(int(t.item()))
+
     def barrier(self):
         if self.active and self.world > 1:
             self._dist.barrier(group=self.group)

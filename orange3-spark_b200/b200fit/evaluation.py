@@ -16,6 +16,8 @@ so the widget works as written).
 Row-sharded multi-GPU: the silhouette statistics and the confusion matrix are all-reduced; the ranking metrics need a
 global sort and are single-rank only.
 """
+from abc import ABCMeta, abstractmethod
+
 import numpy as np
 
 from . import _native as N
@@ -27,10 +29,12 @@ from .param import TypeConverters as TC
 from .param import make_accessors
 
 
-class Evaluator(Params):
-    """pyspark.ml.evaluation.Evaluator protocol: evaluate(dataset, params=None), isLargerBetter()."""
+class Evaluator(Params, metaclass=ABCMeta):
+    """pyspark.ml.evaluation.Evaluator protocol: evaluate(dataset, params=None), isLargerBetter().  Abstract, as in
+    pyspark: the widget's discovery skips abstract classes (orangecontrib/spark/utils/ml_api_utils.py:59-62)."""
 
-    def _evaluate(self, dataset):  # pragma: no cover - abstract
+    @abstractmethod
+    def _evaluate(self, dataset):
         raise NotImplementedError
 
     def evaluate(self, dataset, params=None):
@@ -83,11 +87,11 @@ class ClusteringEvaluator(Evaluator):
         lab = frame.col(self.getOrDefault("predictionCol"))
         lab = lab if isinstance(lab, torch.Tensor) else torch.from_numpy(np.asarray(lab))
         lab = lab.to(device=X.data.device, dtype=torch.int32).contiguous()
-        if lab.shape[0] != X.n:
-            raise ValueError("prediction column has %d rows, features %d" % (lab.shape[0], X.n))
+        comm = Comm()
+        if comm.any_rank(lab.shape[0] != X.n):  # tested on every rank together: nobody raises alone
+            raise ValueError("prediction column has %d rows, features %d (this or another rank)" % (lab.shape[0], X.n))
         wname = self.getOrDefault("weightCol") if self.isDefined("weightCol") else None
         w = _weights(frame, wname, X.n)
-        comm = Comm()
         kmax = torch.tensor([int(lab.max().item()) + 1 if X.n else 0], dtype=torch.int64, device=X.data.device)
         comm.all_reduce_max(kmax)
         k = int(kmax.item())
@@ -100,6 +104,7 @@ class ClusteringEvaluator(Evaluator):
         N.check(L.b2f_silhouette_stats(N.ptr(X.data), X.n, X.d, X.ld, N.ptr(lab), N.ptr(w), k, N.ptr(stats),
                                        N.ptr(bad), s), "b2f_silhouette_stats")
         comm.all_reduce_sum(stats)
+        comm.all_reduce_max(bad)
         if int(bad.item()):
             raise ValueError("ClusteringEvaluator: negative cluster index in %r" % self.getOrDefault("predictionCol"))
         scratch = torch.empty(int(L.b2f_silhouette_scratch_bytes(k, X.d)), dtype=torch.uint8, device=X.data.device)

@@ -59,6 +59,7 @@ def pack_columns(cols, chunk_rows=1 << 22, handle_invalid="error", row0=0):
     flat = []
     for c in cols:
         if isinstance(c, DeviceMatrix):
+            c = c.materialized()
             for j in range(c.d):
                 flat.append((c.data[:, j].contiguous(), N.F32))
             continue
@@ -117,15 +118,17 @@ def pack_columns(cols, chunk_rows=1 << 22, handle_invalid="error", row0=0):
             i += 1
         del esz
     if handle_invalid == "error" and int(bad.item()) != 0:
-        raise ValueError("VectorAssembler: encountered NaN/Inf while assembling a row with handleInvalid='error'")
+        raise ValueError("VectorAssembler: encountered NaN while assembling a row with handleInvalid='error'; "
+                         "remove the NaNs or use handleInvalid='keep'")
     return DeviceMatrix(X, d, row0)
 
 
-def to_device_matrix(col):
-    """Accepts whatever sits in a features column and returns a DeviceMatrix."""
+def to_device_matrix(col, allow_scaled=False):
+    """Accepts whatever sits in a features column and returns a DeviceMatrix.  A scaled VIEW (DeviceMatrix with a
+    pending col_scale) is handed through only to callers that fold the factor into their kernels."""
     torch = _torch()
     if isinstance(col, DeviceMatrix):
-        return col
+        return col if allow_scaled else col.materialized()
     if isinstance(col, torch.Tensor) and col.is_cuda and col.dim() == 2 and col.dtype == torch.float32 \
             and col.stride(1) == 1 and col.shape[1] % 4 == 0 and col.data_ptr() % 16 == 0 \
             and (col.shape[0] <= 1 or col.stride(0) % 4 == 0):
@@ -256,7 +259,12 @@ class StandardScalerModel(Model):
         if self.getOrDefault("withMean"):
             shift[: X.d] = self.mean
         sc = torch.from_numpy(scale[: X.d].astype(np.float32)).to(X.data.device)
-        sh = torch.from_numpy(shift[: X.d].astype(np.float32)).to(X.data.device) if self.getOrDefault("withMean") else None
+        if not self.getOrDefault("withMean"):
+            # pure scaling: hand back a VIEW (raw rows + per-column factor).  KMeans folds the factor into its
+            # operand conversion (b2f_kmeans_step_scaled), so cfg 5 never writes a second 200M x 64 matrix;
+            # any other consumer materialises the copy on first use (DeviceMatrix.materialized).
+            return frame.withColumn(out, DeviceMatrix(X.data, X.d, X.row0, col_scale=sc))
+        sh = torch.from_numpy(shift[: X.d].astype(np.float32)).to(X.data.device)
         Y = torch.empty_like(X.data)
         N.check(N.lib().b2f_scale_columns(N.ptr(X.data), N.ptr(Y), X.n, X.d, X.ld, N.ptr(sc), N.ptr(sh),
                                           N.stream_ptr()), "b2f_scale_columns")

@@ -11,21 +11,48 @@ import numpy as np
 
 class DeviceMatrix:
     """Row-major fp32 feature tile X[n, ld] resident in HBM; ld % 4 == 0 so every row is a
-    legal 16-byte / TMA row.  `row0` is the global index of the first row (row shards)."""
+    legal 16-byte / TMA row.  `row0` is the global index of the first row (row shards).
 
-    def __init__(self, data, d, row0=0):
+    `col_scale` (optional, fp32[d] on the device) makes this a VIEW of data * col_scale -- what
+    StandardScalerModel.transform returns when it only scales (withStd, no centering): consumers
+    that can fold the factor into their kernels (the KMeans filter pipeline) read `data` and
+    `col_scale`; everybody else calls materialized(), which writes the scaled copy once."""
+
+    def __init__(self, data, d, row0=0, col_scale=None):
         assert data.dim() == 2 and data.is_cuda and data.stride(1) == 1
         self.data = data
         self.n = int(data.shape[0])
         self.ld = int(data.stride(0)) if self.n > 1 else int(data.shape[1])
         self.d = int(d)
         self.row0 = int(row0)
+        self.col_scale = col_scale
+        self._copy = None
 
     def __len__(self):
         return self.n
 
+    def materialized(self):
+        """A DeviceMatrix without a pending column scale (self when there is none)."""
+        if self.col_scale is None:
+            return self
+        if self._copy is None:
+            import torch
+
+            from . import _native as N
+
+            Y = torch.empty_like(self.data)
+            N.check(N.lib().b2f_scale_columns(N.ptr(self.data), N.ptr(Y), self.n, self.d, self.ld,
+                                              N.ptr(self.col_scale), None, N.stream_ptr()), "b2f_scale_columns")
+            self._copy = DeviceMatrix(Y, self.d, self.row0)
+        return self._copy
+
+    def rows(self, idx):
+        """Rows idx (device int64 tensor) as fp32 [m, d], scaled the way the kernels see them."""
+        r = self.data[idx, : self.d]
+        return r if self.col_scale is None else r * self.col_scale[None, :]
+
     def numpy(self):
-        return self.data[:, : self.d].cpu().numpy()
+        return self.materialized().data[:, : self.d].cpu().numpy()
 
 
 class _Col:
@@ -42,8 +69,11 @@ class _Col:
 
 
 class ColumnarFrame:
-    def __init__(self, columns=None):
+    def __init__(self, columns=None, origin=None):
         self._cols = dict(columns or {})
+        # (pandas frame the columns were taken from, names taken): lets Model.transform hand the caller's own
+        # frame type back with only the NEW columns converted (return_like)
+        self._origin = origin
         n = {len(v) for v in self._cols.values()}
         if len(n) > 1:
             raise ValueError("ragged columns: lengths %s" % sorted(n))
@@ -56,7 +86,7 @@ class ColumnarFrame:
             if v.dtype == object and len(v) and hasattr(v[0], "toArray"):  # pyspark Vector cells
                 v = np.stack([x.toArray() for x in v])
             cols[str(name)] = v
-        return cls(cols)
+        return cls(cols, origin=(pdf, {k: id(v) for k, v in cols.items()}))
 
     @property
     def columns(self):
@@ -83,7 +113,7 @@ class ColumnarFrame:
         elif isinstance(value, _Col):
             value = value.frame._cols[value.name]
         cols[name] = value
-        return ColumnarFrame(cols)
+        return ColumnarFrame(cols, origin=self._origin)
 
     def select(self, *names):
         return ColumnarFrame({n: self.col(n) for n in names})
@@ -119,9 +149,56 @@ def _cast_float(v, dt):
     return np.asarray(v).astype(dt)
 
 
+def _host_column(v):
+    """A frame column as something a pandas DataFrame can hold: 1-D -> numpy, 2-D (vector column) -> list of rows."""
+    if isinstance(v, DeviceMatrix):
+        return list(v.numpy())
+    if hasattr(v, "cpu"):
+        v = v.cpu().numpy()
+    v = np.asarray(v)
+    return list(v) if v.ndim == 2 else v
+
+
+def return_like(dataset, out):
+    """Hand a transform result back in the CALLER's frame type (the reference's Model widget
+    does `self.out_df = model.transform(self.in_df)`, orangecontrib/spark/widgets/ml/spark_ml_model.py:53-54, and
+    sends it on as a DataFrame):
+      ColumnarFrame / dict in           -> ColumnarFrame out (device-resident columns stay on the device);
+      pandas DataFrame in               -> pandas DataFrame = the caller's frame + the new columns;
+      pyspark-like DataFrame in         -> `session.createDataFrame(pandas frame)` of the same session
+        (anything with toPandas() and a sparkSession / sql_ctx exposing createDataFrame; vector-valued new
+        columns become pyspark.ml.linalg dense vectors when pyspark is importable, lists otherwise).
+    A result that holds a DeviceMatrix (VectorAssembler / StandardScaler output: tens of GB at the BASELINE
+    sizes) is never copied back: it stays a ColumnarFrame handle, which offers what the widgets use
+    (.columns, [name], withColumn, cache)."""
+    if isinstance(dataset, (ColumnarFrame, dict)) or not isinstance(out, ColumnarFrame):
+        return out
+    if any(isinstance(v, DeviceMatrix) for v in out._cols.values()):
+        return out
+    if out._origin is None:
+        return out
+    pdf, taken = out._origin
+    res = pdf.copy(deep=False)
+    for c in out.columns:  # only columns that are new, or were replaced, since the frame was taken from `pdf`
+        if taken.get(c) != id(out._cols[c]):
+            res[c] = _host_column(out._cols[c])
+    session = getattr(dataset, "sparkSession", None) or getattr(dataset, "sql_ctx", None)
+    if hasattr(dataset, "toPandas") and session is not None and hasattr(session, "createDataFrame"):
+        try:
+            from pyspark.ml.linalg import Vectors  # absent here; the list form below is what gets tested
+
+            for c in res.columns:
+                if len(res) and isinstance(res[c].iloc[0], np.ndarray):
+                    res[c] = [Vectors.dense(x) for x in res[c]]
+        except ImportError:
+            pass
+        return session.createDataFrame(res)
+    return res
+
+
 def as_frame(dataset):
-    """ColumnarFrame as-is; dict of columns; pandas DataFrame; or (UNTESTED here: no pyspark)
-    a pyspark DataFrame, collected through toPandas()."""
+    """ColumnarFrame as-is; dict of columns; pandas DataFrame; or a pyspark-like DataFrame (anything with
+    toPandas(): with Arrow enabled that is Spark's columnar collect), see return_like for the way back."""
     if isinstance(dataset, ColumnarFrame):
         return dataset
     if isinstance(dataset, dict):

@@ -2,6 +2,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 static thread_local char g_err[512] = "";
@@ -25,6 +27,30 @@ int b2f_sm_count() {
   return cached[dev];
 }
 
-extern "C" int b2f_version(void) { return 100; }
+cudaError_t b2f_smem_attr_impl(const void* kernel, size_t bytes) {
+  struct Entry {
+    const void* fn;
+    int dev;
+    size_t bytes;
+  };
+  static Entry table[256];
+  static int used = 0;
+  static std::mutex mu;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lock(mu);
+  Entry* hit = nullptr;
+  for (int i = 0; i < used; ++i)
+    if (table[i].fn == kernel && table[i].dev == dev) hit = &table[i];
+  if (hit && hit->bytes >= bytes) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (e != cudaSuccess) return e;
+  if (hit) hit->bytes = bytes;
+  else if (used < 256) table[used++] = Entry{kernel, dev, bytes};
+  return cudaSuccess;
+}
+
+extern "C" int b2f_version(void) { return 200; }
 
 extern "C" const char* b2f_last_error(void) { return g_err; }

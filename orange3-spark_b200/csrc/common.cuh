@@ -36,6 +36,14 @@ static inline cudaStream_t b2f_cs(b2f_stream_t s) { return reinterpret_cast<cuda
 // number of SMs of the current device (cached per device)
 int b2f_sm_count();
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize, set once per (kernel, device) and again only when a launch needs
+// more (api.cu keeps the table; the attribute call is not free and sat on every step before)
+cudaError_t b2f_smem_attr_impl(const void* kernel, size_t bytes);
+template <typename F>
+static inline cudaError_t b2f_smem_attr(F kernel, size_t bytes) {
+  return b2f_smem_attr_impl(reinterpret_cast<const void*>(kernel), bytes);
+}
+
 static inline size_t b2f_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---- kmeans buffer layouts (shared by kmeans_generic.cu / kmeans_tc.cu) ----
@@ -139,9 +147,14 @@ struct KmRecheck {
   const float* cmax;
 };
 
-// implemented in kmeans_generic.cu: exact (fp64, direct form) assignment + accumulation of listed rows
-int km_exact_rows(const float* X, int64_t ld, int d, const void* prep, int k, void* acc, int32_t* labels,
-                  const int* count, const int32_t* idx, int cap, bool accumulate, cudaStream_t stream);
+// implemented in kmeans_generic.cu: exact (fp64) assignment + accumulation of listed rows.
+// colscale (optional, fp32[d]): the rows are taken as fl32(x * colscale) -- the StandardScaler fold.
+int km_exact_rows(const float* X, int64_t ld, int d, const float* colscale, const void* prep, int k, void* acc,
+                  int32_t* labels, const int* count, const int32_t* idx, int cap, bool accumulate,
+                  cudaStream_t stream);
+// squared distance (fp32, direct form on the fp32 centres) of every row to the centre its label names
+int km_dist_to_label(const float* X, int64_t n, int d, int64_t ld, const float* colscale, const void* prep, int k,
+                     const int32_t* labels, float* dist2, cudaStream_t stream);
 
 // implemented in kmeans_tc.cu
 // n_dev (optional, device): the kernel processes min(n, *n_dev) rows (row count known only on the device)
@@ -149,14 +162,17 @@ int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, i
                int passes, bool accumulate, const int* n_dev, const KmRecheck* recheck, cudaStream_t stream);
 bool km_tc_supported(int k, int d, int64_t ld);
 
-// implemented in kmeans_tcb.cu (filter pass + 3xTF32 re-check of uncertain rows + exact fp64 tail)
-// filter: KM_FILTER_BF16X3 = three bf16 MMAs per product, KM_FILTER_FP16 = one fp16 MMA (scaled operands)
+// implemented in kmeans_tcb.cu (filter pass + pair check + 3xTF32 re-check of uncertain rows + exact fp64 tail)
+// filter: KM_FILTER_BF16X3 = three bf16 MMAs per product, KM_FILTER_FP16 = one fp16 MMA (scaled operands),
+//         KM_FILTER_NONE = no filter pass: 3xTF32 over every row with its certainty test, then the fp64 tail
 #define KM_FILTER_BF16X3 0
 #define KM_FILTER_FP16 1
+#define KM_FILTER_NONE 2
 bool km_tcb_supported(int k, int d, int64_t ld);
 size_t km_tcb_ws_bytes(int64_t n, int k, int d);
-int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
-                void* ws, size_t ws_bytes, bool accumulate, int filter, cudaStream_t stream);
+// colscale (optional, fp32[d], FP16 filter only): the pass runs on the rows fl32(x * colscale) without a scaled copy
+int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colscale, const void* prep, int k, void* acc,
+                int32_t* labels, void* ws, size_t ws_bytes, bool accumulate, int filter, cudaStream_t stream);
 
 // implemented in lr_tc.cu (tcgen05 multinomial loss + gradient)
 bool lr_mn_tc_supported(int d, int64_t ld, int K);

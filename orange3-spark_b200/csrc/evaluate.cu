@@ -113,9 +113,9 @@ __global__ void sil_means_kernel(const double* __restrict__ stats, int k, int d,
 
 extern "C" int b2f_silhouette_stats(const float* X, int64_t n, int d, int64_t ld, const int32_t* labels,
                                     const float* w, int k, double* stats, int32_t* bad_flag, b2f_stream_t stream) {
-  B2F_REQUIRE(X && labels && stats, "b2f_silhouette_stats: null pointer");
   B2F_REQUIRE(d > 0 && k > 0 && n >= 0 && ld >= d, "b2f_silhouette_stats: bad shape");
   if (n == 0) return B2F_OK;
+  B2F_REQUIRE(X && labels && stats, "b2f_silhouette_stats: null pointer");
   int64_t want = (n + 7) / 8;
   int64_t cap = (int64_t)b2f_sm_count() * 16;
   sil_stats_kernel<<<(unsigned)(want < cap ? want : cap), 256, 0, b2f_cs(stream)>>>(X, n, d, ld, labels, w, k, stats,
@@ -131,11 +131,11 @@ extern "C" size_t b2f_silhouette_scratch_bytes(int k, int d) {
 extern "C" int b2f_silhouette_score(const float* X, int64_t n, int d, int64_t ld, const int32_t* labels,
                                     const float* w, int k, const double* stats, void* scratch, double* out,
                                     b2f_stream_t stream) {
-  B2F_REQUIRE(X && labels && stats && scratch && out, "b2f_silhouette_score: null pointer");
   B2F_REQUIRE(d > 0 && k > 0 && n >= 0 && ld >= d, "b2f_silhouette_score: bad shape");
   const int ds = (d + 3) & ~3;
   B2F_REQUIRE(ds <= SIL_TILE_FLOATS, "b2f_silhouette_score: d = %d above %d", d, SIL_TILE_FLOATS);
   if (n == 0) return B2F_OK;
+  B2F_REQUIRE(X && labels && stats && scratch && out, "b2f_silhouette_score: null pointer");
   float* mu = static_cast<float*>(scratch);
   float* q = mu + (size_t)k * d;
   sil_means_kernel<<<(k * (d + 1) + 255) / 256, 256, 0, b2f_cs(stream)>>>(stats, k, d, mu, q);

@@ -242,11 +242,11 @@ static int km_generic_launch(const float* X, int64_t n, int d, int64_t ld, const
   int grid = (int)(nblocks < cap ? nblocks : cap);
   if (grid < 1) grid = 1;
   if (acc) {
-    B2F_CUDA(cudaFuncSetAttribute(km_generic_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2F_CUDA(b2f_smem_attr(km_generic_kernel<true>, smem));
     km_generic_kernel<true><<<grid, KG_THREADS, smem, st>>>(X, n, d, ld, w, C32, k, payload, rep, labels, dist2,
                                                             tile_k, table_reps);
   } else {
-    B2F_CUDA(cudaFuncSetAttribute(km_generic_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2F_CUDA(b2f_smem_attr(km_generic_kernel<false>, smem));
     km_generic_kernel<false><<<grid, KG_THREADS, smem, st>>>(X, n, d, ld, w, C32, k, payload, rep, labels, dist2,
                                                              tile_k, 0);
   }
@@ -266,6 +266,7 @@ static int km_generic_launch(const float* X, int64_t n, int d, int64_t ld, const
 #define KX_ROWS 32
 #define KX_MAX_D 512
 __global__ void __launch_bounds__(256) km_exact_kernel(const float* __restrict__ X, int64_t ld, int d,
+                                                       const float* __restrict__ colscale,
                                                        const double* __restrict__ C64,
                                                        const double* __restrict__ CN64, int k,
                                                        double* __restrict__ payload, int32_t* __restrict__ labels,
@@ -282,7 +283,13 @@ __global__ void __launch_bounds__(256) km_exact_kernel(const float* __restrict__
     __syncthreads();
     for (int i = threadIdx.x; i < KX_ROWS * dpad; i += 256) {
       const int r = i / dpad, t = i - r * dpad;
-      xs[i] = (g0 + r < used && t < d) ? (double)X[(int64_t)idx[g0 + r] * ld + t] : 0.0;
+      // (scaled pass: the row is fl32(x * scale), the value a materialised StandardScaler copy would hold)
+      float xv = 0.f;
+      if (g0 + r < used && t < d) {
+        xv = X[(int64_t)idx[g0 + r] * ld + t];
+        if (colscale) xv = __fmul_rn(xv, colscale[t]);
+      }
+      xs[i] = (double)xv;
     }
     __syncthreads();
     double xn[4], best[4];
@@ -362,8 +369,9 @@ __global__ void __launch_bounds__(256) km_exact_kernel(const float* __restrict__
   }
 }
 
-int km_exact_rows(const float* X, int64_t ld, int d, const void* prep, int k, void* acc, int32_t* labels,
-                  const int* count, const int32_t* idx, int cap, bool accumulate, cudaStream_t stream) {
+int km_exact_rows(const float* X, int64_t ld, int d, const float* colscale, const void* prep, int k, void* acc,
+                  int32_t* labels, const int* count, const int32_t* idx, int cap, bool accumulate,
+                  cudaStream_t stream) {
   B2F_REQUIRE(d <= KX_MAX_D, "exact re-check: d = %d above %d", d, KX_MAX_D);
   KmPrepLayout P = km_prep_layout(k, d);
   const double* c64 = reinterpret_cast<const double*>(static_cast<const char*>(prep) + P.off_c64);
@@ -372,11 +380,62 @@ int km_exact_rows(const float* X, int64_t ld, int d, const void* prep, int k, vo
   if (accumulate) payload = reinterpret_cast<double*>(static_cast<char*>(acc) + km_acc_layout(k, d).off_payload);
   const int dpad = (d + 31) & ~31;
   const size_t smem = ((size_t)KX_ROWS * dpad + 32 * 34) * sizeof(double);
-  B2F_CUDA(cudaFuncSetAttribute(km_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  B2F_CUDA(b2f_smem_attr(km_exact_kernel, smem));
   int grid = (cap + KX_ROWS - 1) / KX_ROWS;
   if (grid > b2f_sm_count() * 4) grid = b2f_sm_count() * 4;
-  km_exact_kernel<<<grid, 256, smem, stream>>>(X, ld, d, c64, cn64, k, payload, labels, count, idx, cap,
+  km_exact_kernel<<<grid, 256, smem, stream>>>(X, ld, d, colscale, c64, cn64, k, payload, labels, count, idx, cap,
                                                accumulate ? 1 : 0);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// squared distance of every row to the centre its label names: sum (x - c)^2 in fp32 on the fp32 centres, the
+// same direct form the generic kernel reports.  Warp per row, 16-byte loads; the centre table stays in L2.
+// Serves computeCost and the k-means|| rounds when the labels come from the tensor-core pipeline.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) km_dist_label_kernel(const float* __restrict__ X, int64_t n, int d, int64_t ld,
+                                                            const float* __restrict__ colscale,
+                                                            const float* __restrict__ C32, int k,
+                                                            const int32_t* __restrict__ labels,
+                                                            float* __restrict__ dist2) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < n; r += nwarps) {
+    const int lbl = labels[r];
+    float a = 0.f;
+    if (lbl >= 0 && lbl < k) {
+      const float* xr = X + r * ld;
+      const float* cr = C32 + (size_t)lbl * d;
+      for (int c = lane * 4; c < d; c += 128) {
+        float4 x = ldg_stream(reinterpret_cast<const float4*>(xr + c));
+        if (colscale) {
+          x.x = __fmul_rn(x.x, colscale[c]);
+          if (c + 1 < d) x.y = __fmul_rn(x.y, colscale[c + 1]);
+          if (c + 2 < d) x.z = __fmul_rn(x.z, colscale[c + 2]);
+          if (c + 3 < d) x.w = __fmul_rn(x.w, colscale[c + 3]);
+        }
+        float t = x.x - cr[c];
+        a = fmaf(t, t, a);
+        if (c + 1 < d) { t = x.y - cr[c + 1]; a = fmaf(t, t, a); }
+        if (c + 2 < d) { t = x.z - cr[c + 2]; a = fmaf(t, t, a); }
+        if (c + 3 < d) { t = x.w - cr[c + 3]; a = fmaf(t, t, a); }
+      }
+    }
+    a = warp_sum(a);
+    if (lane == 0) dist2[r] = a;
+  }
+}
+
+int km_dist_to_label(const float* X, int64_t n, int d, int64_t ld, const float* colscale, const void* prep, int k,
+                     const int32_t* labels, float* dist2, cudaStream_t stream) {
+  KmPrepLayout P = km_prep_layout(k, d);
+  const float* c32 = reinterpret_cast<const float*>(static_cast<const char*>(prep) + P.off_c32);
+  int64_t want = (n + 7) / 8;
+  int64_t cap = (int64_t)b2f_sm_count() * 16;
+  km_dist_label_kernel<<<(unsigned)(want < cap ? want : cap), 256, 0, stream>>>(X, n, d, ld, colscale, c32, k, labels,
+                                                                               dist2);
   B2F_LAUNCH_CHECK();
   return B2F_OK;
 }
@@ -385,7 +444,8 @@ int km_exact_rows(const float* X, int64_t ld, int d, const void* prep, int k, vo
 // fold / finalize
 // ---------------------------------------------------------------------------------------------
 __global__ void km_fold_kernel(double* __restrict__ payload, float* __restrict__ rep,
-                               unsigned long long* __restrict__ cnt, int k, int d) {
+                               unsigned long long* __restrict__ cnt, int k, int d,
+                               const float* __restrict__ colscale) {
   const size_t kd = (size_t)k * d;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < kd; i += (size_t)gridDim.x * blockDim.x) {
     double s = 0.0;
@@ -394,6 +454,7 @@ __global__ void km_fold_kernel(double* __restrict__ payload, float* __restrict__
       s += (double)rep[rp * kd + i];
       rep[rp * kd + i] = 0.f;
     }
+    if (colscale) s *= (double)colscale[i % d];
     payload[i] += s;
   }
   for (size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x; j < (size_t)k; j += (size_t)gridDim.x * blockDim.x) {
@@ -478,10 +539,10 @@ static int km_pick_algo(int algo, int k, int d, int64_t ld, const float* w) {
 
 extern "C" int b2f_kmeans_step(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep, int k,
                                void* acc, int32_t* labels, int algo, b2f_stream_t stream) {
-  B2F_REQUIRE(X && prep && acc, "b2f_kmeans_step: null pointer");
   B2F_REQUIRE(n >= 0 && d > 0 && k > 0 && ld >= d && ld % 4 == 0, "b2f_kmeans_step: need ld >= d, ld %% 4 == 0");
+  if (n == 0) return B2F_OK;  // an empty row shard: nothing to add (X may be NULL)
+  B2F_REQUIRE(X && prep && acc, "b2f_kmeans_step: null pointer");
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_kmeans_step: X must be 16-byte aligned");
-  if (n == 0) return B2F_OK;
   KmPrepLayout P = km_prep_layout(k, d);
   KmAccLayout A = km_acc_layout(k, d);
   const char* pp = static_cast<const char*>(prep);
@@ -502,22 +563,46 @@ extern "C" size_t b2f_kmeans_ws_bytes(int64_t n, int k, int d) {
   return (n >= 0 && k > 0 && d > 0) ? km_tcb_ws_bytes(n, k, d) : 0;
 }
 
+// shared by b2f_kmeans_step_ws / b2f_kmeans_step_scaled
+static int km_step_ws_impl(const char* who, const float* X, int64_t n, int d, int64_t ld, const float* colscale,
+                           const float* w, const void* prep, int k, void* acc, int32_t* labels, void* ws,
+                           size_t ws_bytes, int algo, b2f_stream_t stream) {
+  B2F_REQUIRE(n >= 0 && d > 0 && k > 0 && ld >= d && ld % 4 == 0, "%s: need ld >= d, ld %% 4 == 0", who);
+  if (n == 0) return B2F_OK;
+  B2F_REQUIRE(X && prep && acc, "%s: null pointer", who);
+  const bool have_ws = labels && ws;
+  if (algo == B2F_KM_AUTO && !w && have_ws && km_tcb_supported(k, d, ld)) algo = B2F_KM_TCH;
+  // 3xTF32 WITH its certainty test and the fp64 tail (the fallback of the filter pipeline) needs the workspace too
+  const bool tc3_checked = algo == B2F_KM_TC3 && !w && have_ws && km_tc_supported(k, d, ld);
+  if (algo != B2F_KM_TCB && algo != B2F_KM_TCH && !tc3_checked) {
+    B2F_REQUIRE(!colscale, "%s: a column scale needs the filter pipeline (d in {64, 128}, k %% 128 == 0, labels, ws)", who);
+    return b2f_kmeans_step(X, n, d, ld, w, prep, k, acc, labels, algo, stream);
+  }
+  B2F_REQUIRE(!w, "%s: the tensor-core path does not take row weights", who);
+  B2F_REQUIRE(have_ws, "%s: the filter pipeline needs labels and a workspace", who);
+  B2F_REQUIRE(tc3_checked || km_tcb_supported(k, d, ld), "%s: B2F_KM_TCB / B2F_KM_TCH need d in {64, 128} and k %% 128 == 0",
+              who);
+  B2F_REQUIRE(!colscale || algo == B2F_KM_TCH, "%s: a column scale is only taken by B2F_KM_TCH / B2F_KM_AUTO", who);
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "%s: X must be 16-byte aligned", who);
+  const int filter = tc3_checked ? KM_FILTER_NONE : algo == B2F_KM_TCH ? KM_FILTER_FP16 : KM_FILTER_BF16X3;
+  return km_tcb_step(X, n, d, ld, colscale, prep, k, acc, labels, ws, ws_bytes, true, filter, b2f_cs(stream));
+}
+
 extern "C" int b2f_kmeans_step_ws(const float* X, int64_t n, int d, int64_t ld, const float* w, const void* prep,
                                   int k, void* acc, int32_t* labels, void* ws, size_t ws_bytes, int algo,
                                   b2f_stream_t stream) {
-  B2F_REQUIRE(X && prep && acc, "b2f_kmeans_step_ws: null pointer");
-  B2F_REQUIRE(n >= 0 && d > 0 && k > 0 && ld >= d && ld % 4 == 0, "b2f_kmeans_step_ws: need ld >= d, ld %% 4 == 0");
-  if (algo == B2F_KM_AUTO && !w && labels && ws && km_tcb_supported(k, d, ld)) algo = B2F_KM_TCH;
-  if (algo != B2F_KM_TCB && algo != B2F_KM_TCH)
-    return b2f_kmeans_step(X, n, d, ld, w, prep, k, acc, labels, algo, stream);
-  B2F_REQUIRE(!w, "b2f_kmeans_step_ws: the tensor-core path does not take row weights");
-  B2F_REQUIRE(km_tcb_supported(k, d, ld),
-              "b2f_kmeans_step_ws: B2F_KM_TCB / B2F_KM_TCH need d in {64, 128} and k %% 128 == 0");
-  B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_kmeans_step_ws: X must be 16-byte aligned");
-  if (n == 0) return B2F_OK;
-  return km_tcb_step(X, n, d, ld, prep, k, acc, labels, ws, ws_bytes, true,
-                     algo == B2F_KM_TCH ? KM_FILTER_FP16 : KM_FILTER_BF16X3, b2f_cs(stream));
+  return km_step_ws_impl("b2f_kmeans_step_ws", X, n, d, ld, nullptr, w, prep, k, acc, labels, ws, ws_bytes, algo, stream);
 }
+
+extern "C" int b2f_kmeans_step_scaled(const float* X, int64_t n, int d, int64_t ld, const float* col_scale,
+                                      const void* prep, int k, void* acc, int32_t* labels, void* ws, size_t ws_bytes,
+                                      b2f_stream_t stream) {
+  B2F_REQUIRE(col_scale, "b2f_kmeans_step_scaled: null column scale");
+  return km_step_ws_impl("b2f_kmeans_step_scaled", X, n, d, ld, col_scale, nullptr, prep, k, acc, labels, ws, ws_bytes,
+                         B2F_KM_TCH, stream);
+}
+
+extern "C" int b2f_kmeans_scaled_supported(int k, int d, int64_t ld) { return km_tcb_supported(k, d, ld) ? 1 : 0; }
 
 extern "C" int b2f_kmeans_fold(void* acc, int k, int d, b2f_stream_t stream) {
   B2F_REQUIRE(acc && k > 0 && d > 0, "b2f_kmeans_fold: bad arguments");
@@ -528,7 +613,22 @@ extern "C" int b2f_kmeans_fold(void* acc, int k, int d, b2f_stream_t stream) {
   if (grid > b2f_sm_count() * 8) grid = b2f_sm_count() * 8;
   km_fold_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(reinterpret_cast<double*>(ap + A.off_payload),
                                                    reinterpret_cast<float*>(ap + A.off_rep),
-                                                   reinterpret_cast<unsigned long long*>(ap + A.off_cnt), k, d);
+                                                   reinterpret_cast<unsigned long long*>(ap + A.off_cnt), k, d,
+                                                   nullptr);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+// used by the scaled filter pass (kmeans_tcb.cu): replicas hold RAW row sums, the payload scaled ones
+int km_fold_scaled(void* acc, int k, int d, const float* colscale, cudaStream_t stream) {
+  KmAccLayout A = km_acc_layout(k, d);
+  char* ap = static_cast<char*>(acc);
+  size_t kd = (size_t)k * d;
+  int grid = (int)((kd + 255) / 256);
+  if (grid > b2f_sm_count() * 8) grid = b2f_sm_count() * 8;
+  km_fold_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<double*>(ap + A.off_payload),
+                                           reinterpret_cast<float*>(ap + A.off_rep),
+                                           reinterpret_cast<unsigned long long*>(ap + A.off_cnt), k, d, colscale);
   B2F_LAUNCH_CHECK();
   return B2F_OK;
 }
@@ -545,16 +645,46 @@ extern "C" int b2f_kmeans_finalize(const double* payload, int k, int d, double t
 
 extern "C" int b2f_kmeans_predict(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k,
                                   int32_t* labels, float* dist2, int algo, b2f_stream_t stream) {
-  B2F_REQUIRE(X && prep && (labels || dist2), "b2f_kmeans_predict: null pointer");
+  return b2f_kmeans_predict_ws(X, n, d, ld, nullptr, prep, k, labels, dist2, nullptr, 0, algo, stream);
+}
+
+extern "C" int b2f_kmeans_predict_ws(const float* X, int64_t n, int d, int64_t ld, const float* col_scale,
+                                     const void* prep, int k, int32_t* labels, float* dist2, void* ws, size_t ws_bytes,
+                                     int algo, b2f_stream_t stream) {
   B2F_REQUIRE(n >= 0 && d > 0 && k > 0 && ld >= d && ld % 4 == 0, "b2f_kmeans_predict: need ld >= d, ld %% 4 == 0");
   if (n == 0) return B2F_OK;
+  B2F_REQUIRE(X && prep && (labels || dist2), "b2f_kmeans_predict: null pointer");
   KmPrepLayout P = km_prep_layout(k, d);
   const char* pp = static_cast<const char*>(prep);
+  const bool have_ws = labels && ws;
+  // the certainty pipeline (labels equal to fp64 except fp64-level ties) whenever the shape allows it
+  int filter = -1;
+  if ((algo == B2F_KM_AUTO || algo == B2F_KM_TCH) && have_ws && km_tcb_supported(k, d, ld)) filter = KM_FILTER_FP16;
+  else if (algo == B2F_KM_TCB && have_ws && km_tcb_supported(k, d, ld)) filter = KM_FILTER_BF16X3;
+  else if ((algo == B2F_KM_AUTO || algo == B2F_KM_TC3) && have_ws && km_tc_supported(k, d, ld)) filter = KM_FILTER_NONE;
+  if (filter >= 0 && (!col_scale || filter == KM_FILTER_FP16)) {
+    B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_kmeans_predict: X must be 16-byte aligned");
+    int rc = km_tcb_step(X, n, d, ld, col_scale, prep, k, nullptr, labels, ws, ws_bytes, false, filter, b2f_cs(stream));
+    if (rc != B2F_OK) return rc;
+    if (dist2) return km_dist_to_label(X, n, d, ld, col_scale, prep, k, labels, dist2, b2f_cs(stream));
+    return B2F_OK;
+  }
+  B2F_REQUIRE(!col_scale, "b2f_kmeans_predict_ws: a column scale needs the filter pipeline (d in {64, 128}, "
+                          "k %% 128 == 0, labels, ws)");
+  B2F_REQUIRE(algo != B2F_KM_TCB && algo != B2F_KM_TCH, "b2f_kmeans_predict_ws: B2F_KM_TCB / B2F_KM_TCH need labels, a "
+                                                         "workspace, d in {64, 128} and k %% 128 == 0");
   algo = km_pick_algo(algo, k, d, ld, nullptr);
-  if (dist2) algo = B2F_KM_GENERIC;  // exact distances come from the direct-form kernel
   if (algo == B2F_KM_TC3 || algo == B2F_KM_TC1) {
-    B2F_REQUIRE(km_tc_supported(k, d, ld), "b2f_kmeans_predict: tensor-core path needs d %% 32 == 0, d <= 256, k %% 128 == 0");
-    return km_tc_step(X, n, d, ld, prep, k, nullptr, labels, algo == B2F_KM_TC3 ? 3 : 1, false, nullptr, nullptr, b2f_cs(stream));
+    // no workspace: the 3xTF32 (or 1xTF32) scores decide alone -- NOT certified; callers that need the fp64
+    // guarantee pass a workspace.  Distances then come from the labels.
+    B2F_REQUIRE(km_tc_supported(k, d, ld), "b2f_kmeans_predict: tensor-core path needs d %% 32 == 0, d <= 128, k %% 128 == 0");
+    if (labels) {
+      int rc = km_tc_step(X, n, d, ld, prep, k, nullptr, labels, algo == B2F_KM_TC3 ? 3 : 1, false, nullptr, nullptr,
+                          b2f_cs(stream));
+      if (rc != B2F_OK) return rc;
+      if (dist2) return km_dist_to_label(X, n, d, ld, nullptr, prep, k, labels, dist2, b2f_cs(stream));
+      return B2F_OK;
+    }
   }
   return km_generic_launch(X, n, d, ld, nullptr, reinterpret_cast<const float*>(pp + P.off_c32), k, nullptr, nullptr,
                            labels, dist2, false, b2f_cs(stream));

@@ -426,17 +426,22 @@ int km_tc_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, i
                       (size_t)nstages * (passes == 3 ? 2 : 1) * CHUNK_BYTES + sizeof(Smem) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
-  if (const char* g = getenv("B2F_TC_GRID")) grid = atoi(g) > 0 ? atoi(g) : grid;  // dev knob
+#ifdef B2F_DEV  // dev knobs of the timing experiments; not in the product build
+  if (const char* g = getenv("B2F_TC_GRID")) grid = atoi(g) > 0 ? atoi(g) : grid;
+#endif
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
   KmRecheck rck = {};
   if (recheck) rck = *recheck;
-  const int dbg = getenv("B2F_TC_DBG") ? atoi(getenv("B2F_TC_DBG")) : 0;  // dev knob, results invalid when set
+  int dbg = 0;
+#ifdef B2F_DEV
+  dbg = getenv("B2F_TC_DBG") ? atoi(getenv("B2F_TC_DBG")) : 0;  // results invalid when set
+#endif
   if (passes == 3) {
-    B2F_CUDA(cudaFuncSetAttribute(km_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2F_CUDA(b2f_smem_attr(km_tc_kernel<3>, smem));
     km_tc_kernel<3><<<grid, NTHREADS, smem, stream>>>(mx, mh, ml, X, n, d, ld, cn, k, nstages, payload, rep, cnt,
                                                       labels, accumulate ? 1 : 0, dbg, n_dev, rck);
   } else {
-    B2F_CUDA(cudaFuncSetAttribute(km_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B2F_CUDA(b2f_smem_attr(km_tc_kernel<1>, smem));
     km_tc_kernel<1><<<grid, NTHREADS, smem, stream>>>(mx, mh, ml, X, n, d, ld, cn, k, nstages, payload, rep, cnt,
                                                       labels, accumulate ? 1 : 0, dbg, n_dev, rck);
   }

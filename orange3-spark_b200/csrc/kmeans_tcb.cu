@@ -10,7 +10,9 @@
 // A row whose best and second-best scores are more than 2 tau apart has a CERTAIN label and is accumulated here;
 // every other row goes to a list, is gathered into a compact matrix and re-assigned by the 3xTF32 kernel (which has
 // its own certainty test) and, failing that, by the fp64 kernel.  Labels, sums and counts therefore equal the exact
-// path's.  Cost: bf16x3 adds its (zero-mean) score error per certain row; the fp16 variant adds sum ||x||^2 only and
+// path's.  (fp16 filter: an uncertain row whose THIRD best score is clear of the best by more than 2 tau can only
+// belong to its best or second-best centre; such rows go to a pair list and are decided by two fp64 distances
+// (km_pair_exact_kernel) instead of a pass over all k centres.)  Cost: bf16x3 adds its (zero-mean) score error per certain row; the fp16 variant adds sum ||x||^2 only and
 // the centre-dependent remainder sum_j (n_j ||c_j||^2 - 2 c_j . S_j) exactly from the sums (tcb_cost_terms_kernel).
 //
 // Replaces MLlib's findClosest + axpy loop behind KMeans.fit;
@@ -123,13 +125,18 @@ struct SmemB {
   float xnorm2[4][TM];
   float p_b1[2][2][TM], p_b2[2][2][TM];  // [slot][epilogue warp of the lane quarter][row]: best, second best
   int p_i1[2][2][TM];                    // index of the best
+  int p_b3[2][2][TM];                    // fp16 filter: lower bound of the third best key; index of the second best
+  int p_i2[2][2][TM];
+  float cscale[TM];                      // scaled pass: per-column factor (StandardScaler fold), d <= 128 entries
 };
 
-struct TcbWs {  // header of the caller-provided workspace
+struct TcbWs {  // header of the caller-provided workspace (the first four ints are documented in b200fit.h)
   int count;    // rows appended to the re-check list (may exceed cap: the excess is dropped)
   int used;     // min(count, cap), written by the gather kernel
-  int count2;   // rows the 3xTF32 re-check could not certify either -> exact fp64 kernel
-  int pad[61];
+  int count2;   // rows the 3xTF32 re-check could not certify either -> exact fp64 kernel (same: excess dropped)
+  int cap;      // capacity of each of the two lists above
+  int pcount;   // rows appended to the pair list (those beyond its capacity are sent to the re-check list instead)
+  int pad[59];
 };
 
 __device__ __forceinline__ void tc_mma_f16_ss(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
@@ -153,14 +160,15 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, 
 
 }  // namespace
 
-template <int MODE, bool TRACE>
+template <int MODE, bool TRACE, bool SCALED>
 __global__ void __launch_bounds__(TB_THREADS, 1)
     km_tcb_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c1,
                   const __grid_constant__ CUtensorMap map_c2, const float* __restrict__ X, int64_t n, int d,
-                  int64_t ld, const float* __restrict__ cn, const float* __restrict__ misc, float kappa2,
-                  float kappa0, int k, int nstages, double* __restrict__ payload, float* __restrict__ rep,
-                  unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels, int accumulate,
-                  TcbWs* __restrict__ ws, int32_t* __restrict__ amb_idx, int cap,
+                  int64_t ld, const float* __restrict__ colscale, const float* __restrict__ cn,
+                  const float* __restrict__ misc, float kappa2, float kappa0, int k, int nstages,
+                  double* __restrict__ payload, float* __restrict__ rep, unsigned long long* __restrict__ cnt,
+                  int32_t* __restrict__ labels, int accumulate, TcbWs* __restrict__ ws,
+                  int32_t* __restrict__ amb_idx, int cap, int4* __restrict__ pairs, int pcap,
                   unsigned long long* __restrict__ trace) {
   constexpr int TB_STAGE_BYTES = tb_stage_bytes<MODE>();  // per 64-k atom
   constexpr bool H16 = MODE == KM_FILTER_FP16;
@@ -220,6 +228,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> tensor-core reads
   }
+  if (SCALED && threadIdx.x < TM) sm->cscale[threadIdx.x] = (int)threadIdx.x < d ? colscale[threadIdx.x] : 0.f;
   if (warp == W_ALLOC) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm->tmem_base)),
                  "r"(TB_TMEM_COLS)
@@ -375,8 +384,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       float b1a = INFINITY, b2a = INFINITY, b1b = INFINITY, b2b = INFINITY;
       int i1a = 0, i1b = 1;
       // integer-key path (fp16 filter): running best / second best keys and the centre tile of the best
-      int B1 = 0x7fffffff, B2 = 0x7fffffff;
-      int T1 = 0;
+      int B1 = 0x7fffffff, B2 = 0x7fffffff, B3 = 0x7fffffff;  // B3: lower bound of the third best key
+      int T1 = 0, T2 = 0;                                     // centre tiles of the best and the second best
       float arow = 1.f;
       if (H16) {
         // the split warps finished this row tile before its first MMA could start: the norms are there
@@ -438,9 +447,18 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         }
         tc_fence_before();
         mbar_arrive(&sm->t_empty[cbuf]);
-        if (H16) {  // fold the tile's two chains into the running pair; an earlier tile keeps equal keys
+        if (H16) {  // fold the tile's two chains into the running triple; an earlier tile keeps equal keys
           const int k1 = min(k1a, k1b), k2 = min(max(k1a, k1b), min(k2a, k2b));
-          B2 = min(max(B1, k1), min(B2, k2));
+          // The tile's third smallest key is >= l3: if its two smallest sit in different chains it IS min(k2a, k2b);
+          // if one chain holds both, that chain's third is unknown and min(k2a, k2b) = k2 is all that can be said.
+          const int l3 = min(k2a, k2b);
+          // third smallest of the two sorted triples (B1, B2, B3) and (k1, k2, l3)
+          B3 = min(min(B3, l3), min(max(B2, k1), max(B1, k2)));
+          const int lose = max(B1, k1);             // the larger of the two firsts ...
+          const int tl = (k1 < B1) ? T1 : nt;       // ... and the tile it came from
+          const int nB2 = min(lose, min(B2, k2));
+          T2 = (nB2 == B2) ? T2 : ((nB2 == lose) ? tl : nt);
+          B2 = nB2;
           T1 = (k1 < B1) ? nt : T1;
           B1 = min(B1, k1);
         }
@@ -454,6 +472,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         sm->p_b1[ab][half][row_in_tile] = __int_as_float(B1);
         sm->p_b2[ab][half][row_in_tile] = __int_as_float(B2);
         sm->p_i1[ab][half][row_in_tile] = T1 * TN + tb_key_col(B1);
+        sm->p_b3[ab][half][row_in_tile] = B3;
+        sm->p_i2[ab][half][row_in_tile] = T2 * TN + tb_key_col(B2);
       } else {
         sm->p_b1[ab][half][row_in_tile] = a_wins ? b1a : b1b;
         sm->p_i1[ab][half][row_in_tile] = a_wins ? i1a : i1b;
@@ -483,7 +503,11 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           const uint8_t* src = xs + (size_t)kc * CHUNK_BYTES + (size_t)r * 128;
 #pragma unroll
           for (int p = 0; p < 8; ++p) {
-            const float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
+            float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
+            if (SCALED) {  // the row a materialised StandardScaler copy would hold: fl32(x * scale)
+              const float4 sc = *reinterpret_cast<const float4*>(&sm->cscale[kc * 32 + p * 4]);
+              v.x = __fmul_rn(v.x, sc.x); v.y = __fmul_rn(v.y, sc.y); v.z = __fmul_rn(v.z, sc.z); v.w = __fmul_rn(v.w, sc.w);
+            }
             xn = fmaf(v.x, v.x, xn); xn = fmaf(v.y, v.y, xn); xn = fmaf(v.z, v.z, xn); xn = fmaf(v.w, v.w, xn);
             if (H16) {
               amax = fmaxf(fmaxf(amax, fabsf(v.x)), fmaxf(fabsf(v.y), fmaxf(fabsf(v.z), fabsf(v.w))));
@@ -542,18 +566,31 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       if (w4 == 0) TR(10, 1);
       float b1 = sm->p_b1[ab][0][row_in_tile], b2 = sm->p_b2[ab][0][row_in_tile];
       int i1 = sm->p_i1[ab][0][row_in_tile];
-      float gap_units = 0.f;  // fp16 filter: second best - best in key units
+      float gap_units = 0.f;   // fp16 filter: second best - best in key units
+      float gap3_units = 0.f;  // (lower bound of the) third best - best
+      int i2 = -1;             // index of the second best
       {
         const float ob1 = sm->p_b1[ab][1][row_in_tile], ob2 = sm->p_b2[ab][1][row_in_tile];
         const int oi1 = sm->p_i1[ab][1][row_in_tile];
+        int B3 = 0x7fffffff, O3 = 0x7fffffff, mi2 = -1, oi2 = -1;
+        if (H16) {
+          B3 = sm->p_b3[ab][0][row_in_tile];
+          O3 = sm->p_b3[ab][1][row_in_tile];
+          mi2 = sm->p_i2[ab][0][row_in_tile];
+          oi2 = sm->p_i2[ab][1][row_in_tile];
+        }
         mbar_arrive(&sm->a_empty[ab]);
         if (H16) {
           const int B1 = __float_as_int(b1), B2 = __float_as_int(b2);
           const int O1 = __float_as_int(ob1), O2 = __float_as_int(ob2);
           const bool mine = (B1 < O1) || (B1 == O1 && i1 < oi1);
-          const int S2 = min(max(B1, O1), min(B2, O2)), S1 = min(B1, O1);
+          const int lose = max(B1, O1);
+          const int S2 = min(lose, min(B2, O2)), S1 = min(B1, O1);
+          const int S3 = min(min(B3, O3), min(max(B2, O1), max(B1, O2)));
           // (a warp without a centre tile hands over INT_MAX keys: at least one warp has real ones)
           gap_units = (S2 == 0x7fffffff) ? 0.f : (float)(tb_key_value(S2) - tb_key_value(S1));
+          gap3_units = (S3 == 0x7fffffff) ? 0.f : (float)(tb_key_value(S3) - tb_key_value(S1));
+          i2 = (S2 == lose) ? (mine ? oi1 : i1) : ((S2 == B2) ? mi2 : oi2);
           i1 = mine ? i1 : oi1;
         } else {
           const bool mine = (b1 < ob1) || (b1 == ob1 && i1 < oi1);
@@ -574,19 +611,40 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       const int64_t row = tile * TM + row_in_tile;
       const bool live = row < n;
       bool certain = (b2 - b1) > tau2;  // false for NaN as well
+      bool pair_ok = false;  // uncertain, but every centre other than the best two is out of reach
       if (H16) {
         const float sc = tb_row_scale(xn, cmax);
         const float arow = misc[KM_MISC_INV_SCALE2] * sc;
-        certain = gap_units > fmaf(tau2, sc, 2.5f) && arow > 0.f && arow < INFINITY;
+        const float thr = fmaf(tau2, sc, 2.5f);
+        const bool usable = arow > 0.f && arow < INFINITY;
+        certain = gap_units > thr && usable;
+        pair_ok = !certain && usable && pairs != nullptr && gap3_units > thr && i2 >= 0 && i2 < k && i2 != i1;
       }
       if (live) labels[row] = i1;             // provisional for uncertain rows (rewritten by the re-check)
-      // append uncertain rows to the re-check list (one atomic per warp)
-      const unsigned m = __ballot_sync(0xffffffffu, live && !certain);
+      // uncertain rows with exactly two candidates: pair list (row, best, second best), decided by two fp64
+      // distances; a full pair list sends the row to the re-check list instead
+      bool to_list = live && !certain && !pair_ok;
+      if (H16) {
+        const bool to_pair = live && pair_ok;
+        const unsigned pm = __ballot_sync(0xffffffffu, to_pair);
+        if (pm) {
+          int base = 0;
+          if (lane == (__ffs(pm) - 1)) base = atomicAdd(&ws->pcount, __popc(pm));
+          base = __shfl_sync(0xffffffffu, base, __ffs(pm) - 1);
+          if (to_pair) {
+            const int slot = base + __popc(pm & ((1u << lane) - 1));
+            if (slot < pcap) pairs[slot] = make_int4((int)(row & 0x7fffffff), i1, i2, 0);
+            else to_list = true;
+          }
+        }
+      }
+      // append the other uncertain rows to the re-check list (one atomic per warp)
+      const unsigned m = __ballot_sync(0xffffffffu, to_list);
       if (m) {
         int base = 0;
         if (lane == (__ffs(m) - 1)) base = atomicAdd(&ws->count, __popc(m));
         base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-        if (live && !certain) {
+        if (to_list) {
           const int slot = base + __popc(m & ((1u << lane) - 1));
           if (slot < cap) amb_idx[slot] = (int32_t)(row & 0x7fffffff);
         }
@@ -694,16 +752,27 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
 // ---------------------------------------------------------------------------------------------
 // re-check plumbing: gather listed rows into a compact matrix, scatter their labels back
 // ---------------------------------------------------------------------------------------------
-__global__ void tcb_gather_kernel(const float* __restrict__ X, int64_t ld, int d, TcbWs* __restrict__ ws,
-                                  const int32_t* __restrict__ amb_idx, float* __restrict__ Xamb, int cap) {
+__global__ void tcb_gather_kernel(const float* __restrict__ X, int64_t ld, int d, const float* __restrict__ colscale,
+                                  TcbWs* __restrict__ ws, const int32_t* __restrict__ amb_idx,
+                                  float* __restrict__ Xamb, int cap) {
   const int used = min(ws->count, cap);
-  if (blockIdx.x == 0 && threadIdx.x == 0) ws->used = used;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    ws->used = used;
+    ws->cap = cap;
+  }
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
   for (int i = warp; i < used; i += nwarps) {
     const float* src = X + (int64_t)amb_idx[i] * ld;
     float* dst = Xamb + (int64_t)i * d;
-    for (int c = lane * 4; c < d; c += 128) *reinterpret_cast<float4*>(dst + c) = *reinterpret_cast<const float4*>(src + c);
+    for (int c = lane * 4; c < d; c += 128) {
+      float4 v = *reinterpret_cast<const float4*>(src + c);
+      if (colscale) {  // scaled pass: the compact matrix holds fl32(x * scale)
+        const float4 sc = *reinterpret_cast<const float4*>(colscale + c);
+        v.x = __fmul_rn(v.x, sc.x); v.y = __fmul_rn(v.y, sc.y); v.z = __fmul_rn(v.z, sc.z); v.w = __fmul_rn(v.w, sc.w);
+      }
+      *reinterpret_cast<float4*>(dst + c) = v;
+    }
   }
 }
 
@@ -712,6 +781,80 @@ __global__ void tcb_scatter_kernel(const TcbWs* __restrict__ ws, const int32_t* 
   const int used = ws->used;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < used; i += gridDim.x * blockDim.x)
     labels[amb_idx[i]] = lab_amb[i];
+}
+
+__global__ void tcb_set_cap_kernel(TcbWs* __restrict__ ws, int cap) { ws->cap = cap; }
+
+// ---------------------------------------------------------------------------------------------
+// Pair check: rows of the fp16 filter whose label is uncertain but can only be their best or second-best centre.
+// fp64 on the fp64 master centres, the same form as km_exact_kernel (||x||^2 + ||c||^2 - 2 x.c, clamped at 0), equal
+// distances go to the lower index (findClosest order).  Warp per row, lane = 4 columns (d <= 128); the centre table
+// (k * d * 8 bytes) stays in L2.  Accumulates like the tensor-core kernels: 16-byte vector reductions into the fp32
+// replicas, integer counts, fp64 cost.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) km_pair_exact_kernel(const float* __restrict__ X, int64_t ld, int d,
+                                                            const float* __restrict__ colscale,
+                                                            const double* __restrict__ C64,
+                                                            const double* __restrict__ CN64, int k,
+                                                            double* __restrict__ payload, float* __restrict__ rep,
+                                                            unsigned long long* __restrict__ cnt,
+                                                            int32_t* __restrict__ labels,
+                                                            const TcbWs* __restrict__ ws,
+                                                            const int4* __restrict__ pairs, int pcap, int accumulate) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int used = min(ws->pcount, pcap);
+  const int c = lane * 4;
+  const bool on = c < d;
+  float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
+  double cost = 0.0;
+  unsigned long long rows = 0;
+  for (int e = warp; e < used; e += nwarps) {
+    const int4 pr = pairs[e];
+    const int64_t row = pr.x;
+    const int i1 = pr.y, i2 = pr.z;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    double a1[4] = {0, 0, 0, 0}, a2[4] = {0, 0, 0, 0};
+    if (on) {
+      x = *reinterpret_cast<const float4*>(X + row * ld + c);
+      if (colscale) {
+        const float4 sc = *reinterpret_cast<const float4*>(colscale + c);
+        x.x = __fmul_rn(x.x, sc.x); x.y = __fmul_rn(x.y, sc.y); x.z = __fmul_rn(x.z, sc.z); x.w = __fmul_rn(x.w, sc.w);
+      }
+      const double2* p1 = reinterpret_cast<const double2*>(C64 + (size_t)i1 * d + c);
+      const double2* p2 = reinterpret_cast<const double2*>(C64 + (size_t)i2 * d + c);
+      const double2 u0 = p1[0], u1 = p1[1], v0 = p2[0], v1 = p2[1];
+      a1[0] = u0.x; a1[1] = u0.y; a1[2] = u1.x; a1[3] = u1.y;
+      a2[0] = v0.x; a2[1] = v0.y; a2[2] = v1.x; a2[3] = v1.y;
+    }
+    const double xd[4] = {(double)x.x, (double)x.y, (double)x.z, (double)x.w};
+    double xn = 0.0, s1 = 0.0, s2 = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      xn = fma(xd[j], xd[j], xn);
+      s1 = fma(xd[j], a1[j], s1);
+      s2 = fma(xd[j], a2[j], s2);
+    }
+    xn = warp_sum(xn);
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    const double v1 = fmax(xn + CN64[i1] - 2.0 * s1, 0.0), v2 = fmax(xn + CN64[i2] - 2.0 * s2, 0.0);
+    const bool second = (v2 < v1) || (v2 == v1 && i2 < i1);
+    const int pick = second ? i2 : i1;
+    if (lane == 0) labels[row] = pick;
+    if (accumulate) {
+      if (on) red_add_v4(myrep + (size_t)pick * d + c, x);
+      if (lane == 0) {
+        atomicAdd(cnt + pick, 1ull);
+        cost += second ? v2 : v1;
+        ++rows;
+      }
+    }
+  }
+  if (accumulate && lane == 0 && rows) {
+    atomicAdd(payload + (size_t)k * d + k, cost);
+    atomicAdd(payload + (size_t)k * d + k + 1, (double)rows);
+  }
 }
 
 // Centre-dependent part of the cost of everything accumulated so far:
@@ -746,8 +889,10 @@ __global__ void tcb_cost_terms_kernel(double* __restrict__ payload, const float*
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+int km_fold_scaled(void* acc, int k, int d, const float* colscale, cudaStream_t stream);  // kmeans_generic.cu
+
 struct TcbWsLayout {
-  size_t off_idx, off_lab, off_idx2, off_x, bytes;
+  size_t off_idx, off_lab, off_idx2, off_pairs, off_x, bytes;
   int cap;
 };
 static TcbWsLayout tcb_ws_layout(int cap, int d) {
@@ -757,6 +902,7 @@ static TcbWsLayout tcb_ws_layout(int cap, int d) {
   L.off_idx = o; o = b2f_align_up(o + (size_t)cap * 4, 1024);
   L.off_lab = o; o = b2f_align_up(o + (size_t)cap * 4, 1024);
   L.off_idx2 = o; o = b2f_align_up(o + (size_t)cap * 4, 1024);
+  L.off_pairs = o; o = b2f_align_up(o + (size_t)cap * 16, 1024);
   L.off_x = o;   o = b2f_align_up(o + (size_t)cap * d * 4, 1024);
   L.bytes = o;
   return L;
@@ -768,8 +914,8 @@ static int tcb_cap_for_rows(int64_t n) {
   return (int)c;
 }
 static int tcb_cap_from_bytes(size_t bytes, int d) {
-  if (bytes < sizeof(TcbWs) + 4096) return 0;
-  int64_t c = (int64_t)((bytes - sizeof(TcbWs) - 4 * 1024) / (12 + (size_t)d * 4));
+  if (bytes < sizeof(TcbWs) + 5 * 1024) return 0;
+  int64_t c = (int64_t)((bytes - sizeof(TcbWs) - 5 * 1024) / (28 + (size_t)d * 4));
   c = c / TM * TM;
   if (c > (1 << 30)) c = 1 << 30;
   while (c > 0 && tcb_ws_layout((int)c, d).bytes > bytes) c -= TM;
@@ -777,13 +923,15 @@ static int tcb_cap_from_bytes(size_t bytes, int d) {
 }
 
 static int km_tcb_stages(int d, int filter) {
-  const int budget = (filter != KM_FILTER_FP16 ? 227 : getenv("B2F_TC_SMEM_KB") ? atoi(getenv("B2F_TC_SMEM_KB"))  // dev knob
-                                                                                 : 227) * 1024;
-  const int left = budget - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES -
+  int budget_kb = 227, cap = 4;
+#ifdef B2F_DEV  // dev knobs of the timing experiments; not in the product build
+  if (filter == KM_FILTER_FP16 && getenv("B2F_TC_SMEM_KB")) budget_kb = atoi(getenv("B2F_TC_SMEM_KB"));
+  if (getenv("B2F_TC_STAGES")) cap = atoi(getenv("B2F_TC_STAGES"));
+#endif
+  const int left = budget_kb * 1024 - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES -
                    (filter == KM_FILTER_FP16 ? TB_CN_BYTES + 4 * 2 * TB_FX_ROWS * d * 4 : 0);
   // a stage holds one centre tile: two 64-k atoms (space for two even when d == 64), fp16: + the ||c||^2 block
   int s = left / (filter == KM_FILTER_FP16 ? 2 * CHUNK_BYTES + TB_CN_BYTES : 2 * tb_stage_bytes<KM_FILTER_BF16X3>());
-  const int cap = getenv("B2F_TC_STAGES") ? atoi(getenv("B2F_TC_STAGES")) : 4;  // dev knob
   return s > cap ? cap : s;
 }
 
@@ -791,7 +939,7 @@ bool km_tcb_supported(int k, int d, int64_t ld) {
   if (d != 64 && d != 128) return false;  // whole 64-k atoms, X hi/lo pairs fit the tensor memory budget
   if (k % TN != 0 || k < TN) return false;
   if (ld % 4 != 0) return false;
-  return km_tcb_stages(d, KM_FILTER_BF16X3) >= 2 && km_tc_supported(k, d, ld);
+  return km_tcb_stages(d, KM_FILTER_BF16X3) >= 2 && km_tcb_stages(d, KM_FILTER_FP16) >= 2 && km_tc_supported(k, d, ld);
 }
 
 size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
@@ -799,28 +947,95 @@ size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
   return tcb_ws_layout(tcb_cap_for_rows(n), d).bytes;
 }
 
-int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, void* acc, int32_t* labels,
-                void* ws, size_t ws_bytes, bool accumulate, int filter, cudaStream_t stream) {
+template <int MODE, bool SCALED>
+static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const CUtensorMap& mx, const CUtensorMap& m1,
+                             const CUtensorMap& m2, const float* X, int64_t n, int d, int64_t ld, const float* colscale,
+                             const float* cn, const float* misc, float kappa2, float kappa0, int k, int nstages,
+                             double* payload, float* rep, unsigned long long* cnt, int32_t* labels, int accumulate,
+                             TcbWs* hdr, int32_t* amb_idx, int cap, int4* pairs, int pcap) {
+  unsigned long long* trace = nullptr;
+#ifdef B2F_DEV  // hand-off tracer of the timing experiments (allocates; not in the product build)
+  const char* trace_path = getenv("B2F_TC_TRACE");
+  const size_t trace_bytes = (size_t)TR_ROLES * TR_TILES * TR_SLOTS * sizeof(unsigned long long);
+  if (trace_path) {
+    B2F_CUDA(cudaMalloc(&trace, trace_bytes));
+    B2F_CUDA(cudaMemsetAsync(trace, 0, trace_bytes, stream));
+    auto kern = km_tcb_kernel<MODE, true, SCALED>;
+    B2F_CUDA(b2f_smem_attr(kern, smem));
+    kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
+                                             payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, trace);
+    B2F_LAUNCH_CHECK();
+    std::vector<unsigned long long> host(trace_bytes / sizeof(unsigned long long));
+    B2F_CUDA(cudaStreamSynchronize(stream));
+    B2F_CUDA(cudaMemcpy(host.data(), trace, trace_bytes, cudaMemcpyDeviceToHost));
+    B2F_CUDA(cudaFree(trace));
+    if (FILE* f = fopen(trace_path, "wb")) {
+      fwrite(host.data(), 1, trace_bytes, f);
+      fclose(f);
+    }
+    return B2F_OK;
+  }
+#endif
+  auto kern = km_tcb_kernel<MODE, false, SCALED>;
+  B2F_CUDA(b2f_smem_attr(kern, smem));
+  kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
+                                           payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, trace);
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colscale, const void* prep, int k, void* acc,
+                int32_t* labels, void* ws, size_t ws_bytes, bool accumulate, int filter, cudaStream_t stream) {
   B2F_REQUIRE(labels, "b2f_kmeans (filter path): a labels buffer is required");
   B2F_REQUIRE(ws, "b2f_kmeans (filter path): a workspace is required (b2f_kmeans_ws_bytes)");
   B2F_REQUIRE(n < (1ll << 31), "b2f_kmeans (filter path): at most 2^31-1 rows per call");
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "b2f_kmeans (filter path): workspace must be 256-byte aligned");
-  const int cap = tcb_cap_from_bytes(ws_bytes, d);
-  B2F_REQUIRE(cap >= TM, "b2f_kmeans (filter path): workspace of %zu bytes is too small", ws_bytes);
-  TcbWsLayout W = tcb_ws_layout(cap, d);
+  B2F_REQUIRE(!colscale || filter == KM_FILTER_FP16, "b2f_kmeans (filter path): a column scale needs the fp16 filter");
+  B2F_REQUIRE(!colscale || (reinterpret_cast<uintptr_t>(colscale) & 15) == 0,
+              "b2f_kmeans (filter path): the column scale must be 16-byte aligned");
   char* wp = static_cast<char*>(ws);
   TcbWs* hdr = reinterpret_cast<TcbWs*>(wp);
-  int32_t* amb_idx = reinterpret_cast<int32_t*>(wp + W.off_idx);
-  int32_t* lab_amb = reinterpret_cast<int32_t*>(wp + W.off_lab);
-  int32_t* idx2 = reinterpret_cast<int32_t*>(wp + W.off_idx2);
-  float* Xamb = reinterpret_cast<float*>(wp + W.off_x);
-  const bool h16 = filter == KM_FILTER_FP16;
-  const int nstages = km_tcb_stages(d, filter);
   KmPrepLayout P = km_prep_layout(k, d);
   const char* pp = static_cast<const char*>(prep);
   const float* cn = reinterpret_cast<const float*>(pp + P.off_cn);
   const float* misc = reinterpret_cast<const float*>(pp + P.off_misc);
   const float* cmax = misc + KM_MISC_CMAX;
+  // 3xTF32 bound: dropped products 3 u^2 with u = 2^-11 on c' = -2c, plus 48 fp32 accumulation roundings
+  const float kappa2_tc3 = 2.0f * (6.0f * 1.02f / 4194304.0f + 2.0f * (3.0f * d / 8.0f + 16.0f) / 16777216.0f);
+  B2F_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcbWs), stream));
+
+  if (filter == KM_FILTER_NONE) {
+    // No filter pass: 3xTF32 over every row, rows inside its own (narrow) uncertainty band to the fp64 kernel.
+    // The whole workspace behind the header is the list: room for every row when the workspace has its standard size.
+    B2F_REQUIRE(ws_bytes >= sizeof(TcbWs) + 4096, "b2f_kmeans (3xTF32 + re-check): workspace of %zu bytes is too small",
+                ws_bytes);
+    int64_t cap3 = (int64_t)((ws_bytes - sizeof(TcbWs)) / 4);
+    if (cap3 > (1 << 30)) cap3 = 1 << 30;
+    int32_t* idx3 = reinterpret_cast<int32_t*>(wp + sizeof(TcbWs));
+    tcb_set_cap_kernel<<<1, 1, 0, stream>>>(hdr, (int)cap3);
+    B2F_LAUNCH_CHECK();
+    KmRecheck rck;
+    rck.count = &hdr->count2;
+    rck.idx = idx3;
+    rck.cap = (int)cap3;
+    rck.src_idx = nullptr;
+    rck.kappa2 = kappa2_tc3;
+    rck.cmax = cmax;
+    int rc = km_tc_step(X, n, d, ld, prep, k, acc, labels, 3, accumulate, nullptr, &rck, stream);
+    if (rc != B2F_OK) return rc;
+    return km_exact_rows(X, ld, d, nullptr, prep, k, acc, labels, &hdr->count2, idx3, (int)cap3, accumulate, stream);
+  }
+
+  const int cap = tcb_cap_from_bytes(ws_bytes, d);
+  B2F_REQUIRE(cap >= TM, "b2f_kmeans (filter path): workspace of %zu bytes is too small", ws_bytes);
+  TcbWsLayout W = tcb_ws_layout(cap, d);
+  int32_t* amb_idx = reinterpret_cast<int32_t*>(wp + W.off_idx);
+  int32_t* lab_amb = reinterpret_cast<int32_t*>(wp + W.off_lab);
+  int32_t* idx2 = reinterpret_cast<int32_t*>(wp + W.off_idx2);
+  int4* pairs = reinterpret_cast<int4*>(wp + W.off_pairs);
+  float* Xamb = reinterpret_cast<float*>(wp + W.off_x);
+  const bool h16 = filter == KM_FILTER_FP16;
+  const int nstages = km_tcb_stages(d, filter);
   CUtensorMap mx, m1, m2;
   int rc;
   if ((rc = make_map_f32(&mx, X, (uint64_t)n, (uint64_t)d, (uint64_t)ld)) != B2F_OK) return rc;
@@ -850,63 +1065,58 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const void* prep, 
                           : 6.0f * 1.02f / 65536.0f + 2.0f * (3.0f * d + 16.0f) / 8388608.0f;
   const float kappa2 = 2.0f * kappa;
   const float kappa0 = h16 ? 2.0f * 1.01f * sqrtf((float)d) / 33554432.0f : 0.f;
-  const int dbg = getenv("B2F_TC_DBG") ? atoi(getenv("B2F_TC_DBG")) : 0;  // dev knob, results invalid when set
-  const bool acc_main = accumulate && !(dbg & 4);
-  B2F_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcbWs), stream));
+  bool acc_main = accumulate;
+#ifdef B2F_DEV
+  if (getenv("B2F_TC_DBG") && (atoi(getenv("B2F_TC_DBG")) & 4)) acc_main = false;  // results invalid when set
+#endif
   const size_t tile_bytes = h16 ? 2 * (size_t)CHUNK_BYTES + TB_CN_BYTES : 2 * (size_t)tb_stage_bytes<KM_FILTER_BF16X3>();
   const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * tile_bytes +
                       (h16 ? TB_CN_BYTES + 4 * 2 * TB_FX_ROWS * (size_t)d * 4 : 0) + sizeof(SmemB) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
-  unsigned long long* trace = nullptr;
-  const char* trace_path = getenv("B2F_TC_TRACE");  // dev knob: the only place this library allocates
-  const size_t trace_bytes = (size_t)TR_ROLES * TR_TILES * TR_SLOTS * sizeof(unsigned long long);
-  if (trace_path) {
-    B2F_CUDA(cudaMalloc(&trace, trace_bytes));
-    B2F_CUDA(cudaMemsetAsync(trace, 0, trace_bytes, stream));
-  }
   if (h16) {
     const double* c64 = reinterpret_cast<const double*>(pp + P.off_c64);
+    const double* cn64 = reinterpret_cast<const double*>(pp + P.off_cn64);
     const int cgrid = (k + 7) / 8;
+    // scaled pass: this kernel adds RAW rows to the replicas; whatever they hold on entry is folded away first and
+    // the raw sums are folded through the scale right after the kernel, so everything downstream sees scaled sums
+    if (acc_main && colscale && (rc = km_fold_scaled(acc, k, d, nullptr, stream)) != B2F_OK) return rc;
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, -1.0);
-    auto kern = trace ? km_tcb_kernel<KM_FILTER_FP16, true> : km_tcb_kernel<KM_FILTER_FP16, false>;
-    B2F_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, cn, misc, kappa2, kappa0, k, nstages, payload, rep,
-                                             cnt, labels, acc_main ? 1 : 0, hdr, amb_idx, cap, trace);
-    B2F_LAUNCH_CHECK();
+    if (colscale)
+      rc = tcb_launch_filter<KM_FILTER_FP16, true>(grid, smem, stream, mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2,
+                                                   kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
+                                                   amb_idx, cap, pairs, cap);
+    else
+      rc = tcb_launch_filter<KM_FILTER_FP16, false>(grid, smem, stream, mx, m1, m2, X, n, d, ld, nullptr, cn, misc, kappa2,
+                                                    kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
+                                                    amb_idx, cap, pairs, cap);
+    if (rc != B2F_OK) return rc;
+    if (acc_main && colscale && (rc = km_fold_scaled(acc, k, d, colscale, stream)) != B2F_OK) return rc;
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, 1.0);
+    // rows with exactly two candidate centres: two fp64 distances each
+    km_pair_exact_kernel<<<b2f_sm_count() * 8, 256, 0, stream>>>(X, ld, d, colscale, c64, cn64, k, payload, rep, cnt,
+                                                                 labels, hdr, pairs, cap, accumulate ? 1 : 0);
+    B2F_LAUNCH_CHECK();
   } else {
-    auto kern = trace ? km_tcb_kernel<KM_FILTER_BF16X3, true> : km_tcb_kernel<KM_FILTER_BF16X3, false>;
-    B2F_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, cn, misc, kappa2, kappa0, k, nstages, payload, rep,
-                                             cnt, labels, acc_main ? 1 : 0, hdr, amb_idx, cap, trace);
+    rc = tcb_launch_filter<KM_FILTER_BF16X3, false>(grid, smem, stream, mx, m1, m2, X, n, d, ld, nullptr, cn, misc, kappa2,
+                                                    kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
+                                                    amb_idx, cap, nullptr, 0);
+    if (rc != B2F_OK) return rc;
   }
+  tcb_gather_kernel<<<b2f_sm_count() * 4, 256, 0, stream>>>(X, ld, d, colscale, hdr, amb_idx, Xamb, cap);
   B2F_LAUNCH_CHECK();
-  if (trace) {
-    std::vector<unsigned long long> host(trace_bytes / sizeof(unsigned long long));
-    B2F_CUDA(cudaStreamSynchronize(stream));
-    B2F_CUDA(cudaMemcpy(host.data(), trace, trace_bytes, cudaMemcpyDeviceToHost));
-    B2F_CUDA(cudaFree(trace));
-    if (FILE* f = fopen(trace_path, "wb")) {
-      fwrite(host.data(), 1, trace_bytes, f);
-      fclose(f);
-    }
-  }
-  tcb_gather_kernel<<<b2f_sm_count() * 4, 256, 0, stream>>>(X, ld, d, hdr, amb_idx, Xamb, cap);
-  B2F_LAUNCH_CHECK();
-  // 3xTF32 bound: dropped products 3 u^2 with u = 2^-11 on c' = -2c, plus 48 fp32 accumulation roundings
   KmRecheck rck;
   rck.count = &hdr->count2;
   rck.idx = idx2;
   rck.cap = cap;
   rck.src_idx = amb_idx;
-  rck.kappa2 = 2.0f * (6.0f * 1.02f / 4194304.0f + 2.0f * (3.0f * d / 8.0f + 16.0f) / 16777216.0f);
+  rck.kappa2 = kappa2_tc3;
   rck.cmax = cmax;
   rc = km_tc_step(Xamb, (int64_t)cap, d, (int64_t)d, prep, k, acc, lab_amb, 3, accumulate, &hdr->used, &rck, stream);
   if (rc != B2F_OK) return rc;
   tcb_scatter_kernel<<<b2f_sm_count() * 2, 256, 0, stream>>>(hdr, amb_idx, lab_amb, labels);
   B2F_LAUNCH_CHECK();
   // rows still uncertain after 3xTF32: exact fp64 assignment + accumulation (writes labels after the scatter)
-  return km_exact_rows(X, ld, d, prep, k, acc, labels, &hdr->count2, idx2, cap, accumulate, stream);
+  return km_exact_rows(X, ld, d, colscale, prep, k, acc, labels, &hdr->count2, idx2, cap, accumulate, stream);
 }

@@ -40,6 +40,7 @@ __global__ void __launch_bounds__(LR_THREADS, (NCH >= 8) ? 1 : 2)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double* my64 = acc64 + (size_t)warp * NCH * 128;
   for (int i = lane; i < NCH * 128; i += 32) my64[i] = 0.0;
+  __syncwarp();  // lanes zero one layout (i = lane + 32 j) and accumulate in another (lane * 4 + j)
 
   float4 bh[NCH], bl[NCH], g[NCH];
 #pragma unroll
@@ -481,7 +482,7 @@ template <int NCH>
 static int lr_binary_launch(const float* X, const float* y, const float* w, int64_t n, int d, int64_t ld,
                             const double* beta, const double* icpt, double* partials, int grid, cudaStream_t st) {
   size_t smem = (size_t)LR_WARPS * NCH * 128 * sizeof(double);
-  B2F_CUDA(cudaFuncSetAttribute(lr_binary_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  B2F_CUDA(b2f_smem_attr(lr_binary_kernel<NCH>, smem));
   lr_binary_kernel<NCH><<<grid, LR_THREADS, smem, st>>>(X, y, w, n, d, ld, beta, icpt, partials);
   B2F_LAUNCH_CHECK();
   return B2F_OK;
@@ -490,11 +491,11 @@ static int lr_binary_launch(const float* X, const float* y, const float* w, int6
 extern "C" int b2f_lr_binary_lossgrad(const float* X, const float* y, const float* w, int64_t n, int d, int64_t ld,
                                       const double* beta, const double* icpt, double* out, void* scratch,
                                       b2f_stream_t stream) {
-  B2F_REQUIRE(X && y && beta && icpt && out && scratch, "b2f_lr_binary_lossgrad: null pointer");
   B2F_REQUIRE(n >= 0 && d > 0 && ld >= d && ld % 4 == 0, "b2f_lr_binary_lossgrad: need ld >= d, ld %% 4 == 0");
   B2F_REQUIRE(ld <= 1024, "b2f_lr_binary_lossgrad: d (padded) must be <= 1024, got %lld", (long long)ld);
+  if (n == 0) return B2F_OK;  // an empty row shard adds nothing (X / y may be NULL)
+  B2F_REQUIRE(X && y && beta && icpt && out && scratch, "b2f_lr_binary_lossgrad: null pointer");
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_lr_binary_lossgrad: X must be 16-byte aligned");
-  if (n == 0) return B2F_OK;
   cudaStream_t st = b2f_cs(stream);
   const int grid = lr_grid_binary();
   double* partials = static_cast<double*>(scratch);
@@ -518,7 +519,7 @@ static int lr_multi_launch(const float* X, const float* y, const float* w, int64
   size_t smem = floats * sizeof(float);
   B2F_REQUIRE(smem <= 227 * 1024, "b2f_lr_multinomial_lossgrad: K=%d, d=%d needs %zu bytes of shared memory (> 227 KB)", K,
               d, smem);
-  B2F_CUDA(cudaFuncSetAttribute(lr_multinomial_kernel<KP, NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  B2F_CUDA(b2f_smem_attr(lr_multinomial_kernel<KP, NJ>, smem));
   lr_multinomial_kernel<KP, NJ><<<grid, LR_THREADS, smem, st>>>(X, y, w, n, d, ld, K, beta, icpt, partials);
   B2F_LAUNCH_CHECK();
   return B2F_OK;
@@ -527,11 +528,11 @@ static int lr_multi_launch(const float* X, const float* y, const float* w, int64
 extern "C" int b2f_lr_multinomial_lossgrad(const float* X, const float* y, const float* w, int64_t n, int d,
                                            int64_t ld, int n_classes, const double* beta, const double* icpt,
                                            double* out, void* scratch, b2f_stream_t stream) {
-  B2F_REQUIRE(X && y && beta && icpt && out && scratch, "b2f_lr_multinomial_lossgrad: null pointer");
   B2F_REQUIRE(n >= 0 && d > 0 && ld >= d && ld % 4 == 0, "b2f_lr_multinomial_lossgrad: need ld >= d, ld %% 4 == 0");
   B2F_REQUIRE(n_classes >= 2 && n_classes <= 32, "b2f_lr_multinomial_lossgrad: n_classes must be in [2, 32]");
+  if (n == 0) return B2F_OK;  // an empty row shard adds nothing (X / y may be NULL)
+  B2F_REQUIRE(X && y && beta && icpt && out && scratch, "b2f_lr_multinomial_lossgrad: null pointer");
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_lr_multinomial_lossgrad: X must be 16-byte aligned");
-  if (n == 0) return B2F_OK;
   cudaStream_t st = b2f_cs(stream);
   const int K = n_classes;
   const int kp = (K + 7) / 8 * 8;
@@ -540,7 +541,11 @@ extern "C" int b2f_lr_multinomial_lossgrad(const float* X, const float* y, const
               "b2f_lr_multinomial_lossgrad: unsupported shape K=%d d=%d (need ceil(K/8)*8 * ceil(d/256) <= 64)", K, d);
   const int grid = lr_grid_multi();
   double* partials = static_cast<double*>(scratch);
-  if (lr_mn_tc_supported(d, ld, K) && !getenv("B2F_LR_NO_TC")) {
+  bool use_tc = lr_mn_tc_supported(d, ld, K);
+#ifdef B2F_DEV
+  if (getenv("B2F_LR_NO_TC")) use_tc = false;
+#endif
+  if (use_tc) {
     const size_t plen_ = (size_t)K * d + K + 2;
     void* wbuf = static_cast<char*>(scratch) + b2f_align_up((size_t)grid * plen_ * sizeof(double), 1024);
     int rc_ = lr_mn_tc_launch(X, y, w, n, d, K, beta, icpt, partials, grid, wbuf, st);
@@ -571,10 +576,10 @@ extern "C" int b2f_lr_multinomial_lossgrad(const float* X, const float* y, const
 extern "C" int b2f_lr_predict(const float* X, int64_t n, int d, int64_t ld, int n_classes, const double* beta,
                               const double* icpt, double threshold, float* raw, float* prob, float* pred,
                               b2f_stream_t stream) {
-  B2F_REQUIRE(X && beta && icpt, "b2f_lr_predict: null pointer");
   B2F_REQUIRE(n >= 0 && d > 0 && ld >= d, "b2f_lr_predict: need ld >= d");
   B2F_REQUIRE(n_classes >= 2 && n_classes <= 32, "b2f_lr_predict: n_classes must be in [2, 32]");
   if (n == 0) return B2F_OK;
+  B2F_REQUIRE(X && beta && icpt, "b2f_lr_predict: null pointer");
   int64_t want = (n + 7) / 8;
   int64_t cap = (int64_t)b2f_sm_count() * 8;
   int grid = (int)(want < cap ? want : cap);
@@ -606,6 +611,9 @@ static __device__ __align__(256) double lr_na_scratch[LR_NA_SCRATCH_DOUBLES];
 // Device address of lr_na_scratch, looked up once per device.  In host code the symbol name is
 // only a handle for the runtime, not a pointer a kernel can use, so the address has to come
 // from cudaGetSymbolAddress with the right device current.
+// (The cache is written without a lock.  Two host threads making their first call on one device
+// at the same moment both look the address up and store the same value, which is harmless; the
+// calls themselves must be serialised anyway because they share the array.)
 static int lr_na_scratch_ptr(double** out) {
   static double* cached[64];
   int dev = 0;

@@ -580,7 +580,7 @@ int lr_mn_tc_launch(const float* X, const float* y, const float* w, int64_t n, i
     return rc;
   const size_t smem = (size_t)LT_XS * CHUNK_BYTES + (size_t)LT_WS * LT_WSTAGE + 4 * CHUNK_BYTES + 2 * 16384 +
                       sizeof(SmemL) + 64;
-  B2F_CUDA(cudaFuncSetAttribute(lr_mn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  B2F_CUDA(b2f_smem_attr(lr_mn_tc_kernel, smem));
   lr_mn_tc_kernel<<<grid, LT_THREADS, smem, st>>>(mx, mh, ml, y, w, n, d, K, icpt, partials);
   B2F_LAUNCH_CHECK();
 #ifdef LT_TRACE

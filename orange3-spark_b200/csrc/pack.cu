@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(256) pack_columns_kernel(const void* const* __
         float v = 0.f;
         if (p && r < n) {
           v = load_as_f32(p, dt, r);
-          bad |= !isfinite(v);
+          bad |= isnan(v);  // upstream's assembler rejects NaN (and null) under handleInvalid = "error"; Inf passes
         }
         tile[rl][cl] = v;
       }
@@ -181,10 +181,10 @@ __global__ void __launch_bounds__(256) label_hist_kernel(const float* __restrict
 
 extern "C" int b2f_pack_columns(const void* const* col_ptrs_dev, const int32_t* col_dtypes_dev, int d, int64_t n,
                                 float* X, int64_t ld, int32_t* bad_flag, b2f_stream_t stream) {
-  B2F_REQUIRE(col_ptrs_dev && col_dtypes_dev && X, "b2f_pack_columns: null pointer");
   B2F_REQUIRE(d > 0 && n >= 0 && ld >= d && ld % 4 == 0, "b2f_pack_columns: need d > 0, ld >= d, ld %% 4 == 0");
-  B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_pack_columns: X must be 16-byte aligned");
   if (n == 0) return B2F_OK;
+  B2F_REQUIRE(col_ptrs_dev && col_dtypes_dev && X, "b2f_pack_columns: null pointer");
+  B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_pack_columns: X must be 16-byte aligned");
   int64_t tiles = ((n + PK_ROWS - 1) / PK_ROWS) * ((ld + PK_COLS - 1) / PK_COLS);
   int64_t cap = (int64_t)b2f_sm_count() * 8;
   int grid = (int)(tiles < cap ? tiles : cap);
@@ -195,9 +195,9 @@ extern "C" int b2f_pack_columns(const void* const* col_ptrs_dev, const int32_t* 
 
 extern "C" int b2f_colstats(const float* X, int64_t n, int d, int64_t ld, const float* w, const float* shift,
                             double* out, b2f_stream_t stream) {
-  B2F_REQUIRE(X && out, "b2f_colstats: null pointer");
   B2F_REQUIRE(d > 0 && n >= 0 && ld >= d && ld % 4 == 0, "b2f_colstats: need d > 0, ld >= d, ld %% 4 == 0");
   if (n == 0) return B2F_OK;
+  B2F_REQUIRE(X && out, "b2f_colstats: null pointer");
   dim3 grid;
   grid.y = (d + 255) / 256;
   const int g0 = d >= 256 ? 64 : (d + 3) / 4;        // column groups of the first chunk -> row lanes per CTA
@@ -237,8 +237,9 @@ __global__ void scale_columns_kernel(const float* __restrict__ X, float* Y, int6
 
 extern "C" int b2f_scale_columns(const float* X, float* Y, int64_t n, int d, int64_t ld, const float* scale,
                                  const float* shift, b2f_stream_t stream) {
-  B2F_REQUIRE(X && Y, "b2f_scale_columns: null pointer");
   B2F_REQUIRE(d > 0 && n >= 0 && ld >= d && ld % 4 == 0, "b2f_scale_columns: need d > 0, ld >= d, ld %% 4 == 0");
+  if (n == 0) return B2F_OK;
+  B2F_REQUIRE(X && Y, "b2f_scale_columns: null pointer");
   B2F_REQUIRE(((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(Y)) & 15) == 0,
               "b2f_scale_columns: X and Y must be 16-byte aligned");
   if (n == 0) return B2F_OK;
@@ -251,9 +252,9 @@ extern "C" int b2f_scale_columns(const float* X, float* Y, int64_t n, int d, int
 
 extern "C" int b2f_label_hist(const float* y, const float* w, int64_t n, int n_bins, double* hist, int32_t* bad_flag,
                               b2f_stream_t stream) {
-  B2F_REQUIRE(y && hist, "b2f_label_hist: null pointer");
   B2F_REQUIRE(n_bins > 0 && n_bins <= 4096 && n >= 0, "b2f_label_hist: n_bins must be in [1, 4096]");
   if (n == 0) return B2F_OK;
+  B2F_REQUIRE(y && hist, "b2f_label_hist: null pointer");
   int64_t want = (n + 255) / 256;
   int64_t cap = (int64_t)b2f_sm_count() * 4;
   int grid = (int)(want < cap ? want : cap);

@@ -66,8 +66,17 @@ def test_pack_columns_chunked_host_pipeline_and_nan_policy():
     cols[2][77] = np.nan
     with pytest.raises(ValueError):
         pack_columns(cols)
+    with pytest.raises(ValueError):
+        oracle.assemble(cols)  # the oracle holds the same policy
     Xk = pack_columns(cols, handle_invalid="keep")
     assert np.isnan(Xk.data[77, 2].item())
+    assert np.array_equal(Xk.data.cpu().numpy()[:, :5], oracle.assemble(cols, handle_invalid="keep").astype(np.float32),
+                          equal_nan=True)
+    # infinities are ordinary values under both settings (only NaN / null are "invalid" upstream)
+    cols[2][77] = np.inf
+    cols[3][5] = -np.inf
+    Xi = pack_columns(cols)
+    assert np.array_equal(Xi.data.cpu().numpy()[:, :5], oracle.assemble(cols).astype(np.float32))
     with pytest.raises(ValueError):
         pack_columns([np.zeros(3), np.zeros(4)])
 

@@ -124,11 +124,15 @@ def test_assemble_and_scaler():
     a = np.array([1, 2, 3], dtype=np.int32)
     b = np.array([True, False, True])
     c = np.array([0.5, np.nan, 2.5], dtype=np.float32)
-    X = oracle.assemble([a, b, c])
+    # handleInvalid: 'error' (default) rejects NaN and null, 'keep' lets NaN through, Inf is an ordinary value
+    with pytest.raises(ValueError):
+        oracle.assemble([a, b, c])
+    X = oracle.assemble([a, b, c], handle_invalid="keep")
     assert X.dtype == np.float64 and X.shape == (3, 3)
     assert np.isnan(X[1, 2]) and X[2, 0] == 3.0 and X[0, 1] == 1.0
     with pytest.raises(ValueError):
         oracle.assemble([np.array([1.0, None], dtype=object)])
+    assert np.isinf(oracle.assemble([np.array([1.0, np.inf, -np.inf])])[1:, 0]).all()
     Z = np.array([[1.0, 5.0], [2.0, 5.0], [4.0, 5.0]])
     mean, std = oracle.standard_scaler_fit(Z)
     np.testing.assert_allclose(std, [np.std(Z[:, 0], ddof=1), 0.0])
