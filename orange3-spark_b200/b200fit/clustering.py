@@ -27,7 +27,7 @@ def _torch():
 class CudaLloydEngine:
     """Device state + kernel calls for one rank's row shard."""
 
-    def __init__(self, X, k, w=None, algo=N.KM_AUTO):
+    def __init__(self, X, k, w=None, algo=N.KM_AUTO, ws_bytes=None):
         N.require_cuda()
         torch = _torch()
         self.L = N.lib()
@@ -54,7 +54,8 @@ class CudaLloydEngine:
         if self.col_scale is not None and not (self.use_ws and algo in (N.KM_AUTO, N.KM_TCH)):
             raise ValueError("a scaled view needs the fp16 filter pipeline; materialise it first")
         if self.use_ws:
-            self.ws_bytes = int(self.L.b2f_kmeans_ws_bytes(X.n, self.k, self.d))
+            # (ws_bytes: tests shrink the workspace to force the overflow fallback)
+            self.ws_bytes = int(self.L.b2f_kmeans_ws_bytes(X.n, self.k, self.d)) if ws_bytes is None else int(ws_bytes)
             self.ws = torch.zeros(self.ws_bytes, dtype=torch.uint8, device=dev)
             self.labels_buf = torch.empty(X.n, dtype=torch.int32, device=dev)
 

@@ -83,8 +83,11 @@ class ColumnarFrame:
         cols = {}
         for name in pdf.columns:
             v = pdf[name].to_numpy()
-            if v.dtype == object and len(v) and hasattr(v[0], "toArray"):  # pyspark Vector cells
-                v = np.stack([x.toArray() for x in v])
+            if v.dtype == object and len(v):
+                if hasattr(v[0], "toArray"):  # pyspark.ml.linalg Vector cells (dense or sparse)
+                    v = np.stack([x.toArray() for x in v])
+                elif isinstance(v[0], (np.ndarray, list, tuple)):  # Arrow list<double> / numpy-array cells
+                    v = np.stack([np.asarray(x, dtype=np.float64) for x in v])
             cols[str(name)] = v
         return cls(cols, origin=(pdf, {k: id(v) for k, v in cols.items()}))
 

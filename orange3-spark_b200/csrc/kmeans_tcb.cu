@@ -92,7 +92,7 @@ constexpr int TB_CN_BYTES = 128 * 32;  // the ||c||^2 k-block of a centre tile: 
 #define TB_FX_ROWS 8
 #endif
 // dev tracing (B2F_TC_TRACE=<file>): block 0 stamps clock64() at the hand-offs of its first TR_TILES row tiles
-constexpr int TR_TILES = 64, TR_SLOTS = 32, TR_ROLES = 12;  // mma | 8 epilogue warps | split | finish | B producer
+[[maybe_unused]] constexpr int TR_TILES = 64, TR_SLOTS = 32, TR_ROLES = 12;  // mma | 8 epilogue warps | split | finish | B producer
 #define TR(role, slot)                                                                      \
   do {                                                                                      \
     if (TRACE && blockIdx.x == 0 && lane == 0 && it < (uint32_t)TR_TILES)                   \

@@ -5,7 +5,7 @@
 //   softmax / loss / (P - Y) per row (thread == row), written to shared memory as bf16 pairs
 //   GEMM2  G^T[d x 32]       += X_tile^T[d x 128] . (P - Y)[128 x 32]   tcgen05 kind::f16, bf16x3,
 //                                                                 A = X^T read MN-major from smem
-//          as x1 . [p1 | p2] (one N = 64 instruction, so x1 is read from shared memory once) + x2 . p1
+//          as x1 . [p1 | p2] + x2 . [p1 | p2] (N = 64 instructions: each X piece is read from shared memory once)
 // X is streamed from HBM once (GEMM1) and re-read from L2 for GEMM2; G^T stays in tensor memory for the
 // CTA's lifetime.
 // What bounds it (hand-off trace, tools/lr_trace.py): shared-memory bandwidth.  Per 128 x 512 tile the shared
@@ -58,7 +58,7 @@ constexpr uint32_t LT_D1 = 0;      // margins, 2 buffers x 32 columns
 constexpr uint32_t LT_A1 = 64;     // GEMM1 operand ring: LT_A1_SLOTS slots x (32 hi + 32 lo) columns
 constexpr uint32_t LT_A1_SLOTS = LT_PCAT ? 3 : 4;
 constexpr uint32_t LT_G = LT_A1 + LT_A1_SLOTS * 64;  // G^T: d/128 blocks x LT_GW columns (features on lanes)
-constexpr uint32_t LT_GW = LT_PCAT ? 64 : 32;        // LT_PCAT: columns 0-31 = x1.p1 + x2.p1, columns 32-63 = x1.p2
+constexpr uint32_t LT_GW = LT_PCAT ? 64 : 32;        // LT_PCAT: columns 0-31 = (x1 + x2).p1, columns 32-63 = (x1 + x2).p2
 static_assert(LT_G + 4 * LT_GW <= LT_TMEM_COLS, "tensor memory budget");
 // (P - Y) operand tile in shared memory, per buffer 16 KB: bf16 pieces p1, p2, each two K atoms (64 rows of X) of
 // 32 class rows x 128 B.  LT_PCAT puts p2's class rows right behind p1's inside an atom so that one N = 64 operand
@@ -313,8 +313,11 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
           const uint32_t aoff = (uint32_t)s * (2048 >> 4);                            // 16 rows x 128 B
           const uint32_t boff = (uint32_t)(s >> 2) * (LT_PY_ATOM >> 4) + (s & 3) * 2;  // atom of 64 rows, 32 B steps
           if (LT_PCAT) {
-            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, IDESC_G2_N64, (t | s) ? 1u : 0u);  // x1 . [p1 | p2]
-            mma_bf16_ss(dg, ax2 + aoff, bp1 + boff, IDESC_G2, 1u);                     // x2 . p1
+            // x1 . [p1 | p2] and x2 . [p1 | p2]: all four products of the two-piece split.  (Until round 2 the
+            // second one was x2 . p1 only: the dropped x2 . p2 term, 2^-18 |x||p| per product, and a TRUNCATED
+            // x2 put the gradient at ~2e-5 of its largest entry; the N = 64 form costs tensor time only.)
+            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, IDESC_G2_N64, (t | s) ? 1u : 0u);
+            mma_bf16_ss(dg, ax2 + aoff, bp1 + boff, IDESC_G2_N64, 1u);
           } else {
             mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, IDESC_G2, (t | s) ? 1u : 0u);
             mma_bf16_ss(dg, ax1 + aoff, bp2 + boff, IDESC_G2, 1u);
@@ -510,12 +513,13 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
           uint32_t o1[4], o2[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            // x1 = x rounded to bf16 (nearest, ties away) and x2 = (x - x1) truncated to bf16, with
-            // full-rate integer ops; __byte_perm packs the two high halves (even k in the low 16 bits)
+            // x1 = x rounded to bf16 (nearest, ties away) and x2 = (x - x1) rounded the same way (what is left of
+            // x is then below 2^-18 |x|; truncating x2 left 2^-16), with full-rate integer ops; __byte_perm packs
+            // the two high halves (even k in the low 16 bits)
             const uint32_t ra = (__float_as_uint(f[2 * e]) + 0x8000u) & 0xFFFF0000u;
             const uint32_t rb = (__float_as_uint(f[2 * e + 1]) + 0x8000u) & 0xFFFF0000u;
-            const uint32_t la = __float_as_uint(f[2 * e] - __uint_as_float(ra));
-            const uint32_t lb = __float_as_uint(f[2 * e + 1] - __uint_as_float(rb));
+            const uint32_t la = __float_as_uint(f[2 * e] - __uint_as_float(ra)) + 0x8000u;
+            const uint32_t lb = __float_as_uint(f[2 * e + 1] - __uint_as_float(rb)) + 0x8000u;
             o1[e] = __byte_perm(ra, rb, 0x7632);
             o2[e] = __byte_perm(la, lb, 0x7632);
           }

@@ -109,3 +109,26 @@ def press_apply_evaluator(cls, in_df, edits=None):
         param_map[ForeignParam(inst, "metricName", "")] = metric
         values[metric] = inst.apply(in_df, param_map)
     return values
+
+
+class _FakeSparkSession:
+    def createDataFrame(self, pdf):
+        return FakeSparkDataFrame(pdf)
+
+
+class FakeSparkDataFrame:
+    """The slice of pyspark.sql.DataFrame the bridge touches: `.columns`, `.toPandas()` (Spark's columnar collect)
+    and `.sparkSession.createDataFrame(pandas_frame)` for the way back.  Counts its collects."""
+
+    def __init__(self, pdf):
+        self._pdf = pdf
+        self.sparkSession = _FakeSparkSession()
+        self.collected = 0
+
+    @property
+    def columns(self):
+        return list(self._pdf.columns)
+
+    def toPandas(self):
+        self.collected += 1
+        return self._pdf.copy()

@@ -33,21 +33,30 @@ def kmeans_state(C, k, d):
     return cen, prep, acc
 
 
-def kmeans_step_raw(X, n, d, ld, C, algo, w=None, want_labels=True, ws_bytes=None, info=None):
-    """One b2f_kmeans_step (or _step_ws for B2F_KM_TCB / B2F_KM_TCH) + fold.
-    Returns labels, sums[k,d], counts[k], cost, nrows (host)."""
+def kmeans_step_raw(X, n, d, ld, C, algo, w=None, want_labels=True, ws_bytes=None, info=None, use_ws=False,
+                    col_scale=None):
+    """One b2f_kmeans_step (or _step_ws for B2F_KM_TCB / B2F_KM_TCH, or any algo with use_ws; _step_scaled with a
+    column scale) + fold.  Returns labels, sums[k,d], counts[k], cost, nrows (host)."""
     L = N.lib()
     k = C.shape[0]
     cen, prep, acc = kmeans_state(C, k, d)
     labels = torch.full((n,), -1, dtype=torch.int32, device=dev()) if want_labels else None
-    if algo in (N.KM_TCB, N.KM_TCH):
+    if algo in (N.KM_TCB, N.KM_TCH) or use_ws or col_scale is not None:
         wsb = int(L.b2f_kmeans_ws_bytes(n, k, d)) if ws_bytes is None else ws_bytes
         ws = torch.zeros(wsb, dtype=torch.uint8, device=dev())
-        N.check(L.b2f_kmeans_step_ws(N.ptr(X), n, d, ld, N.ptr(w), N.ptr(prep), k, N.ptr(acc), N.ptr(labels),
-                                     N.ptr(ws), wsb, algo, stream()), "step_ws")
+        if col_scale is not None:
+            N.check(L.b2f_kmeans_step_scaled(N.ptr(X), n, d, ld, N.ptr(col_scale), N.ptr(prep), k, N.ptr(acc),
+                                             N.ptr(labels), N.ptr(ws), wsb, stream()), "step_scaled")
+        else:
+            N.check(L.b2f_kmeans_step_ws(N.ptr(X), n, d, ld, N.ptr(w), N.ptr(prep), k, N.ptr(acc), N.ptr(labels),
+                                         N.ptr(ws), wsb, algo, stream()), "step_ws")
         if info is not None:
-            hdr = ws[:8].view(torch.int32).cpu().numpy()
-            info["uncertain"], info["rechecked"] = int(hdr[0]), int(hdr[1])
+            # workspace header (include/b200fit.h): [0] rows listed for the 3xTF32 re-check, [1] rows re-checked,
+            # [2] rows listed for the fp64 kernel, [3] capacity of each list, [4] rows offered to the pair check
+            hdr = ws[:20].view(torch.int32).cpu().numpy()
+            info["listed"], info["rechecked"], info["exact"], info["cap"] = (int(v) for v in hdr[:4])
+            info["pairs"] = min(int(hdr[4]), int(hdr[3]))
+            info["uncertain"] = info["listed"] + info["pairs"]
     else:
         N.check(L.b2f_kmeans_step(N.ptr(X), n, d, ld, N.ptr(w), N.ptr(prep), k, N.ptr(acc), N.ptr(labels), algo,
                                   stream()), "step")

@@ -100,6 +100,15 @@ def _worker(rank, world, port, out):
         trail = LBFGS(30, 10, 1e-9).run(f, x0)
         assert len(trail) == len(ref_lr["states"])
         np.testing.assert_allclose(trail[-1].x, ref_lr["states"][-1]["x"], rtol=1e-8, atol=1e-10)
+        # an EMPTY shard on one rank: it must still join every collective of the Lloyd loop
+        lo2, hi2 = (0, n) if rank == 0 else (n, n)
+        eng2 = OracleLloydEngine(X[lo2:hi2], k)
+        eng2.set_centers(C0)
+        it2, costs2, conv2, _ = lloyd(eng2, comm, 15, 1e-6)
+        assert it2 == ref["numIter"] and conv2 == ref["converged"]
+        np.testing.assert_allclose(eng2.get_centers(), ref["centers"], rtol=1e-12, atol=1e-12)
+        # an error condition seen by ONE rank is raised by all of them (no rank left waiting in a collective)
+        assert comm.any_rank(rank == 1, device="cpu") is True and comm.any_rank(False, device="cpu") is False
         t = torch.tensor([float(rank)])
         comm.all_reduce_max(t)
         assert t.item() == world - 1

@@ -79,8 +79,8 @@ def test_lr_multinomial_lossgrad_matches_oracle(n, d, K):
             loss, g, gb, W = G.lr_lossgrad_raw(X, y, ww, n, d, ld, K, B, b0)
             rl, rg, rgb = oracle.lr_multinomial_lossgrad(Xh, yh, wwh, B, b0, np.ones(d))
             assert loss == pytest.approx(rl, rel=1e-5)
-            _grad_close(g, rg, rtol=2e-5)
-            _grad_close(gb, rgb, rtol=2e-5)
+            _grad_close(g, rg)   # north_star's 1e-5 (round 1 needed 2e-5: truncated x2 piece, dropped x2.p2 term)
+            _grad_close(gb, rgb)
 
 
 def _fit_both(Xh, yh, wh=None, **kw):
@@ -153,11 +153,11 @@ def test_lr_multinomial_elastic_net_follows_oracle_trajectory():
     """BASELINE config 4 shape at reduced N: 20 classes, elasticNetParam=0.5 => OWL-QN."""
     Xh, yh = _multi_data(8000, 64, 20, 21)
     m, ref = _fit_both(Xh, yh, regParam=0.01, elasticNetParam=0.5, family="multinomial", maxIter=12)
-    _check_trajectory(m, ref, rtol=2e-5)
+    _check_trajectory(m, ref)
     assert m.coefficientMatrix.shape == (20, 64)
     sc = np.abs(ref["coefficients"]).max()
-    np.testing.assert_allclose(m.coefficientMatrix, ref["coefficients"], rtol=2e-5, atol=2e-5 * sc)
-    np.testing.assert_allclose(m.interceptVector, ref["intercept"], rtol=2e-5, atol=2e-5)
+    np.testing.assert_allclose(m.coefficientMatrix, ref["coefficients"], rtol=1e-5, atol=1e-5 * sc)
+    np.testing.assert_allclose(m.interceptVector, ref["intercept"], rtol=1e-5, atol=1e-5)
 
 
 def test_lr_model_transform_matches_oracle_prediction():

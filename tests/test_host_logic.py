@@ -35,12 +35,16 @@ def test_cabi_library_exports_every_declared_symbol():
 
 
 def test_estimator_discovery_and_description():
-    est = fw.list_estimators(b200fit.clustering)
-    assert "KMeans" in est and "KMeansModel" not in est
-    est = fw.list_estimators(b200fit.classification)
-    assert "LogisticRegression" in est and "LogisticRegressionModel" not in est
-    assert "VectorAssembler" in fw.list_transformers(b200fit.feature)
-    assert "StandardScalerModel" not in fw.list_transformers(b200fit.feature)
+    # exact sets: the abstract bases imported into the modules (Estimator, Transformer, Model) must NOT show up as
+    # selectable entries -- pyspark's are ABCs and the widget filters with inspect.isabstract
+    assert set(fw.list_estimators(b200fit.clustering)) == {"KMeans"}
+    assert set(fw.list_estimators(b200fit.classification)) == {"LogisticRegression"}
+    assert set(fw.list_estimators(b200fit.feature)) == {"StandardScaler"}
+    assert set(fw.list_transformers(b200fit.feature)) == {"VectorAssembler"}
+    for base in (b200fit.base.Estimator, b200fit.base.Transformer, b200fit.base.Model, b200fit.evaluation.Evaluator):
+        assert inspect.isabstract(base)
+        with pytest.raises(TypeError):
+            base()
     name, doc, table = fw.describe(b200fit.clustering.KMeans)
     assert name == "b200fit.clustering.KMeans" and doc
     assert list(table)[:3] == ["featuresCol", "predictionCol", "k"]
@@ -89,6 +93,59 @@ def test_param_map_is_resolved_by_name_and_types():
         km.copy({"k": "many"})
     lr = b200fit.classification.LogisticRegression(regParam=1)
     assert lr.getRegParam() == 1.0 and lr.setMaxIter(5).getMaxIter() == 5
+
+
+def test_dataframe_bridge_round_trip_with_a_pyspark_shaped_frame():
+    """as_frame() collects a pyspark-like frame once through toPandas(); return_like() hands the result back as
+    the caller's own frame type with only the new columns converted."""
+    import pandas as pd
+
+    from b200fit.frame import as_frame, return_like
+
+    feats = [np.array([1.0, 2.0]), np.array([3.0, 4.0]), np.array([5.0, 6.0])]
+    pdf = pd.DataFrame({"id": [7, 8, 9], "features": feats})
+    sdf = fw.FakeSparkDataFrame(pdf)
+    frame = as_frame(sdf)
+    assert sdf.collected == 1 and frame.columns == ["id", "features"]
+    assert frame.col("features").shape == (3, 2)  # vector cells stacked into one 2-D column
+    out = frame.withColumn("prediction", np.array([0, 1, 1], dtype=np.int32))
+    back = return_like(sdf, out)
+    assert isinstance(back, fw.FakeSparkDataFrame) and back.columns == ["id", "features", "prediction"]
+    res = back.toPandas()
+    assert res["prediction"].tolist() == [0, 1, 1] and res["id"].tolist() == [7, 8, 9]
+    assert all(np.array_equal(a, b) for a, b in zip(res["features"], feats))  # caller's column untouched
+    # pandas in -> pandas out; vector-valued new columns become one array per row
+    out2 = as_frame(pdf).withColumn("probability", np.array([[0.9, 0.1], [0.2, 0.8], [0.3, 0.7]]))
+    back2 = return_like(pdf, out2)
+    assert isinstance(back2, pd.DataFrame) and back2["probability"].iloc[1].tolist() == [0.2, 0.8]
+    # our own frame type (and dicts) stay as they are
+    cf = ColumnarFrame({"a": np.zeros(2)})
+    assert return_like(cf, cf.withColumn("b", np.ones(2))).columns == ["a", "b"]
+
+
+def test_thresholds_text_is_parsed_like_a_list():
+    from b200fit.classification import _parse_thresholds
+
+    assert _parse_thresholds(None) is None and _parse_thresholds("None") is None and _parse_thresholds("") is None
+    assert _parse_thresholds("[0.5, 0.25, 0.25]") == [0.5, 0.25, 0.25]
+    assert _parse_thresholds("0.5;0.5") == [0.5, 0.5] and _parse_thresholds((1, 2)) == [1.0, 2.0]
+    for bad in ("[0.5, x]", [-0.1, 0.5], [0.0, 0.0, 1.0]):
+        with pytest.raises(ValueError):
+            _parse_thresholds(bad)
+
+
+def test_constant_label_oracle_matches_mllib_short_circuit():
+    rng = np.random.default_rng(0)
+    X = rng.normal(size=(50, 3))
+    r1 = oracle.lr_fit(X, np.ones(50, dtype=np.int64))
+    r0 = oracle.lr_fit(X, np.zeros(50, dtype=np.int64))
+    assert r1["intercept"] == np.inf and r0["intercept"] == -np.inf
+    assert not r1["coefficients"].any() and r1["objectiveHistory"] == [] and r1["totalIterations"] == 0
+    rm = oracle.lr_fit(X, np.full(50, 2, dtype=np.int64), family="multinomial")
+    assert rm["intercept"].tolist() == [0.0, 0.0, np.inf] and rm["coefficients"].shape == (3, 3)
+    # without an intercept there is no short circuit
+    rn = oracle.lr_fit(X, np.ones(50, dtype=np.int64), fit_intercept=False, reg_param=0.1, max_iter=5)
+    assert np.isfinite(rn["coefficients"]).all() and len(rn["objectiveHistory"]) > 1
 
 
 def test_frame_behaves_like_the_dataframe_calls_the_widgets_make():

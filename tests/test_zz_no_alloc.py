@@ -4,11 +4,14 @@ call cudaMalloc).  It keeps its per-CTA partial sums in an array built into the 
 
 The check: through the C ABI, its output must equal the regular entry point's (which uses
 caller-provided scratch) on the same inputs, twice in a row -- the second call runs on top of
-whatever the first one left in the shared array.  The file name sorts last so that a failure here
+whatever the first one left in the shared array -- and, so that the comparison is not just one
+code path against its twin, the CPU oracle's loss and gradient for the same rows.  The file name sorts last so that a failure here
 cannot hide the result of any other test in a stop-at-first-failure run."""
 import numpy as np
 import pytest
 import torch
+
+import oracle
 
 pytestmark = pytest.mark.gpu
 
@@ -48,7 +51,13 @@ def test_noalloc_entry_matches_regular_entry_on_two_calls_in_a_row():
         # (1e-5 relative) is far looser than needed
         scale = np.abs(ref).max()
         np.testing.assert_allclose(got, ref, rtol=1e-5, atol=1e-5 * scale)
-        assert got[d + 2] == pytest.approx(float(wh.astype(np.float64).sum()), rel=1e-12)
+        W = float(wh.astype(np.float64).sum())
+        assert got[d + 2] == pytest.approx(W, rel=1e-12)
+        # and against the oracle (numpy fp64 restatement of the MLlib aggregator), at the parity tests' tolerance
+        rl, rg, rgb = oracle.lr_binary_lossgrad(Xh, yh, wh.astype(np.float64), beta, 0.25, np.ones(d))
+        assert got[d + 1] / W == pytest.approx(rl, rel=1e-5)
+        np.testing.assert_allclose(got[:d] / W, rg, rtol=1e-5, atol=1e-5 * np.abs(rg).max())
+        assert got[d] / W == pytest.approx(rgb, rel=1e-5, abs=1e-5 * np.abs(rg).max())
 
 
 def test_noalloc_entry_rejects_rows_wider_than_its_scratch():
