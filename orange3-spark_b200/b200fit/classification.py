@@ -44,6 +44,9 @@ class CudaLogRegEngine:
         self.scratch = torch.empty(max(1, self.L.b2f_lr_scratch_bytes(self.d, self.nc)), dtype=torch.uint8, device=dev)
         self.beta = torch.zeros(self.K * self.d, dtype=torch.float64, device=dev)
         self.icpt = torch.zeros(self.K, dtype=torch.float64, device=dev)
+        # pinned staging for the per-pass traffic of a fit: iterate up (K*d + K doubles), payload down
+        self.h_x = torch.empty(self.K * self.d + self.K, dtype=torch.float64, pin_memory=True)
+        self.h_out = torch.empty(self.plen, dtype=torch.float64, pin_memory=True)
         self.launches = 0
 
     def lossgrad_device(self):
@@ -62,10 +65,19 @@ class CudaLogRegEngine:
         return self.out
 
     def lossgrad(self, beta, icpt):
-        torch = _torch()
-        self.beta.copy_(torch.from_numpy(np.ascontiguousarray(beta, dtype=np.float64).ravel()))
-        self.icpt.copy_(torch.from_numpy(np.ascontiguousarray(icpt, dtype=np.float64).ravel()))
+        kd = self.K * self.d
+        hx = self.h_x.numpy()
+        hx[:kd] = np.asarray(beta, dtype=np.float64).ravel()
+        hx[kd:] = np.asarray(icpt, dtype=np.float64).ravel()
+        self.beta.copy_(self.h_x[:kd], non_blocking=True)
+        self.icpt.copy_(self.h_x[kd:], non_blocking=True)
         return self.lossgrad_device()
+
+    def payload_to_host(self, payload):
+        """The (all-reduced) payload as a numpy view of pinned memory: one async copy + one stream sync."""
+        self.h_out.copy_(payload, non_blocking=True)
+        _torch().cuda.current_stream().synchronize()
+        return self.h_out.numpy()
 
 
 def make_objective(engine, comm, K, d, inv_std, l2w, fit_intercept, active):
@@ -76,7 +88,7 @@ def make_objective(engine, comm, K, d, inv_std, l2w, fit_intercept, active):
         b = x[K * d:] if fit_intercept else np.zeros(K)
         payload = engine.lossgrad(C * inv_std[None, :], b)
         comm.all_reduce_sum(payload)
-        p = payload.cpu().numpy()
+        p = engine.payload_to_host(payload) if hasattr(engine, "payload_to_host") else payload.cpu().numpy()
         W = p[K * d + K + 1]
         G = p[: K * d].reshape(K, d) * inv_std[None, :] / W
         gb = p[K * d: K * d + K] / W
