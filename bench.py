@@ -199,6 +199,9 @@ def b200_arm(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    from b200fit.dist import bind_to_gpu_numa_node
+
+    numa = bind_to_gpu_numa_node(local) if world > 1 else None  # before any pinned allocation
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     comm = Comm()
@@ -277,6 +280,8 @@ def b200_arm(args):
                       "pair_checked_rows_last_iter_this_rank": pair_rows}}
     if args.rows:
         line["reduced"] = True
+    if numa:
+        line["numa_binding_rank0"] = numa
 
     # ---------------- end to end through the public API with HOST buffers ----------------
     if not args.no_e2e:

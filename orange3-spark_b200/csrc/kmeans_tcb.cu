@@ -80,7 +80,14 @@ __device__ __forceinline__ float tb_row_scale(float xn, float cmax) {
   e = max(1, min(254, e));
   return __int_as_float(e << 23);
 }
-constexpr int TB_THREADS = 640;
+// TB_ACC_WARPS = 1 adds a sixth warpgroup (warps 20-23) that takes HALF of every row tile's accumulation off the
+// finish warps (which the hand-off trace shows pacing the kernel: ~2 400 cycles of merge / certainty / labels and
+// then ~8 000 of accumulation per row tile): the finish warps publish the labels in shared memory, keep rows 0-15 of
+// their 32 and the new warps do rows 16-31.  Row slots shrink to 4 rows so the eight warps fit the same 32 KB.
+#ifndef TB_ACC_WARPS
+#define TB_ACC_WARPS 0
+#endif
+constexpr int TB_THREADS = TB_ACC_WARPS ? 768 : 640;
 constexpr int TB_CN_BYTES = 128 * 32;  // the ||c||^2 k-block of a centre tile: 128 centres x 16 halves
 #ifndef TB_REG_CTRL
 // what the epilogue warpgroups gain, (EPI - 96) * 256, must be given back first by the others:
@@ -88,9 +95,12 @@ constexpr int TB_CN_BYTES = 128 * 32;  // the ||c||^2 k-block of a centre tile: 
 #define TB_REG_CTRL 48
 #define TB_REG_FIN 80
 #define TB_REG_EPI 128
+#define TB_REG_ACC 40
 #define TB_FIN_ROWS 8
-#define TB_FX_ROWS 8
+#define TB_FX_ROWS (TB_ACC_WARPS ? 4 : 8)
 #endif
+constexpr int TB_FX_WARPS = TB_ACC_WARPS ? 8 : 4;       // warps that own row slots
+constexpr int TB_FX_SPAN = TB_ACC_WARPS ? 16 : 32;      // rows of a tile each of them accumulates
 // dev tracing (B2F_TC_TRACE=<file>): block 0 stamps clock64() at the hand-offs of its first TR_TILES row tiles
 [[maybe_unused]] constexpr int TR_TILES = 64, TR_SLOTS = 32, TR_ROLES = 12;  // mma | 8 epilogue warps | split | finish | B producer
 #define TR(role, slot)                                                                      \
@@ -111,6 +121,7 @@ constexpr int W_EPI0 = 0;    // warps 0-7   epilogue
 constexpr int W_SPLIT0 = 8;  // warps 8-11  split
 constexpr int W_FIN0 = 12;   // warps 12-15 finish
 constexpr int W_XPROD = 16, W_MMA = 17, W_BPROD = 18, W_ALLOC = 19;  // W_ALLOC: TMEM allocator + second MMA issuer
+constexpr int W_ACC0 = 20;   // warps 20-23 (TB_ACC_WARPS): second half of the accumulation
 
 struct SmemB {
   uint64_t xs_full[4], xs_empty[4];  // fp32 staging, per 32-float chunk
@@ -120,7 +131,9 @@ struct SmemB {
   uint64_t a_full[2], a_empty[2];    // epilogue -> finish hand-off
   uint64_t n_full[4], n_empty[4];    // split -> finish: squared row norms of a tile
   uint64_t tok[2];                   // MMA issue token: warp p has put its batch into the tensor queue
-  uint64_t fx_full[4][2];            // finish warps (fp16 filter): rows of a batch have landed in their slot
+  uint64_t fx_full[8][2];            // accumulating warps (fp16 filter): rows of a batch have landed in their slot
+  uint64_t l_full[2], l_empty[2];    // finish -> accumulate warps: labels of a row tile (TB_ACC_WARPS)
+  int lab[2][TM];
   uint32_t tmem_base;
   float xnorm2[4][TM];
   float p_b1[2][2][TM], p_b2[2][2][TM];  // [slot][epilogue warp of the lane quarter][row]: best, second best
@@ -160,6 +173,57 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, 
 
 }  // namespace
 
+// Accumulation of TB_FX_SPAN consecutive rows (first row r0; lane u < TB_FX_SPAN holds the label of row r0 + u, or -1
+// for a row that is not to be added) into the replica table, entirely on the copy engine: bulk copy L2 -> shared
+// memory slot, then bulk reduce-add of each row into the replica row of its label.  No registers hold row data and no
+// load latency sits in this warp; two batches of TB_FX_ROWS rows are in flight (two slots, `fx_full` their barriers,
+// `fxc` the running batch count of this warp).  At 8 rows in flight through registers this loop set the pace of the
+// whole kernel (hand-off trace).
+__device__ __forceinline__ void tb_bulk_accumulate(const float* __restrict__ X, int64_t n, int64_t ld, int d, int64_t r0,
+                                                   int my_lab, float* __restrict__ myrep, uint8_t* mybuf,
+                                                   uint64_t* fx_full, uint32_t& fxc, int lane) {
+  constexpr int NB = TB_FX_SPAN / TB_FX_ROWS;
+  const uint32_t rowbytes = (uint32_t)d * 4u;
+  const int u = lane & (TB_FX_ROWS - 1);
+  int lbl_b[NB];
+#pragma unroll
+  for (int b = 0; b < NB; ++b) lbl_b[b] = __shfl_sync(0xffffffffu, my_lab, b * TB_FX_ROWS + u);
+  auto issue_load = [&](int b, bool newest_may_pend) {
+    const uint32_t slot = (fxc + b) & 1u;
+    const bool merged = ld == d;  // the batch's rows are one contiguous block: one copy instead of TB_FX_ROWS
+    const int64_t rb = r0 + b * TB_FX_ROWS;
+    const int nlive = (int)max((int64_t)0, min((int64_t)TB_FX_ROWS, n - rb));
+    const bool act = lane < TB_FX_ROWS && lbl_b[b] >= 0;
+    const unsigned m = __ballot_sync(0xffffffffu, act);
+    // the reduction that read this slot two batches ago must be done with it
+    if (newest_may_pend) bulk_wait_read<1>();
+    else bulk_wait_read<0>();
+    if (lane == 0) {
+      const uint32_t bytes = merged ? (m ? (uint32_t)nlive * rowbytes : 0u) : (uint32_t)__popc(m) * rowbytes;
+      if (bytes) mbar_expect_tx(&fx_full[slot], bytes);
+      else mbar_arrive(&fx_full[slot]);
+      if (merged && bytes)
+        bulk_load_hint(mybuf + (size_t)slot * TB_FX_ROWS * rowbytes, X + rb * ld, bytes, &fx_full[slot], L2_EVICT_FIRST);
+    }
+    __syncwarp();
+    if (act && !merged)
+      bulk_load_hint(mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes, X + (rb + lane) * ld, rowbytes,
+                     &fx_full[slot], L2_EVICT_FIRST);
+  };
+  issue_load(0, true);
+  issue_load(1, false);
+#pragma unroll
+  for (int b = 0; b < NB; ++b) {
+    const uint32_t slot = (fxc + b) & 1u;
+    mbar_wait_ns(&fx_full[slot], ((fxc + b) >> 1) & 1u, 64);
+    if (lane < TB_FX_ROWS && lbl_b[b] >= 0)
+      bulk_reduce_add_f32(myrep + (size_t)lbl_b[b] * d, mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes, rowbytes);
+    bulk_commit();
+    if (b + 2 < NB) issue_load(b + 2, false);
+  }
+  fxc += NB;
+}
+
 template <int MODE, bool TRACE, bool SCALED>
 __global__ void __launch_bounds__(TB_THREADS, 1)
     km_tcb_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c1,
@@ -186,7 +250,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   uint8_t* aconst = stages + (size_t)nstages * TB_TILE_BYTES;
   // fp16: row buffers of the finish warps: 4 warps x 2 slots x TB_FX_ROWS rows of d floats
   uint8_t* fxbuf = aconst + (H16 ? TB_CN_BYTES : 0);
-  SmemB* sm = reinterpret_cast<SmemB*>(fxbuf + (H16 ? 4 * 2 * TB_FX_ROWS * d * 4 : 0));
+  SmemB* sm = reinterpret_cast<SmemB*>(fxbuf + (H16 ? TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4 : 0));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t ntiles = (n + TM - 1) / TM;
@@ -205,13 +269,15 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_init(&sm->t_full[c], 1);
       mbar_init(&sm->t_empty[c], EPI_THREADS);
     }
-    for (int c = 0; c < 8; ++c) mbar_init(&sm->fx_full[c >> 1][c & 1], 1);
+    for (int c = 0; c < 16; ++c) mbar_init(&sm->fx_full[c >> 1][c & 1], 1);
     for (int c = 0; c < 2; ++c) {
       mbar_init(&sm->tok[c], 1);
       mbar_init(&sm->xa_full[c], EPI_THREADS);
       mbar_init(&sm->xa_empty[c], 1);
       mbar_init(&sm->a_full[c], 2 * EPI_THREADS);
       mbar_init(&sm->a_empty[c], EPI_THREADS);
+      mbar_init(&sm->l_full[c], EPI_THREADS);
+      mbar_init(&sm->l_empty[c], EPI_THREADS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -244,7 +310,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   // 96 registers it spills its loop state to local memory, and with all of L1 carved out for shared memory each
   // reload is an L2 round trip (~1000 idle cycles per centre tile in the hand-off trace).  The control and finish warpgroups
   // give registers back, the two epilogue warpgroups take them (setmaxnreg works per 4-warp group).
-  if (warp >= W_XPROD) {
+  if (warp >= W_XPROD && warp < W_ACC0) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_CTRL));
   }
   if (warp == W_XPROD) {
@@ -548,7 +614,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_arrive(&sm->n_full[it & 3]);
     }
   } else if (warp < W_XPROD) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_FIN));
+    if (!TB_ACC_WARPS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_FIN));  // (768 threads launch at 80)
     // ===================== finish: merge the two epilogue warps' results, certainty test, labels, re-check list,
     // accumulation of certain rows (16-byte vector reductions), cost, counts.  Thread == row.
     const int w4 = warp - W_FIN0;
@@ -657,51 +723,13 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       const float my_sc = H16 ? xn : fmaxf(xn + b1, 0.f);
       const int64_t r0 = tile * TM + w4 * 32;
       if (H16) {
-        // Rows travel L2 -> shared memory -> L2 reduction entirely on the copy engine (bulk copy, then bulk
-        // reduce-add into the replica row of the label): no registers, no load latency in this warp, two batches in
-        // flight.  At 8 rows in flight through registers this loop set the pace of the whole kernel (hand-off trace).
-        const uint32_t rowbytes = (uint32_t)d * 4u;
-        uint8_t* mybuf = fxbuf + (size_t)w4 * 2 * TB_FX_ROWS * rowbytes;
-        const int u = lane & (TB_FX_ROWS - 1);
-        int lbl_b[32 / TB_FX_ROWS];
-#pragma unroll
-        for (int b = 0; b < 32 / TB_FX_ROWS; ++b) lbl_b[b] = __shfl_sync(0xffffffffu, my_lab, b * TB_FX_ROWS + u);
-        auto issue_load = [&](int b, bool newest_may_pend) {
-          const uint32_t slot = (fxc + b) & 1u;
-          const bool merged = ld == d;  // the batch's rows are one contiguous block: one copy instead of eight
-          const int64_t rb = r0 + b * TB_FX_ROWS;
-          const int nlive = (int)max((int64_t)0, min((int64_t)TB_FX_ROWS, n - rb));
-          const bool act = lane < TB_FX_ROWS && lbl_b[b] >= 0;
-          const unsigned m = __ballot_sync(0xffffffffu, act);
-          // the reduction that read this slot two batches ago must be done with it
-          if (newest_may_pend) bulk_wait_read<1>();
-          else bulk_wait_read<0>();
-          if (lane == 0) {
-            const uint32_t bytes = merged ? (m ? (uint32_t)nlive * rowbytes : 0u) : (uint32_t)__popc(m) * rowbytes;
-            if (bytes) mbar_expect_tx(&sm->fx_full[w4][slot], bytes);
-            else mbar_arrive(&sm->fx_full[w4][slot]);
-            if (merged && bytes)
-              bulk_load_hint(mybuf + (size_t)slot * TB_FX_ROWS * rowbytes, X + rb * ld, bytes, &sm->fx_full[w4][slot],
-                             L2_EVICT_FIRST);
-          }
-          __syncwarp();
-          if (act && !merged)
-            bulk_load_hint(mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes,
-                           X + (r0 + b * TB_FX_ROWS + lane) * ld, rowbytes, &sm->fx_full[w4][slot], L2_EVICT_FIRST);
-        };
-        issue_load(0, true);
-        issue_load(1, false);
-#pragma unroll
-        for (int b = 0; b < 32 / TB_FX_ROWS; ++b) {
-          const uint32_t slot = (fxc + b) & 1u;
-          mbar_wait_ns(&sm->fx_full[w4][slot], ((fxc + b) >> 1) & 1u, 64);
-          if (lane < TB_FX_ROWS && lbl_b[b] >= 0)
-            bulk_reduce_add_f32(myrep + (size_t)lbl_b[b] * d, mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes,
-                                rowbytes);
-          bulk_commit();
-          if (b + 2 < 32 / TB_FX_ROWS) issue_load(b + 2, false);
+        if (TB_ACC_WARPS) {  // hand the labels to the accumulate warps (they take rows 16-31 of every quarter)
+          mbar_wait_ns(&sm->l_empty[ab], ((it >> 1) & 1) ^ 1, 64);
+          sm->lab[ab][row_in_tile] = my_lab;
+          mbar_arrive(&sm->l_full[ab]);
         }
-        fxc += 32 / TB_FX_ROWS;
+        tb_bulk_accumulate(X, n, ld, d, r0, (lane < TB_FX_SPAN) ? my_lab : -1, myrep,
+                           fxbuf + (size_t)w4 * 2 * TB_FX_ROWS * d * 4, sm->fx_full[w4], fxc, lane);
       }
       // TB_FIN_ROWS rows in flight per warp: the re-reads come from L2 (~800 cycles each way under load) and this
       // loop, not the epilogue, set the pace of the whole kernel at 8 rows in flight (hand-off trace)
@@ -741,6 +769,27 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
     }
   }
+#if TB_ACC_WARPS
+  else if (warp >= W_ACC0) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_ACC));
+    // ===================== accumulate (fp16 filter): rows 16-31 of every lane quarter, labels from the finish warps
+    if (H16 && accumulate) {
+      const int w4 = warp - W_ACC0;
+      float* myrep = rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d;
+      uint8_t* mybuf = fxbuf + (size_t)(4 + w4) * 2 * TB_FX_ROWS * d * 4;
+      uint32_t it = 0, fxc = 0;
+      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const uint32_t ab = it & 1;
+        mbar_wait_ns(&sm->l_full[ab], (it >> 1) & 1, 128);
+        const int lbl = (lane < TB_FX_SPAN) ? sm->lab[ab][w4 * 32 + TB_FX_SPAN + lane] : -1;
+        mbar_arrive(&sm->l_empty[ab]);
+        tb_bulk_accumulate(X, n, ld, d, tile * TM + w4 * 32 + TB_FX_SPAN, lbl, myrep, mybuf, sm->fx_full[4 + w4], fxc,
+                           lane);
+      }
+      bulk_wait_all();
+    }
+  }
+#endif
   tc_fence_before();
   __syncthreads();
   if (warp == W_ALLOC) {
@@ -929,7 +978,7 @@ static int km_tcb_stages(int d, int filter) {
   if (getenv("B2F_TC_STAGES")) cap = atoi(getenv("B2F_TC_STAGES"));
 #endif
   const int left = budget_kb * 1024 - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES -
-                   (filter == KM_FILTER_FP16 ? TB_CN_BYTES + 4 * 2 * TB_FX_ROWS * d * 4 : 0);
+                   (filter == KM_FILTER_FP16 ? TB_CN_BYTES + TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4 : 0);
   // a stage holds one centre tile: two 64-k atoms (space for two even when d == 64), fp16: + the ||c||^2 block
   int s = left / (filter == KM_FILTER_FP16 ? 2 * CHUNK_BYTES + TB_CN_BYTES : 2 * tb_stage_bytes<KM_FILTER_BF16X3>());
   return s > cap ? cap : s;
@@ -1071,7 +1120,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
 #endif
   const size_t tile_bytes = h16 ? 2 * (size_t)CHUNK_BYTES + TB_CN_BYTES : 2 * (size_t)tb_stage_bytes<KM_FILTER_BF16X3>();
   const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * tile_bytes +
-                      (h16 ? TB_CN_BYTES + 4 * 2 * TB_FX_ROWS * (size_t)d * 4 : 0) + sizeof(SmemB) + 64;
+                      (h16 ? TB_CN_BYTES + TB_FX_WARPS * 2 * TB_FX_ROWS * (size_t)d * 4 : 0) + sizeof(SmemB) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
