@@ -140,7 +140,8 @@ struct SmemB {
   int p_i1[2][2][TM];                    // index of the best
   int p_b3[2][2][TM];                    // fp16 filter: lower bound of the third best key; index of the second best
   int p_i2[2][2][TM];
-  float cscale[TM];                      // scaled pass: per-column factor (StandardScaler fold), d <= 128 entries
+  alignas(16) float cscale[TM];          // scaled pass: per-column factor (StandardScaler fold), d <= 128 entries
+                                         // (read as float4: the 4-byte tmem_base above breaks the natural alignment)
 };
 
 struct TcbWs {  // header of the caller-provided workspace (the first four ints are documented in b200fit.h)

@@ -161,7 +161,10 @@ def test_tcb_uncertain_rows_are_rechecked_and_overflow_is_visible(filt):
     n, d, k = 20000, 128, 128
     Xh = synth.mixture(n, 0, d, SEED, 4, 2.0)
     C = synth.mixture_centers(d, SEED, k, 2.0).astype(np.float64)
-    C[5] = C[0] + 1e-3  # near-duplicate of component 0's centre
+    # near-duplicate of component 0's centre.  (Index 6, not 5: the fp16 filter's epilogue folds columns {0, 1} mod 4
+    # and {2, 3} mod 4 of a centre tile in separate chains and can only bound the THIRD best score -- the condition
+    # for its pair check -- when the two best sit in different chains; same-chain pairs go to the 3xTF32 re-check.)
+    C[6] = C[0] + 1e-3
     X, _, ld = G.upload_matrix(Xh)
     info = {}
     big = int(N.lib().b2f_kmeans_ws_bytes(16 * n, k, d))  # room for every row on the re-check list
