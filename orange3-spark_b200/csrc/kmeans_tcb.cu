@@ -92,10 +92,12 @@ constexpr int TB_CN_BYTES = 128 * 32;  // the ||c||^2 k-block of a centre tile: 
 #ifndef TB_REG_CTRL
 // what the epilogue warpgroups gain, (EPI - 96) * 256, must be given back first by the others:
 // (96 - CTRL) * 128 + (96 - FIN) * 128  (the pool is per CTA)
-#define TB_REG_CTRL 48
-#define TB_REG_FIN 80
+// (640 threads launch at 96 registers: 8192 to find, CTRL 48 + FIN 80 give exactly that.  768 threads launch at 80:
+// 12288 to find -- the pool is what the CTA was launched with, not the SM's file -- CTRL 40 + ACC 32 + FIN 72.)
+#define TB_REG_CTRL (TB_ACC_WARPS ? 40 : 48)
+#define TB_REG_FIN (TB_ACC_WARPS ? 72 : 80)
 #define TB_REG_EPI 128
-#define TB_REG_ACC 40
+#define TB_REG_ACC 32
 #define TB_FIN_ROWS 8
 #define TB_FX_ROWS (TB_ACC_WARPS ? 4 : 8)
 #endif
@@ -615,7 +617,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_arrive(&sm->n_full[it & 3]);
     }
   } else if (warp < W_XPROD) {
-    if (!TB_ACC_WARPS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_FIN));  // (768 threads launch at 80)
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_FIN));
     // ===================== finish: merge the two epilogue warps' results, certainty test, labels, re-check list,
     // accumulation of certain rows (16-byte vector reductions), cost, counts.  Thread == row.
     const int w4 = warp - W_FIN0;

@@ -47,6 +47,14 @@ constexpr int LT_SPLIT_THREADS = 256;
 #ifndef LT_PCAT
 #define LT_PCAT 1        // GEMM2 reads x1 once against [p1 | p2] (N = 64) instead of twice (N = 32 each)
 #endif
+// G^T is moved out of tensor memory into the CTA's fp64 partial every LT_FLUSH row tiles.  Measured at 20M x 512
+// (135 000 rows per CTA in one fp32 accumulator): 2.7e-4 of the largest gradient entry, i.e. eps/4 per accumulating
+// MMA relative to the running sum -- the tensor core TRUNCATES when it adds into the accumulator, so the error is a
+// bias that grows with the number of accumulations, not a random walk.  16 accumulations per tile and block:
+// LT_FLUSH = 8 keeps the bias near 2e-6.
+#ifndef LT_FLUSH
+#define LT_FLUSH 8
+#endif
 constexpr int LT_NP = 32;          // classes padded to the MMA N
 constexpr int LT_XS = 6;           // X staging slots (16 KB each); must stay a multiple of the number of split groups (2):
                                    // a slot is then always consumed by the same group and its parity waits cannot alias
@@ -79,6 +87,7 @@ struct SmemL {
   uint64_t py_full[2], py_empty[2];
   uint64_t a2_full, a2_empty;
   uint64_t g_done;
+  uint64_t g_part;   // the GEMM2 blocks of a tile that ends a flush period have completed
   uint32_t tmem_base;
   float icpt[LT_NP];
   double red[4][LT_NP + 2];
@@ -192,6 +201,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     mbar_init(&sm->a2_full, LT_SPLIT_THREADS);
     mbar_init(&sm->a2_empty, 1);
     mbar_init(&sm->g_done, 1);
+    mbar_init(&sm->g_part, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (threadIdx.x < LT_NP) sm->icpt[threadIdx.x] = (threadIdx.x < K) ? (float)icpt[threadIdx.x] : 0.f;
@@ -316,16 +326,19 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
             // x1 . [p1 | p2] and x2 . [p1 | p2]: all four products of the two-piece split.  (Until round 2 the
             // second one was x2 . p1 only: the dropped x2 . p2 term, 2^-18 |x||p| per product, and a TRUNCATED
             // x2 put the gradient at ~2e-5 of its largest entry; the N = 64 form costs tensor time only.)
-            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, IDESC_G2_N64, (t | s) ? 1u : 0u);
+            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, IDESC_G2_N64, ((t % LT_FLUSH) | s) ? 1u : 0u);
             mma_bf16_ss(dg, ax2 + aoff, bp1 + boff, IDESC_G2_N64, 1u);
           } else {
-            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, IDESC_G2, (t | s) ? 1u : 0u);
+            mma_bf16_ss(dg, ax1 + aoff, bp1 + boff, IDESC_G2, ((t % LT_FLUSH) | s) ? 1u : 0u);
             mma_bf16_ss(dg, ax1 + aoff, bp2 + boff, IDESC_G2, 1u);
             mma_bf16_ss(dg, ax2 + aoff, bp1 + boff, IDESC_G2, 1u);
           }
         }
         tc_commit(&sm->a2_empty);
         if (fb == FB - 1) tc_commit(&sm->py_empty[buf]);
+        // end of a flush period: the softmax warps move G^T out before this warp restarts the accumulators (they do
+        // so ahead of arriving on py_full of the next tile, which the first GEMM2 block of that tile waits for)
+        if (fb == FB - 1 && (t + 1) % LT_FLUSH == 0 && t + 1 < my_tiles) tc_commit(&sm->g_part);
       }
       __syncwarp();
       ++g2;
@@ -344,8 +357,38 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     float gb[LT_NP];
 #pragma unroll
     for (int k = 0; k < LT_NP; ++k) gb[k] = 0.f;
+    const int plen = K * d + K + 2;
+    double* part = partials + (size_t)blockIdx.x * plen;
+    // this thread owns gradient entries (class k, feature fb * 128 + r) of the CTA's fp64 partial: zero them, add
+    // G^T in at every flush and once more at the end
+    for (int fb = 0; fb < FB; ++fb)
+      for (int k = 0; k < K; ++k) part[(size_t)k * d + fb * 128 + r] = 0.0;
+    auto flush_g = [&]() {
+      for (int fb = 0; fb < FB; ++fb) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + lane_addr + LT_G + fb * LT_GW, v);
+        tmem_ld_wait();
+        const int f = fb * 128 + r;  // lane == feature
+        if (LT_PCAT) {
+          uint32_t v2[32];
+          tmem_ld32(tmem_base + lane_addr + LT_G + fb * LT_GW + 32, v2);
+          tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < LT_NP; ++k) v[k] = __float_as_uint(__uint_as_float(v[k]) + __uint_as_float(v2[k]));
+        }
+#pragma unroll
+        for (int k = 0; k < LT_NP; ++k)
+          if (k < K) part[(size_t)k * d + f] += (double)__uint_as_float(v[k]);
+      }
+    };
     for (int t = 0; t < my_tiles; ++t) {
       const int buf = t & 1;
+      if (t > 0 && t % LT_FLUSH == 0) {
+        mbar_wait(&sm->g_part, (uint32_t)(t / LT_FLUSH - 1) & 1u);
+        tc_fence_after();
+        flush_g();
+        tc_fence_before();
+      }
       const int64_t row = (blockIdx.x + (int64_t)t * gridDim.x) * TM + r;
       const bool live = row < n;
       const float wi = live ? (w ? w[row] : 1.f) : 0.f;
@@ -415,24 +458,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     }
     mbar_wait(&sm->g_done, 0);
     tc_fence_after();
-    const int plen = K * d + K + 2;
-    double* part = partials + (size_t)blockIdx.x * plen;
-    for (int fb = 0; fb < FB; ++fb) {
-      uint32_t v[32];
-      tmem_ld32(tmem_base + lane_addr + LT_G + fb * LT_GW, v);
-      tmem_ld_wait();
-      const int f = fb * 128 + r;  // lane == feature
-      if (LT_PCAT) {
-        uint32_t v2[32];
-        tmem_ld32(tmem_base + lane_addr + LT_G + fb * LT_GW + 32, v2);
-        tmem_ld_wait();
-#pragma unroll
-        for (int k = 0; k < LT_NP; ++k) v[k] = __float_as_uint(__uint_as_float(v[k]) + __uint_as_float(v2[k]));
-      }
-#pragma unroll
-      for (int k = 0; k < LT_NP; ++k)
-        if (k < K) part[(size_t)k * d + f] = (my_tiles > 0) ? (double)__uint_as_float(v[k]) : 0.0;
-    }
+    if (my_tiles > 0) flush_g();
     asm volatile("bar.sync 1, 128;" ::: "memory");
     if (r < K + 2) {
       const int src = (r < K) ? r : LT_NP + (r - K);

@@ -16,12 +16,78 @@ __device__ __forceinline__ float load_as_f32(const void* p, int dtype, int64_t i
   }
 }
 
+// Fast path of the loader for fp32 columns (what the Dataset Builder hands over after its casts, and what the BASELINE
+// configs hold): tile = 128 rows x 32 columns.  A lane reads FOUR consecutive rows of one column with one 16-byte
+// load (512 B per warp instruction instead of 128 B: the scalar version ran at 0.45 of the HBM peak), the tile is
+// transposed through padded shared memory and leaves as whole 128-byte row segments.
+#define PK4_ROWS 128
+__device__ __forceinline__ void pack_columns_f32_body(float (*tile)[PK_COLS + 1], const void* const* __restrict__ cols,
+                                                      int d, int64_t n, float* __restrict__ X, int64_t ld,
+                                                      int32_t* bad_flag) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t row_tiles = (n + PK4_ROWS - 1) / PK4_ROWS;
+  const int col_tiles = (int)((ld + PK_COLS - 1) / PK_COLS);
+  const int64_t tiles = row_tiles * col_tiles;
+  bool bad = false;
+  for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const int64_t r0 = (t / col_tiles) * PK4_ROWS;
+    const int c0 = (int)(t % col_tiles) * PK_COLS;
+    float4 v[PK_COLS / 8];
+#pragma unroll
+    for (int cc = 0; cc < PK_COLS / 8; ++cc) {  // all four loads of this thread in flight before the first store
+      const int c = c0 + warp + cc * 8;
+      const int64_t r = r0 + lane * 4;
+      v[cc] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (c < d) {
+        const float* p = static_cast<const float*>(cols[c]);
+        if (r + 3 < n) {
+          v[cc] = ldg_stream(reinterpret_cast<const float4*>(p + r));
+        } else {
+          if (r < n) v[cc].x = __ldg(p + r);
+          if (r + 1 < n) v[cc].y = __ldg(p + r + 1);
+          if (r + 2 < n) v[cc].z = __ldg(p + r + 2);
+        }
+      }
+    }
+#pragma unroll
+    for (int cc = 0; cc < PK_COLS / 8; ++cc) {
+      const int cl = warp + cc * 8;
+      bad |= isnan(v[cc].x) | isnan(v[cc].y) | isnan(v[cc].z) | isnan(v[cc].w);
+      tile[lane * 4 + 0][cl] = v[cc].x;
+      tile[lane * 4 + 1][cl] = v[cc].y;
+      tile[lane * 4 + 2][cl] = v[cc].z;
+      tile[lane * 4 + 3][cl] = v[cc].w;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int rr = 0; rr < PK4_ROWS / 32; ++rr) {
+      const int rl = (threadIdx.x >> 3) + rr * 32;
+      const int c4 = (threadIdx.x & 7) * 4;
+      const int64_t r = r0 + rl;
+      if (r < n && c0 + c4 < ld) {
+        float4 o = make_float4(tile[rl][c4], tile[rl][c4 + 1], tile[rl][c4 + 2], tile[rl][c4 + 3]);
+        *reinterpret_cast<float4*>(X + r * ld + c0 + c4) = o;
+      }
+    }
+    __syncthreads();
+  }
+  if (bad_flag && bad) atomicExch(bad_flag, 1);
+}
+
 // CTA = 256 threads, tile = 64 rows x 32 columns.  Reads run along N inside each column (coalesced),
 // the tile is transposed through padded shared memory, and rows leave as 16-byte stores.
 __global__ void __launch_bounds__(256) pack_columns_kernel(const void* const* __restrict__ cols,
                                                            const int32_t* __restrict__ dtypes, int d, int64_t n,
                                                            float* __restrict__ X, int64_t ld, int32_t* bad_flag) {
-  __shared__ float tile[PK_ROWS][PK_COLS + 1];
+  __shared__ float tile[PK4_ROWS][PK_COLS + 1];
+  // all columns fp32 and 16-byte aligned -> the 16-byte-load path (decided per CTA, the same everywhere)
+  int ok = 1;
+  for (int c = threadIdx.x; c < d; c += 256)
+    ok &= (dtypes[c] == B2F_F32) && ((reinterpret_cast<uintptr_t>(cols[c]) & 15) == 0);
+  if (__syncthreads_and(ok)) {
+    pack_columns_f32_body(tile, cols, d, n, X, ld, bad_flag);
+    return;
+  }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t row_tiles = (n + PK_ROWS - 1) / PK_ROWS;
   const int col_tiles = (int)((ld + PK_COLS - 1) / PK_COLS);
@@ -185,7 +251,7 @@ extern "C" int b2f_pack_columns(const void* const* col_ptrs_dev, const int32_t* 
   if (n == 0) return B2F_OK;
   B2F_REQUIRE(col_ptrs_dev && col_dtypes_dev && X, "b2f_pack_columns: null pointer");
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_pack_columns: X must be 16-byte aligned");
-  int64_t tiles = ((n + PK_ROWS - 1) / PK_ROWS) * ((ld + PK_COLS - 1) / PK_COLS);
+  int64_t tiles = ((n + PK4_ROWS - 1) / PK4_ROWS) * ((ld + PK_COLS - 1) / PK_COLS);  // (fast path: 128-row tiles)
   int64_t cap = (int64_t)b2f_sm_count() * 8;
   int grid = (int)(tiles < cap ? tiles : cap);
   pack_columns_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(col_ptrs_dev, col_dtypes_dev, d, n, X, ld, bad_flag);
