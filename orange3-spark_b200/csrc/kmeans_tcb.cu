@@ -235,11 +235,12 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
                   const float* __restrict__ misc, float kappa2, float kappa0, int k, int nstages,
                   double* __restrict__ payload, float* __restrict__ rep, unsigned long long* __restrict__ cnt,
                   int32_t* __restrict__ labels, int accumulate, TcbWs* __restrict__ ws,
-                  int32_t* __restrict__ amb_idx, int cap, int4* __restrict__ pairs, int pcap,
+                  int32_t* __restrict__ amb_idx, int cap, int4* __restrict__ pairs, int pcap, int table_mode,
                   unsigned long long* __restrict__ trace) {
   constexpr int TB_STAGE_BYTES = tb_stage_bytes<MODE>();  // per 64-k atom
   constexpr bool H16 = MODE == KM_FILTER_FP16;
-  constexpr int TB_TILE_BYTES = 2 * TB_STAGE_BYTES + (H16 ? TB_CN_BYTES : 0);  // a stage: two atoms (+ ||c||^2 block)
+  // a stage holds one centre tile: KA atoms (+ the ||c||^2 block)
+  const int TB_TILE_BYTES = (d / 64) * TB_STAGE_BYTES + (H16 ? TB_CN_BYTES : 0);
   constexpr uint32_t XBUFS = 2;  // row-tile buffers of the TMEM operand
   constexpr uint32_t TB_A1 = H16 ? TB_A1_H : TB_A1_BF, TB_A2 = TB_A2_BF;
   constexpr uint32_t NBUF = H16 ? 3 : 2;  // accumulator buffers in tensor memory
@@ -253,7 +254,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   uint8_t* aconst = stages + (size_t)nstages * TB_TILE_BYTES;
   // fp16: row buffers of the finish warps: 4 warps x 2 slots x TB_FX_ROWS rows of d floats
   uint8_t* fxbuf = aconst + (H16 ? TB_CN_BYTES : 0);
-  SmemB* sm = reinterpret_cast<SmemB*>(fxbuf + (H16 ? TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4 : 0));
+  // (table mode, small k * d: the row tile re-read from L2, TM x d floats, then a [k, d] fp32 accumulation table)
+  SmemB* sm = reinterpret_cast<SmemB*>(fxbuf + (!H16 ? 0 : table_mode ? (TM + k) * d * 4 : TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t ntiles = (n + TM - 1) / TM;
@@ -345,7 +347,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             if (!H16) tma_load_2d(dst + CHUNK_BYTES, &map_c2, a * 64, nt * TN, &sm->b_full[s]);
           }
           // fp16: map_c2 is the ||c||^2 plane (16 halves per centre, three of them non-zero; 32-byte swizzle)
-          if (H16) tma_load_2d(stages + (size_t)s * TB_TILE_BYTES + 2 * TB_STAGE_BYTES, &map_c2, 0, nt * TN, &sm->b_full[s]);
+          if (H16) tma_load_2d(stages + (size_t)s * TB_TILE_BYTES + KA * TB_STAGE_BYTES, &map_c2, 0, nt * TN, &sm->b_full[s]);
           if (++s == (uint32_t)nstages) {
             s = 0;
             ph ^= 1;
@@ -425,7 +427,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           // (operands of this one: 128 x 16 halves, 32-byte swizzle, 8-row groups 256 B apart)
           if (H16)
             tc_mma_f16_ss(tmem_d, desc_sw32 | (uint64_t)(smem_u32(aconst) >> 4),
-                          desc_sw32 | (uint64_t)(st_a + cstage * ((uint32_t)TB_TILE_BYTES >> 4) + 2 * stage16), IDESC_FP16, 1u);
+                          desc_sw32 | (uint64_t)(st_a + cstage * ((uint32_t)TB_TILE_BYTES >> 4) + KA * stage16), IDESC_FP16, 1u);
           mbar_arrive(&sm->tok[mp]);  // batch is in the queue: the other warp may issue the next tile
           tc_commit(&sm->b_empty[cstage]);
           if (nt == NT - 1) tc_commit(&sm->xa_empty[xb]);
@@ -731,8 +733,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           sm->lab[ab][row_in_tile] = my_lab;
           mbar_arrive(&sm->l_full[ab]);
         }
-        tb_bulk_accumulate(X, n, ld, d, r0, (lane < TB_FX_SPAN) ? my_lab : -1, myrep,
-                           fxbuf + (size_t)w4 * 2 * TB_FX_ROWS * d * 4, sm->fx_full[w4], fxc, lane);
+        if (!table_mode)
+          tb_bulk_accumulate(X, n, ld, d, r0, (lane < TB_FX_SPAN) ? my_lab : -1, myrep,
+                             fxbuf + (size_t)w4 * 2 * TB_FX_ROWS * d * 4, sm->fx_full[w4], fxc, lane);
       }
       // TB_FIN_ROWS rows in flight per warp: the re-reads come from L2 (~800 cycles each way under load) and this
       // loop, not the epilogue, set the pace of the whole kernel at 8 rows in flight (hand-off trace)
@@ -760,7 +763,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
       if (w4 == 0) TR(10, 3);
     }
-    if (H16) bulk_wait_all();  // the reductions read this CTA's shared memory
+    if (H16 && !table_mode) bulk_wait_all();  // the reductions read this CTA's shared memory
     if (accumulate) {
       cost = warp_sum(cost);
       unsigned long long tot = nrows;
@@ -776,7 +779,66 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   else if (warp >= W_ACC0) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_ACC));
     // ===================== accumulate (fp16 filter): rows 16-31 of every lane quarter, labels from the finish warps
-    if (H16 && accumulate) {
+    if (H16 && accumulate && table_mode) {
+      // ---- small k * d (cfg 5: k = 256, d = 64): a [k, d] fp32 table in shared memory takes every certain row of
+      // this CTA; nothing goes to L2 until the end.  Warp w owns columns [16 w, 16 w + 16) of the table for ALL rows
+      // (so no two warps touch the same entry), lane = (row parity, column): plain read-add-write, two rows per step;
+      // the rare step whose two rows share a label is done in two halves.  The row tile comes back from L2 with one
+      // bulk copy issued a whole tile ahead of its labels.
+      const int w4 = warp - W_ACC0, tid = threadIdx.x - W_ACC0 * 32;
+      float* rf = reinterpret_cast<float*>(fxbuf);
+      float* table = rf + (size_t)TM * d;
+      for (int i = tid; i < k * d / 4; i += 128) reinterpret_cast<float4*>(table)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      asm volatile("bar.sync 3, 128;" ::: "memory");
+      const int h = lane >> 4, col = w4 * 16 + (lane & 15);
+      const uint32_t rowbytes = (uint32_t)d * 4u;
+      uint64_t* rf_full = &sm->fx_full[0][0];
+      uint32_t it = 0;
+      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const uint32_t ab = it & 1;
+        const int nrows = (int)min((int64_t)TM, n - tile * TM);
+        if (tid == 0) mbar_expect_tx(rf_full, (uint32_t)nrows * rowbytes);
+        if (ld == d) {
+          if (tid == 0) bulk_load_hint(rf, X + tile * TM * ld, (uint32_t)nrows * rowbytes, rf_full, L2_EVICT_FIRST);
+        } else if (tid < nrows) {
+          bulk_load_hint(rf + (size_t)tid * d, X + (tile * TM + tid) * ld, rowbytes, rf_full, L2_EVICT_FIRST);
+        }
+        mbar_wait_ns(&sm->l_full[ab], (it >> 1) & 1, 128);
+        mbar_wait_ns(rf_full, it & 1, 64);
+#pragma unroll 2
+        for (int R = 0; R < TM; R += 8) {
+          int lb[4];
+          float xv[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int row = R + 2 * q + h;
+            lb[q] = sm->lab[ab][row];
+            xv[q] = rf[(size_t)row * d + col];
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int other = __shfl_xor_sync(0xffffffffu, lb[q], 16);
+            float* t = table + (size_t)max(lb[q], 0) * d + col;
+            if (other != lb[q]) {  // warp-uniform: the step's two rows have different labels
+              if (lb[q] >= 0) *t += xv[q];
+            } else {
+              if (h == 0 && lb[q] >= 0) *t += xv[q];
+              __syncwarp();
+              if (h == 1 && lb[q] >= 0) *t += xv[q];
+            }
+            __syncwarp();
+          }
+        }
+        asm volatile("bar.sync 3, 128;" ::: "memory");  // every warp is done with this tile's labels and rows
+        mbar_arrive(&sm->l_empty[ab]);
+      }
+      asm volatile("bar.sync 3, 128;" ::: "memory");
+      float* myrep = rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d;
+      for (int i = tid; i < k * d / 4; i += 128) {
+        const float4 v = reinterpret_cast<const float4*>(table)[i];
+        if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) red_add_v4(myrep + (size_t)i * 4, v);
+      }
+    } else if (H16 && accumulate) {
       const int w4 = warp - W_ACC0;
       float* myrep = rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d;
       uint8_t* mybuf = fxbuf + (size_t)(4 + w4) * 2 * TB_FX_ROWS * d * 4;
@@ -974,16 +1036,28 @@ static int tcb_cap_from_bytes(size_t bytes, int d) {
   return (int)c;
 }
 
-static int km_tcb_stages(int d, int filter) {
+static int tcb_tile_bytes(int d, int filter) {
+  return filter == KM_FILTER_FP16 ? (d / 64) * CHUNK_BYTES + TB_CN_BYTES : (d / 64) * tb_stage_bytes<KM_FILTER_BF16X3>();
+}
+// shared memory behind the centre-operand stages that the accumulation needs (fp16 filter): row slots of the
+// accumulating warps, or -- table mode -- the re-read row tile and the [k, d] table
+static bool tcb_table_mode(int k, int d, bool h16, bool accumulate) {
+  return TB_ACC_WARPS && h16 && accumulate && d == 64 && (size_t)k * d * 4 <= 65536;
+}
+static int tcb_fx_bytes(int k, int d, bool table) {
+  return table ? (TM + k) * d * 4 : TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4;
+}
+
+static int km_tcb_stages(int d, int filter, int fx_bytes) {
   int budget_kb = 227, cap = 4;
 #ifdef B2F_DEV  // dev knobs of the timing experiments; not in the product build
   if (filter == KM_FILTER_FP16 && getenv("B2F_TC_SMEM_KB")) budget_kb = atoi(getenv("B2F_TC_SMEM_KB"));
   if (getenv("B2F_TC_STAGES")) cap = atoi(getenv("B2F_TC_STAGES"));
 #endif
   const int left = budget_kb * 1024 - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES -
-                   (filter == KM_FILTER_FP16 ? TB_CN_BYTES + TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4 : 0);
-  // a stage holds one centre tile: two 64-k atoms (space for two even when d == 64), fp16: + the ||c||^2 block
-  int s = left / (filter == KM_FILTER_FP16 ? 2 * CHUNK_BYTES + TB_CN_BYTES : 2 * tb_stage_bytes<KM_FILTER_BF16X3>());
+                   (filter == KM_FILTER_FP16 ? TB_CN_BYTES + fx_bytes : 0);
+  // a stage holds one centre tile: d / 64 atoms, fp16: + the ||c||^2 block
+  int s = left / tcb_tile_bytes(d, filter);
   return s > cap ? cap : s;
 }
 
@@ -991,7 +1065,8 @@ bool km_tcb_supported(int k, int d, int64_t ld) {
   if (d != 64 && d != 128) return false;  // whole 64-k atoms, X hi/lo pairs fit the tensor memory budget
   if (k % TN != 0 || k < TN) return false;
   if (ld % 4 != 0) return false;
-  return km_tcb_stages(d, KM_FILTER_BF16X3) >= 2 && km_tcb_stages(d, KM_FILTER_FP16) >= 2 && km_tc_supported(k, d, ld);
+  return km_tcb_stages(d, KM_FILTER_BF16X3, 0) >= 2 &&
+         km_tcb_stages(d, KM_FILTER_FP16, tcb_fx_bytes(k, d, tcb_table_mode(k, d, true, true))) >= 2 && km_tc_supported(k, d, ld);
 }
 
 size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
@@ -1004,7 +1079,7 @@ static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const C
                              const CUtensorMap& m2, const float* X, int64_t n, int d, int64_t ld, const float* colscale,
                              const float* cn, const float* misc, float kappa2, float kappa0, int k, int nstages,
                              double* payload, float* rep, unsigned long long* cnt, int32_t* labels, int accumulate,
-                             TcbWs* hdr, int32_t* amb_idx, int cap, int4* pairs, int pcap) {
+                             TcbWs* hdr, int32_t* amb_idx, int cap, int4* pairs, int pcap, int table_mode) {
   unsigned long long* trace = nullptr;
 #ifdef B2F_DEV  // hand-off tracer of the timing experiments (allocates; not in the product build)
   const char* trace_path = getenv("B2F_TC_TRACE");
@@ -1015,7 +1090,8 @@ static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const C
     auto kern = km_tcb_kernel<MODE, true, SCALED>;
     B2F_CUDA(b2f_smem_attr(kern, smem));
     kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
-                                             payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, trace);
+                                             payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, table_mode,
+                                             trace);
     B2F_LAUNCH_CHECK();
     std::vector<unsigned long long> host(trace_bytes / sizeof(unsigned long long));
     B2F_CUDA(cudaStreamSynchronize(stream));
@@ -1031,7 +1107,8 @@ static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const C
   auto kern = km_tcb_kernel<MODE, false, SCALED>;
   B2F_CUDA(b2f_smem_attr(kern, smem));
   kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
-                                           payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, trace);
+                                           payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, table_mode,
+                                           trace);
   B2F_LAUNCH_CHECK();
   return B2F_OK;
 }
@@ -1087,7 +1164,10 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
   int4* pairs = reinterpret_cast<int4*>(wp + W.off_pairs);
   float* Xamb = reinterpret_cast<float*>(wp + W.off_x);
   const bool h16 = filter == KM_FILTER_FP16;
-  const int nstages = km_tcb_stages(d, filter);
+  const bool table = tcb_table_mode(k, d, h16, accumulate);
+  const int fx_bytes = tcb_fx_bytes(k, d, table);
+  const int nstages = km_tcb_stages(d, filter, fx_bytes);
+  B2F_REQUIRE(nstages >= 2, "b2f_kmeans (filter path): k = %d, d = %d does not fit in shared memory", k, d);
   CUtensorMap mx, m1, m2;
   int rc;
   if ((rc = make_map_f32(&mx, X, (uint64_t)n, (uint64_t)d, (uint64_t)ld)) != B2F_OK) return rc;
@@ -1121,9 +1201,8 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
 #ifdef B2F_DEV
   if (getenv("B2F_TC_DBG") && (atoi(getenv("B2F_TC_DBG")) & 4)) acc_main = false;  // results invalid when set
 #endif
-  const size_t tile_bytes = h16 ? 2 * (size_t)CHUNK_BYTES + TB_CN_BYTES : 2 * (size_t)tb_stage_bytes<KM_FILTER_BF16X3>();
-  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * tile_bytes +
-                      (h16 ? TB_CN_BYTES + TB_FX_WARPS * 2 * TB_FX_ROWS * (size_t)d * 4 : 0) + sizeof(SmemB) + 64;
+  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * tcb_tile_bytes(d, filter) +
+                      (h16 ? TB_CN_BYTES + fx_bytes : 0) + sizeof(SmemB) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
@@ -1138,11 +1217,11 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
     if (colscale)
       rc = tcb_launch_filter<KM_FILTER_FP16, true>(grid, smem, stream, mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2,
                                                    kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
-                                                   amb_idx, cap, pairs, cap);
+                                                   amb_idx, cap, pairs, cap, table ? 1 : 0);
     else
       rc = tcb_launch_filter<KM_FILTER_FP16, false>(grid, smem, stream, mx, m1, m2, X, n, d, ld, nullptr, cn, misc, kappa2,
                                                     kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
-                                                    amb_idx, cap, pairs, cap);
+                                                    amb_idx, cap, pairs, cap, table ? 1 : 0);
     if (rc != B2F_OK) return rc;
     if (acc_main && colscale && (rc = km_fold_scaled(acc, k, d, colscale, stream)) != B2F_OK) return rc;
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, 1.0);
@@ -1153,7 +1232,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
   } else {
     rc = tcb_launch_filter<KM_FILTER_BF16X3, false>(grid, smem, stream, mx, m1, m2, X, n, d, ld, nullptr, cn, misc, kappa2,
                                                     kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
-                                                    amb_idx, cap, nullptr, 0);
+                                                    amb_idx, cap, nullptr, 0, 0);
     if (rc != B2F_OK) return rc;
   }
   tcb_gather_kernel<<<b2f_sm_count() * 4, 256, 0, stream>>>(X, ld, d, colscale, hdr, amb_idx, Xamb, cap);
