@@ -80,29 +80,21 @@ __device__ __forceinline__ float tb_row_scale(float xn, float cmax) {
   e = max(1, min(254, e));
   return __int_as_float(e << 23);
 }
-// TB_ACC_WARPS = 1 adds a sixth warpgroup (warps 20-23) that takes HALF of every row tile's accumulation off the
-// finish warps (which the hand-off trace shows pacing the kernel: ~2 400 cycles of merge / certainty / labels and
-// then ~8 000 of accumulation per row tile): the finish warps publish the labels in shared memory, keep rows 0-15 of
-// their 32 and the new warps do rows 16-31.  Row slots shrink to 4 rows so the eight warps fit the same 32 KB.
-#ifndef TB_ACC_WARPS
-#define TB_ACC_WARPS 0
-#endif
-constexpr int TB_THREADS = TB_ACC_WARPS ? 768 : 640;
+
+constexpr int TB_THREADS = 640;
 constexpr int TB_CN_BYTES = 128 * 32;  // the ||c||^2 k-block of a centre tile: 128 centres x 16 halves
 #ifndef TB_REG_CTRL
 // what the epilogue warpgroups gain, (EPI - 96) * 256, must be given back first by the others:
 // (96 - CTRL) * 128 + (96 - FIN) * 128  (the pool is per CTA)
-// (640 threads launch at 96 registers: 8192 to find, CTRL 48 + FIN 80 give exactly that.  768 threads launch at 80:
-// 12288 to find -- the pool is what the CTA was launched with, not the SM's file -- CTRL 40 + ACC 32 + FIN 72.)
-#define TB_REG_CTRL (TB_ACC_WARPS ? 40 : 48)
-#define TB_REG_FIN (TB_ACC_WARPS ? 72 : 80)
+// (the pool is what the CTA was LAUNCHED with -- 640 threads x 96 -- not the SM's register file)
+#define TB_REG_CTRL 48
+#define TB_REG_FIN 80
 #define TB_REG_EPI 128
-#define TB_REG_ACC 32
 #define TB_FIN_ROWS 8
-#define TB_FX_ROWS (TB_ACC_WARPS ? 4 : 8)
+#define TB_FX_ROWS 8
 #endif
-constexpr int TB_FX_WARPS = TB_ACC_WARPS ? 8 : 4;       // warps that own row slots
-constexpr int TB_FX_SPAN = TB_ACC_WARPS ? 16 : 32;      // rows of a tile each of them accumulates
+constexpr int TB_FX_WARPS = 4;    // warps that own row slots (the finish warps)
+constexpr int TB_FX_SPAN = 32;    // rows of a tile each of them accumulates
 // dev tracing (B2F_TC_TRACE=<file>): block 0 stamps clock64() at the hand-offs of its first TR_TILES row tiles
 [[maybe_unused]] constexpr int TR_TILES = 64, TR_SLOTS = 32, TR_ROLES = 12;  // mma | 8 epilogue warps | split | finish | B producer
 #define TR(role, slot)                                                                      \
@@ -123,7 +115,6 @@ constexpr int W_EPI0 = 0;    // warps 0-7   epilogue
 constexpr int W_SPLIT0 = 8;  // warps 8-11  split
 constexpr int W_FIN0 = 12;   // warps 12-15 finish
 constexpr int W_XPROD = 16, W_MMA = 17, W_BPROD = 18, W_ALLOC = 19;  // W_ALLOC: TMEM allocator + second MMA issuer
-constexpr int W_ACC0 = 20;   // warps 20-23 (TB_ACC_WARPS): second half of the accumulation
 
 struct SmemB {
   uint64_t xs_full[4], xs_empty[4];  // fp32 staging, per 32-float chunk
@@ -133,9 +124,7 @@ struct SmemB {
   uint64_t a_full[2], a_empty[2];    // epilogue -> finish hand-off
   uint64_t n_full[4], n_empty[4];    // split -> finish: squared row norms of a tile
   uint64_t tok[2];                   // MMA issue token: warp p has put its batch into the tensor queue
-  uint64_t fx_full[8][2];            // accumulating warps (fp16 filter): rows of a batch have landed in their slot
-  uint64_t l_full[2], l_empty[2];    // finish -> accumulate warps: labels of a row tile (TB_ACC_WARPS)
-  int lab[2][TM];
+  uint64_t fx_full[4][2];            // finish warps (fp16 filter): rows of a batch have landed in their slot
   uint32_t tmem_base;
   float xnorm2[4][TM];
   float p_b1[2][2][TM], p_b2[2][2][TM];  // [slot][epilogue warp of the lane quarter][row]: best, second best
@@ -176,22 +165,25 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, 
 
 }  // namespace
 
-// Accumulation of TB_FX_SPAN consecutive rows (first row r0; lane u < TB_FX_SPAN holds the label of row r0 + u, or -1
+// Accumulation of the 32 consecutive rows of a finish warp (first row r0; lane u holds the label of row r0 + u, or -1
 // for a row that is not to be added) into the replica table, entirely on the copy engine: bulk copy L2 -> shared
 // memory slot, then bulk reduce-add of each row into the replica row of its label.  No registers hold row data and no
 // load latency sits in this warp; two batches of TB_FX_ROWS rows are in flight (two slots, `fx_full` their barriers,
 // `fxc` the running batch count of this warp).  At 8 rows in flight through registers this loop set the pace of the
-// whole kernel (hand-off trace).
-__device__ __forceinline__ void tb_bulk_accumulate(const float* __restrict__ X, int64_t n, int64_t ld, int d, int64_t r0,
-                                                   int my_lab, float* __restrict__ myrep, uint8_t* mybuf,
-                                                   uint64_t* fx_full, uint32_t& fxc, int lane) {
-  constexpr int NB = TB_FX_SPAN / TB_FX_ROWS;
-  const uint32_t rowbytes = (uint32_t)d * 4u;
-  const int u = lane & (TB_FX_ROWS - 1);
+// whole kernel (hand-off trace).  Split in two so that the caller can put its list appends -- atomics whose return
+// value costs an L2 round trip -- between issuing the first two copies and waiting for them.
+struct TbAcc {
+  static constexpr int NB = TB_FX_SPAN / TB_FX_ROWS;
+  const float* X;
+  int64_t n, ld, r0;
+  int d, lane;
+  float* myrep;
+  uint8_t* mybuf;
+  uint64_t* fx_full;
   int lbl_b[NB];
-#pragma unroll
-  for (int b = 0; b < NB; ++b) lbl_b[b] = __shfl_sync(0xffffffffu, my_lab, b * TB_FX_ROWS + u);
-  auto issue_load = [&](int b, bool newest_may_pend) {
+
+  __device__ __forceinline__ void issue_load(uint32_t fxc, int b, bool newest_may_pend) {
+    const uint32_t rowbytes = (uint32_t)d * 4u;
     const uint32_t slot = (fxc + b) & 1u;
     const bool merged = ld == d;  // the batch's rows are one contiguous block: one copy instead of TB_FX_ROWS
     const int64_t rb = r0 + b * TB_FX_ROWS;
@@ -212,20 +204,29 @@ __device__ __forceinline__ void tb_bulk_accumulate(const float* __restrict__ X, 
     if (act && !merged)
       bulk_load_hint(mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes, X + (rb + lane) * ld, rowbytes,
                      &fx_full[slot], L2_EVICT_FIRST);
-  };
-  issue_load(0, true);
-  issue_load(1, false);
-#pragma unroll
-  for (int b = 0; b < NB; ++b) {
-    const uint32_t slot = (fxc + b) & 1u;
-    mbar_wait_ns(&fx_full[slot], ((fxc + b) >> 1) & 1u, 64);
-    if (lane < TB_FX_ROWS && lbl_b[b] >= 0)
-      bulk_reduce_add_f32(myrep + (size_t)lbl_b[b] * d, mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes, rowbytes);
-    bulk_commit();
-    if (b + 2 < NB) issue_load(b + 2, false);
   }
-  fxc += NB;
-}
+  // labels -> per-batch labels, copies of the first two batches on their way
+  __device__ __forceinline__ void begin(uint32_t fxc, int my_lab) {
+    const int u = lane & (TB_FX_ROWS - 1);
+#pragma unroll
+    for (int b = 0; b < NB; ++b) lbl_b[b] = __shfl_sync(0xffffffffu, my_lab, b * TB_FX_ROWS + u);
+    issue_load(fxc, 0, true);
+    issue_load(fxc, 1, false);
+  }
+  __device__ __forceinline__ void finish(uint32_t& fxc) {
+    const uint32_t rowbytes = (uint32_t)d * 4u;
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      const uint32_t slot = (fxc + b) & 1u;
+      mbar_wait_ns(&fx_full[slot], ((fxc + b) >> 1) & 1u, 64);
+      if (lane < TB_FX_ROWS && lbl_b[b] >= 0)
+        bulk_reduce_add_f32(myrep + (size_t)lbl_b[b] * d, mybuf + (size_t)(slot * TB_FX_ROWS + lane) * rowbytes, rowbytes);
+      bulk_commit();
+      if (b + 2 < NB) issue_load(fxc, b + 2, false);
+    }
+    fxc += NB;
+  }
+};
 
 template <int MODE, bool TRACE, bool SCALED>
 __global__ void __launch_bounds__(TB_THREADS, 1)
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
                   const float* __restrict__ misc, float kappa2, float kappa0, int k, int nstages,
                   double* __restrict__ payload, float* __restrict__ rep, unsigned long long* __restrict__ cnt,
                   int32_t* __restrict__ labels, int accumulate, TcbWs* __restrict__ ws,
-                  int32_t* __restrict__ amb_idx, int cap, int4* __restrict__ pairs, int pcap, int table_mode,
+                  int32_t* __restrict__ amb_idx, int cap, int4* __restrict__ pairs, int pcap,
                   unsigned long long* __restrict__ trace) {
   constexpr int TB_STAGE_BYTES = tb_stage_bytes<MODE>();  // per 64-k atom
   constexpr bool H16 = MODE == KM_FILTER_FP16;
@@ -254,8 +255,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   uint8_t* aconst = stages + (size_t)nstages * TB_TILE_BYTES;
   // fp16: row buffers of the finish warps: 4 warps x 2 slots x TB_FX_ROWS rows of d floats
   uint8_t* fxbuf = aconst + (H16 ? TB_CN_BYTES : 0);
-  // (table mode, small k * d: the row tile re-read from L2, TM x d floats, then a [k, d] fp32 accumulation table)
-  SmemB* sm = reinterpret_cast<SmemB*>(fxbuf + (!H16 ? 0 : table_mode ? (TM + k) * d * 4 : TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4));
+  SmemB* sm = reinterpret_cast<SmemB*>(fxbuf + (H16 ? TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4 : 0));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t ntiles = (n + TM - 1) / TM;
@@ -274,15 +274,13 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_init(&sm->t_full[c], 1);
       mbar_init(&sm->t_empty[c], EPI_THREADS);
     }
-    for (int c = 0; c < 16; ++c) mbar_init(&sm->fx_full[c >> 1][c & 1], 1);
+    for (int c = 0; c < 8; ++c) mbar_init(&sm->fx_full[c >> 1][c & 1], 1);
     for (int c = 0; c < 2; ++c) {
       mbar_init(&sm->tok[c], 1);
       mbar_init(&sm->xa_full[c], EPI_THREADS);
       mbar_init(&sm->xa_empty[c], 1);
       mbar_init(&sm->a_full[c], 2 * EPI_THREADS);
       mbar_init(&sm->a_empty[c], EPI_THREADS);
-      mbar_init(&sm->l_full[c], EPI_THREADS);
-      mbar_init(&sm->l_empty[c], EPI_THREADS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -315,7 +313,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   // 96 registers it spills its loop state to local memory, and with all of L1 carved out for shared memory each
   // reload is an L2 round trip (~1000 idle cycles per centre tile in the hand-off trace).  The control and finish warpgroups
   // give registers back, the two epilogue warpgroups take them (setmaxnreg works per 4-warp group).
-  if (warp >= W_XPROD && warp < W_ACC0) {
+  if (warp >= W_XPROD) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_CTRL));
   }
   if (warp == W_XPROD) {
@@ -626,6 +624,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     const int row_in_tile = w4 * 32 + lane;
     const float cmax = misc[KM_MISC_CMAX];
     const float tau0 = H16 ? kappa0 / misc[KM_MISC_SCALE] : 0.f;  // fp16 underflow term of the bound
+    const float inv_s2 = H16 ? misc[KM_MISC_INV_SCALE2] : 0.f;     // (read once: there is no L1 behind these loads)
     double cost = 0.0;
     unsigned long long nrows = 0;
     float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
@@ -678,20 +677,33 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       // itself and of the final add (~ max||c||^2: matters only for rows much closer to the origin than the centres)
       // (fp16 filter: ||c||^2 enters as three fp16 pieces times 2^15; their underflow adds 3 * 2^-10 / S^2)
       const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax) + 3.6e-7f * cmax * cmax +
-                         (H16 ? 5.9e-3f * misc[KM_MISC_INV_SCALE2] : 0.f);
+                         (H16 ? 5.9e-3f * inv_s2 : 0.f);
       const int64_t row = tile * TM + row_in_tile;
       const bool live = row < n;
       bool certain = (b2 - b1) > tau2;  // false for NaN as well
       bool pair_ok = false;  // uncertain, but every centre other than the best two is out of reach
       if (H16) {
         const float sc = tb_row_scale(xn, cmax);
-        const float arow = misc[KM_MISC_INV_SCALE2] * sc;
+        const float arow = inv_s2 * sc;
         const float thr = fmaf(tau2, sc, 2.5f);
         const bool usable = arow > 0.f && arow < INFINITY;
         certain = gap_units > thr && usable;
         pair_ok = !certain && usable && pairs != nullptr && gap3_units > thr && i2 >= 0 && i2 < k && i2 != i1;
       }
       if (live) labels[row] = i1;             // provisional for uncertain rows (rewritten by the re-check)
+      const int my_lab = (live && certain) ? i1 : -1;
+      const int64_t r0 = tile * TM + w4 * 32;
+      // The copies of the first two batches of certain rows go out NOW: the list appends below are atomics whose
+      // return value is an L2 round trip (~94 % of the warp-tiles have a pair row at cfg 2), and that wait then
+      // overlaps the copies instead of preceding them.
+      TbAcc acc_rows;
+      if (H16 && accumulate) {
+        acc_rows.X = X; acc_rows.n = n; acc_rows.ld = ld; acc_rows.r0 = r0; acc_rows.d = d; acc_rows.lane = lane;
+        acc_rows.myrep = myrep;
+        acc_rows.mybuf = fxbuf + (size_t)w4 * 2 * TB_FX_ROWS * d * 4;
+        acc_rows.fx_full = sm->fx_full[w4];
+        acc_rows.begin(fxc, my_lab);
+      }
       // uncertain rows with exactly two candidates: pair list (row, best, second best), decided by two fp64
       // distances; a full pair list sends the row to the re-check list instead
       bool to_list = live && !certain && !pair_ok;
@@ -722,21 +734,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
       if (w4 == 0) TR(10, 2);
       if (!accumulate) continue;
-      const int my_lab = (live && certain) ? i1 : -1;
       // bf16x3: squared distance to the chosen centre.  fp16: ||x||^2 only -- the remaining part of the cost,
       // sum_j (n_j ||c_j||^2 - 2 c_j . S_j), is added exactly from the sums (tcb_cost_terms_kernel)
       const float my_sc = H16 ? xn : fmaxf(xn + b1, 0.f);
-      const int64_t r0 = tile * TM + w4 * 32;
-      if (H16) {
-        if (TB_ACC_WARPS) {  // hand the labels to the accumulate warps (they take rows 16-31 of every quarter)
-          mbar_wait_ns(&sm->l_empty[ab], ((it >> 1) & 1) ^ 1, 64);
-          sm->lab[ab][row_in_tile] = my_lab;
-          mbar_arrive(&sm->l_full[ab]);
-        }
-        if (!table_mode)
-          tb_bulk_accumulate(X, n, ld, d, r0, (lane < TB_FX_SPAN) ? my_lab : -1, myrep,
-                             fxbuf + (size_t)w4 * 2 * TB_FX_ROWS * d * 4, sm->fx_full[w4], fxc, lane);
-      }
+      if (H16) acc_rows.finish(fxc);
       // TB_FIN_ROWS rows in flight per warp: the re-reads come from L2 (~800 cycles each way under load) and this
       // loop, not the epilogue, set the pace of the whole kernel at 8 rows in flight (hand-off trace)
       for (int g = 0; g < (H16 ? 0 : 32); g += TB_FIN_ROWS) {
@@ -763,7 +764,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
       if (w4 == 0) TR(10, 3);
     }
-    if (H16 && !table_mode) bulk_wait_all();  // the reductions read this CTA's shared memory
+    if (H16) bulk_wait_all();  // the reductions read this CTA's shared memory
     if (accumulate) {
       cost = warp_sum(cost);
       unsigned long long tot = nrows;
@@ -775,86 +776,6 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
     }
   }
-#if TB_ACC_WARPS
-  else if (warp >= W_ACC0) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TB_REG_ACC));
-    // ===================== accumulate (fp16 filter): rows 16-31 of every lane quarter, labels from the finish warps
-    if (H16 && accumulate && table_mode) {
-      // ---- small k * d (cfg 5: k = 256, d = 64): a [k, d] fp32 table in shared memory takes every certain row of
-      // this CTA; nothing goes to L2 until the end.  Warp w owns columns [16 w, 16 w + 16) of the table for ALL rows
-      // (so no two warps touch the same entry), lane = (row parity, column): plain read-add-write, two rows per step;
-      // the rare step whose two rows share a label is done in two halves.  The row tile comes back from L2 with one
-      // bulk copy issued a whole tile ahead of its labels.
-      const int w4 = warp - W_ACC0, tid = threadIdx.x - W_ACC0 * 32;
-      float* rf = reinterpret_cast<float*>(fxbuf);
-      float* table = rf + (size_t)TM * d;
-      for (int i = tid; i < k * d / 4; i += 128) reinterpret_cast<float4*>(table)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-      asm volatile("bar.sync 3, 128;" ::: "memory");
-      const int h = lane >> 4, col = w4 * 16 + (lane & 15);
-      const uint32_t rowbytes = (uint32_t)d * 4u;
-      uint64_t* rf_full = &sm->fx_full[0][0];
-      uint32_t it = 0;
-      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const uint32_t ab = it & 1;
-        const int nrows = (int)min((int64_t)TM, n - tile * TM);
-        if (tid == 0) mbar_expect_tx(rf_full, (uint32_t)nrows * rowbytes);
-        if (ld == d) {
-          if (tid == 0) bulk_load_hint(rf, X + tile * TM * ld, (uint32_t)nrows * rowbytes, rf_full, L2_EVICT_FIRST);
-        } else if (tid < nrows) {
-          bulk_load_hint(rf + (size_t)tid * d, X + (tile * TM + tid) * ld, rowbytes, rf_full, L2_EVICT_FIRST);
-        }
-        mbar_wait_ns(&sm->l_full[ab], (it >> 1) & 1, 128);
-        mbar_wait_ns(rf_full, it & 1, 64);
-#pragma unroll 2
-        for (int R = 0; R < TM; R += 8) {
-          int lb[4];
-          float xv[4];
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int row = R + 2 * q + h;
-            lb[q] = sm->lab[ab][row];
-            xv[q] = rf[(size_t)row * d + col];
-          }
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int other = __shfl_xor_sync(0xffffffffu, lb[q], 16);
-            float* t = table + (size_t)max(lb[q], 0) * d + col;
-            if (other != lb[q]) {  // warp-uniform: the step's two rows have different labels
-              if (lb[q] >= 0) *t += xv[q];
-            } else {
-              if (h == 0 && lb[q] >= 0) *t += xv[q];
-              __syncwarp();
-              if (h == 1 && lb[q] >= 0) *t += xv[q];
-            }
-            __syncwarp();
-          }
-        }
-        asm volatile("bar.sync 3, 128;" ::: "memory");  // every warp is done with this tile's labels and rows
-        mbar_arrive(&sm->l_empty[ab]);
-      }
-      asm volatile("bar.sync 3, 128;" ::: "memory");
-      float* myrep = rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d;
-      for (int i = tid; i < k * d / 4; i += 128) {
-        const float4 v = reinterpret_cast<const float4*>(table)[i];
-        if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) red_add_v4(myrep + (size_t)i * 4, v);
-      }
-    } else if (H16 && accumulate) {
-      const int w4 = warp - W_ACC0;
-      float* myrep = rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d;
-      uint8_t* mybuf = fxbuf + (size_t)(4 + w4) * 2 * TB_FX_ROWS * d * 4;
-      uint32_t it = 0, fxc = 0;
-      for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const uint32_t ab = it & 1;
-        mbar_wait_ns(&sm->l_full[ab], (it >> 1) & 1, 128);
-        const int lbl = (lane < TB_FX_SPAN) ? sm->lab[ab][w4 * 32 + TB_FX_SPAN + lane] : -1;
-        mbar_arrive(&sm->l_empty[ab]);
-        tb_bulk_accumulate(X, n, ld, d, tile * TM + w4 * 32 + TB_FX_SPAN, lbl, myrep, mybuf, sm->fx_full[4 + w4], fxc,
-                           lane);
-      }
-      bulk_wait_all();
-    }
-  }
-#endif
   tc_fence_before();
   __syncthreads();
   if (warp == W_ALLOC) {
@@ -1039,16 +960,8 @@ static int tcb_cap_from_bytes(size_t bytes, int d) {
 static int tcb_tile_bytes(int d, int filter) {
   return filter == KM_FILTER_FP16 ? (d / 64) * CHUNK_BYTES + TB_CN_BYTES : (d / 64) * tb_stage_bytes<KM_FILTER_BF16X3>();
 }
-// shared memory behind the centre-operand stages that the accumulation needs (fp16 filter): row slots of the
-// accumulating warps, or -- table mode -- the re-read row tile and the [k, d] table
-static bool tcb_table_mode(int k, int d, bool h16, bool accumulate) {
-  return TB_ACC_WARPS && h16 && accumulate && d == 64 && (size_t)k * d * 4 <= 65536;
-}
-static int tcb_fx_bytes(int k, int d, bool table) {
-  return table ? (TM + k) * d * 4 : TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4;
-}
-
-static int km_tcb_stages(int d, int filter, int fx_bytes) {
+static int km_tcb_stages(int d, int filter) {
+  const int fx_bytes = TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4;  // row slots of the finish warps (fp16 filter)
   int budget_kb = 227, cap = 4;
 #ifdef B2F_DEV  // dev knobs of the timing experiments; not in the product build
   if (filter == KM_FILTER_FP16 && getenv("B2F_TC_SMEM_KB")) budget_kb = atoi(getenv("B2F_TC_SMEM_KB"));
@@ -1065,8 +978,7 @@ bool km_tcb_supported(int k, int d, int64_t ld) {
   if (d != 64 && d != 128) return false;  // whole 64-k atoms, X hi/lo pairs fit the tensor memory budget
   if (k % TN != 0 || k < TN) return false;
   if (ld % 4 != 0) return false;
-  return km_tcb_stages(d, KM_FILTER_BF16X3, 0) >= 2 &&
-         km_tcb_stages(d, KM_FILTER_FP16, tcb_fx_bytes(k, d, tcb_table_mode(k, d, true, true))) >= 2 && km_tc_supported(k, d, ld);
+  return km_tcb_stages(d, KM_FILTER_BF16X3) >= 2 && km_tcb_stages(d, KM_FILTER_FP16) >= 2 && km_tc_supported(k, d, ld);
 }
 
 size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
@@ -1079,7 +991,7 @@ static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const C
                              const CUtensorMap& m2, const float* X, int64_t n, int d, int64_t ld, const float* colscale,
                              const float* cn, const float* misc, float kappa2, float kappa0, int k, int nstages,
                              double* payload, float* rep, unsigned long long* cnt, int32_t* labels, int accumulate,
-                             TcbWs* hdr, int32_t* amb_idx, int cap, int4* pairs, int pcap, int table_mode) {
+                             TcbWs* hdr, int32_t* amb_idx, int cap, int4* pairs, int pcap) {
   unsigned long long* trace = nullptr;
 #ifdef B2F_DEV  // hand-off tracer of the timing experiments (allocates; not in the product build)
   const char* trace_path = getenv("B2F_TC_TRACE");
@@ -1090,8 +1002,7 @@ static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const C
     auto kern = km_tcb_kernel<MODE, true, SCALED>;
     B2F_CUDA(b2f_smem_attr(kern, smem));
     kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
-                                             payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, table_mode,
-                                             trace);
+                                             payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, trace);
     B2F_LAUNCH_CHECK();
     std::vector<unsigned long long> host(trace_bytes / sizeof(unsigned long long));
     B2F_CUDA(cudaStreamSynchronize(stream));
@@ -1107,8 +1018,7 @@ static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const C
   auto kern = km_tcb_kernel<MODE, false, SCALED>;
   B2F_CUDA(b2f_smem_attr(kern, smem));
   kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
-                                           payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, table_mode,
-                                           trace);
+                                           payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, trace);
   B2F_LAUNCH_CHECK();
   return B2F_OK;
 }
@@ -1164,9 +1074,8 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
   int4* pairs = reinterpret_cast<int4*>(wp + W.off_pairs);
   float* Xamb = reinterpret_cast<float*>(wp + W.off_x);
   const bool h16 = filter == KM_FILTER_FP16;
-  const bool table = tcb_table_mode(k, d, h16, accumulate);
-  const int fx_bytes = tcb_fx_bytes(k, d, table);
-  const int nstages = km_tcb_stages(d, filter, fx_bytes);
+  const int fx_bytes = TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4;
+  const int nstages = km_tcb_stages(d, filter);
   B2F_REQUIRE(nstages >= 2, "b2f_kmeans (filter path): k = %d, d = %d does not fit in shared memory", k, d);
   CUtensorMap mx, m1, m2;
   int rc;
@@ -1217,11 +1126,11 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
     if (colscale)
       rc = tcb_launch_filter<KM_FILTER_FP16, true>(grid, smem, stream, mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2,
                                                    kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
-                                                   amb_idx, cap, pairs, cap, table ? 1 : 0);
+                                                   amb_idx, cap, pairs, cap);
     else
       rc = tcb_launch_filter<KM_FILTER_FP16, false>(grid, smem, stream, mx, m1, m2, X, n, d, ld, nullptr, cn, misc, kappa2,
                                                     kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
-                                                    amb_idx, cap, pairs, cap, table ? 1 : 0);
+                                                    amb_idx, cap, pairs, cap);
     if (rc != B2F_OK) return rc;
     if (acc_main && colscale && (rc = km_fold_scaled(acc, k, d, colscale, stream)) != B2F_OK) return rc;
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, 1.0);
@@ -1232,7 +1141,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
   } else {
     rc = tcb_launch_filter<KM_FILTER_BF16X3, false>(grid, smem, stream, mx, m1, m2, X, n, d, ld, nullptr, cn, misc, kappa2,
                                                     kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
-                                                    amb_idx, cap, nullptr, 0, 0);
+                                                    amb_idx, cap, nullptr, 0);
     if (rc != B2F_OK) return rc;
   }
   tcb_gather_kernel<<<b2f_sm_count() * 4, 256, 0, stream>>>(X, ld, d, colscale, hdr, amb_idx, Xamb, cap);
