@@ -17,6 +17,8 @@ ap.add_argument("--k", type=int, default=1024)
 ap.add_argument("--algo", type=int, default=2)
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--predict", action="store_true", help="labels only (no accumulation)")
+ap.add_argument("--predict-ws", action="store_true", help="labels only through the certainty pipeline (filter pass "
+                                                            "without accumulation)")
 ap.add_argument("--lloyd", type=int, default=0, help="run this many real Lloyd iterations first (centres move)")
 a = ap.parse_args()
 L = N.lib()
@@ -46,7 +48,10 @@ for i in range(a.reps + 2):
     N.check(L.b2f_kmeans_acc_zero(N.ptr(acc), a.k, a.d, N.stream_ptr()), "zero")
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    if a.predict:
+    if a.predict_ws:
+        N.check(L.b2f_kmeans_predict_ws(N.ptr(X), a.n, a.d, a.d, None, N.ptr(prep), a.k, N.ptr(lab), None, N.ptr(ws),
+                                        wsb, a.algo, N.stream_ptr()), "predict_ws")
+    elif a.predict:
         N.check(L.b2f_kmeans_predict(N.ptr(X), a.n, a.d, a.d, N.ptr(prep), a.k, N.ptr(lab), None, a.algo,
                                      N.stream_ptr()), "predict")
     elif a.algo in (4, 5):
