@@ -482,6 +482,13 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         for (int c = 0; c < 4; ++c) {
           tmem_ld_wait();
           if (c + 1 < 4) tmem_ld32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+          if (c == 3) {
+            // The last 32 columns are in registers: hand the accumulator back NOW, a quarter of the tile's
+            // arithmetic earlier.  The MMA that refills it is what the OTHER epilogue warp of this lane quarter
+            // waits for three centre tiles on (hand-off trace: ~14 % of an epilogue warp's time went into t_full).
+            tc_fence_before();
+            mbar_arrive(&sm->t_empty[cbuf]);
+          }
           const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + c * 32);
           const int jbase = nt * TN + c * 32;
 #pragma unroll
@@ -514,8 +521,6 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             i1b = (s3 < b1b) ? j + 3 : i1b;   b2b = fminf(b2b, fmaxf(b1b, s3)); b1b = fminf(b1b, s3);
           }
         }
-        tc_fence_before();
-        mbar_arrive(&sm->t_empty[cbuf]);
         if (H16) {  // fold the tile's two chains into the running triple; an earlier tile keeps equal keys
           const int k1 = min(k1a, k1b), k2 = min(max(k1a, k1b), min(k2a, k2b));
           // The tile's third smallest key is >= l3: if its two smallest sit in different chains it IS min(k2a, k2b);

@@ -17,26 +17,33 @@ __device__ __forceinline__ float load_as_f32(const void* p, int dtype, int64_t i
 }
 
 // Fast path of the loader for fp32 columns (what the Dataset Builder hands over after its casts, and what the BASELINE
-// configs hold): tile = 128 rows x 32 columns.  A lane reads FOUR consecutive rows of one column with one 16-byte
-// load (512 B per warp instruction instead of 128 B: the scalar version ran at 0.45 of the HBM peak), the tile is
-// transposed through padded shared memory and leaves as whole 128-byte row segments.
-#define PK4_ROWS 128
-__device__ __forceinline__ void pack_columns_f32_body(float (*tile)[PK_COLS + 1], const void* const* __restrict__ cols,
-                                                      int d, int64_t n, float* __restrict__ X, int64_t ld,
-                                                      int32_t* bad_flag) {
+// configs hold).  A CTA takes 32 rows x up to 128 columns at a time, so that BOTH sides of the transpose move whole
+// 128-byte lines: a lane reads four consecutive rows of one column with one 16-byte load (eight lanes = the 32 rows
+// of a column = one line), and the rows leave as contiguous 512-byte pieces.  (The first version, 64 x 32 tiles with
+// scalar loads, ran at 0.45 of the HBM peak; 128 x 32 tiles with 16-byte loads but 128-byte row pieces at 0.58.)
+// Shared-memory tile [32][128] floats, swizzled at 16-byte granularity with the row group as key: the four scalars a
+// lane scatters and the 16-byte reads of the output phase are both conflict-free without padding.
+#define PK4_ROWS 32
+#define PK4_COLS 128
+__device__ __forceinline__ int pk4_slot(int row, int col) {  // float index of (row, col) in the swizzled tile
+  return row * PK4_COLS + ((((col >> 2) ^ ((row >> 2) & 7)) << 2) | (col & 3));
+}
+__device__ __forceinline__ void pack_columns_f32_body(float* tile, const void* const* __restrict__ cols, int d, int64_t n,
+                                                      float* __restrict__ X, int64_t ld, int32_t* bad_flag) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int rg = lane & 7, cq = lane >> 3;  // row group (4 rows) and column within the warp's group of four
   const int64_t row_tiles = (n + PK4_ROWS - 1) / PK4_ROWS;
-  const int col_tiles = (int)((ld + PK_COLS - 1) / PK_COLS);
+  const int col_tiles = (int)((ld + PK4_COLS - 1) / PK4_COLS);
   const int64_t tiles = row_tiles * col_tiles;
   bool bad = false;
   for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
     const int64_t r0 = (t / col_tiles) * PK4_ROWS;
-    const int c0 = (int)(t % col_tiles) * PK_COLS;
-    float4 v[PK_COLS / 8];
+    const int c0 = (int)(t % col_tiles) * PK4_COLS;
+    const int64_t r = r0 + rg * 4;
+    float4 v[4];
 #pragma unroll
-    for (int cc = 0; cc < PK_COLS / 8; ++cc) {  // all four loads of this thread in flight before the first store
-      const int c = c0 + warp + cc * 8;
-      const int64_t r = r0 + lane * 4;
+    for (int cc = 0; cc < 4; ++cc) {  // all four loads of this thread in flight before the first store
+      const int c = c0 + (warp * 4 + cc) * 4 + cq;
       v[cc] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (c < d) {
         const float* p = static_cast<const float*>(cols[c]);
@@ -50,24 +57,22 @@ __device__ __forceinline__ void pack_columns_f32_body(float (*tile)[PK_COLS + 1]
       }
     }
 #pragma unroll
-    for (int cc = 0; cc < PK_COLS / 8; ++cc) {
-      const int cl = warp + cc * 8;
+    for (int cc = 0; cc < 4; ++cc) {
+      const int cl = (warp * 4 + cc) * 4 + cq;
       bad |= isnan(v[cc].x) | isnan(v[cc].y) | isnan(v[cc].z) | isnan(v[cc].w);
-      tile[lane * 4 + 0][cl] = v[cc].x;
-      tile[lane * 4 + 1][cl] = v[cc].y;
-      tile[lane * 4 + 2][cl] = v[cc].z;
-      tile[lane * 4 + 3][cl] = v[cc].w;
+      tile[pk4_slot(rg * 4 + 0, cl)] = v[cc].x;
+      tile[pk4_slot(rg * 4 + 1, cl)] = v[cc].y;
+      tile[pk4_slot(rg * 4 + 2, cl)] = v[cc].z;
+      tile[pk4_slot(rg * 4 + 3, cl)] = v[cc].w;
     }
     __syncthreads();
 #pragma unroll
-    for (int rr = 0; rr < PK4_ROWS / 32; ++rr) {
-      const int rl = (threadIdx.x >> 3) + rr * 32;
-      const int c4 = (threadIdx.x & 7) * 4;
-      const int64_t r = r0 + rl;
-      if (r < n && c0 + c4 < ld) {
-        float4 o = make_float4(tile[rl][c4], tile[rl][c4 + 1], tile[rl][c4 + 2], tile[rl][c4 + 3]);
-        *reinterpret_cast<float4*>(X + r * ld + c0 + c4) = o;
-      }
+    for (int rr = 0; rr < PK4_ROWS / 8; ++rr) {  // a warp writes one row (512 B) per instruction
+      const int rl = warp + rr * 8;
+      const int c4 = lane * 4;
+      const int64_t row = r0 + rl;
+      if (row < n && c0 + c4 < ld)
+        *reinterpret_cast<float4*>(X + row * ld + c0 + c4) = *reinterpret_cast<const float4*>(tile + pk4_slot(rl, c4));
     }
     __syncthreads();
   }
@@ -79,7 +84,7 @@ __device__ __forceinline__ void pack_columns_f32_body(float (*tile)[PK_COLS + 1]
 __global__ void __launch_bounds__(256) pack_columns_kernel(const void* const* __restrict__ cols,
                                                            const int32_t* __restrict__ dtypes, int d, int64_t n,
                                                            float* __restrict__ X, int64_t ld, int32_t* bad_flag) {
-  __shared__ float tile[PK4_ROWS][PK_COLS + 1];
+  __shared__ __align__(16) float tile[PK4_ROWS * PK4_COLS];  // 16 KB; the generic path uses it as [64][33]
   // all columns fp32 and 16-byte aligned -> the 16-byte-load path (decided per CTA, the same everywhere)
   int ok = 1;
   for (int c = threadIdx.x; c < d; c += 256)
@@ -88,6 +93,7 @@ __global__ void __launch_bounds__(256) pack_columns_kernel(const void* const* __
     pack_columns_f32_body(tile, cols, d, n, X, ld, bad_flag);
     return;
   }
+  float (*gt)[PK_COLS + 1] = reinterpret_cast<float (*)[PK_COLS + 1]>(tile);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t row_tiles = (n + PK_ROWS - 1) / PK_ROWS;
   const int col_tiles = (int)((ld + PK_COLS - 1) / PK_COLS);
@@ -114,7 +120,7 @@ __global__ void __launch_bounds__(256) pack_columns_kernel(const void* const* __
           v = load_as_f32(p, dt, r);
           bad |= isnan(v);  // upstream's assembler rejects NaN (and null) under handleInvalid = "error"; Inf passes
         }
-        tile[rl][cl] = v;
+        gt[rl][cl] = v;
       }
     }
     __syncthreads();
@@ -124,7 +130,7 @@ __global__ void __launch_bounds__(256) pack_columns_kernel(const void* const* __
       const int c4 = (threadIdx.x & 7) * 4;
       const int64_t r = r0 + rl;
       if (r < n && c0 + c4 < ld) {
-        float4 o = make_float4(tile[rl][c4], tile[rl][c4 + 1], tile[rl][c4 + 2], tile[rl][c4 + 3]);
+        float4 o = make_float4(gt[rl][c4], gt[rl][c4 + 1], gt[rl][c4 + 2], gt[rl][c4 + 3]);
         *reinterpret_cast<float4*>(X + r * ld + c0 + c4) = o;
       }
     }
@@ -251,7 +257,7 @@ extern "C" int b2f_pack_columns(const void* const* col_ptrs_dev, const int32_t* 
   if (n == 0) return B2F_OK;
   B2F_REQUIRE(col_ptrs_dev && col_dtypes_dev && X, "b2f_pack_columns: null pointer");
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "b2f_pack_columns: X must be 16-byte aligned");
-  int64_t tiles = ((n + PK4_ROWS - 1) / PK4_ROWS) * ((ld + PK_COLS - 1) / PK_COLS);  // (fast path: 128-row tiles)
+  int64_t tiles = ((n + PK_ROWS - 1) / PK_ROWS) * ((ld + PK_COLS - 1) / PK_COLS);
   int64_t cap = (int64_t)b2f_sm_count() * 8;
   int grid = (int)(tiles < cap ? tiles : cap);
   pack_columns_kernel<<<grid, 256, 0, b2f_cs(stream)>>>(col_ptrs_dev, col_dtypes_dev, d, n, X, ld, bad_flag);
