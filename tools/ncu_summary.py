@@ -30,6 +30,12 @@ KEEP = [
 ]
 KEEP_SUFFIX = [
     "sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed",
+    "sm__inst_executed_pipe_alu_realtime.avg.pct_of_peak_sustained_elapsed",
+    "sm__inst_executed_pipe_fma_realtime.avg.pct_of_peak_sustained_elapsed",
+    "sm__inst_executed_pipe_fmaheavy_realtime.avg.pct_of_peak_sustained_elapsed",
+    "sm__inst_executed_pipe_lsu_realtime.avg.pct_of_peak_sustained_elapsed",
+    "l1tex__t_requests_pipe_lsu_mem_local_op_ld.sum",
+    "l1tex__t_requests_pipe_lsu_mem_local_op_st.sum",
     "sm__ops_path_tensor_op_utchmma_src_bf16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed",
     "sm__ops_path_tensor_op_utchmma_src_tf32_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed",
 ]
