@@ -164,15 +164,12 @@ def test_two_rank_fits_equal_the_one_rank_fits():
             # single passes at a fixed iterate: only the order of the sums differs between 1 and 2 ranks
             for key in ("b_pass", "m_pass"):
                 close(pre + key, two[key], one[key], 1e-7, 1e-7 * np.abs(one[key]).max())
-            # OWL-QN (multinomial, L1) is NOT a smooth map of its inputs: Breeze's backtracking search tests the
-            # slope of a piecewise objective (grow / shrink on kinks) and the orthant projection switches coordinates
-            # where |gradient| is within rounding of the L1 weight, so two runs whose passes agree to 1e-7 may accept
-            # different steps and part by 1e-3 in the objective for a few iterations (observed) before meeting again
-            # near the optimum.  What is held here: same number of states +- 2, objective decreasing, final
-            # objectives within 1 %; the pass-level agreement above is the parity statement.
-            assert abs(len(two["m_hist"]) - len(one["m_hist"])) <= 2
-            assert two["m_hist"][-1] < two["m_hist"][0]
-            close(pre + "multinomial final objective", two["m_hist"][-1:], one["m_hist"][-1:], 1e-2)
+            # OWL-QN (multinomial, elastic net): the same bar as the binary L-BFGS fit.  (This comparison is what
+            # exposed the tensor-core kernel's d = 128 hazard in round 2: with it the two runs parted by 1e-3 after
+            # one iteration; d = 128 now runs on the CUDA-core kernel and the histories agree to 1e-9.)
+            close(pre + "multinomial objective", two["m_hist"], one["m_hist"], 1e-7)
+            close(pre + "multinomial coefficients", two["m_coef"], one["m_coef"], 1e-5,
+                  1e-7 * np.abs(one["m_coef"]).max())
     print("\n" + "\n".join(report))
     assert not failures, "\n".join(failures)
     # ranks of one run hold identical models (no root, no broadcast: every rank ran the same finalize)
