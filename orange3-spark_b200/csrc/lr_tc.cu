@@ -56,9 +56,15 @@ constexpr int LT_SPLIT_THREADS = 256;
 #define LT_FLUSH 8
 #endif
 constexpr int LT_NP = 32;          // classes padded to the MMA N
-constexpr int LT_XS = 6;           // X staging slots (16 KB each); must stay a multiple of the number of split groups (2):
+#ifndef LT_XS_SLOTS
+#define LT_XS_SLOTS 6
+#endif
+#ifndef LT_W_STAGES
+#define LT_W_STAGES 4
+#endif
+constexpr int LT_XS = LT_XS_SLOTS; // X staging slots (16 KB each); must stay a multiple of the number of split groups (2):
                                    // a slot is then always consumed by the same group and its parity waits cannot alias
-constexpr int LT_WS = 4;           // W stages (hi + lo, 8 KB each)
+constexpr int LT_WS = LT_W_STAGES; // W stages (hi + lo, 8 KB each)
 constexpr int LT_WSTAGE = 2 * LT_NP * 128;
 // tensor memory columns
 constexpr uint32_t LT_TMEM_COLS = 512;
@@ -597,7 +603,10 @@ __global__ void lr_mn_prep_kernel(const double* __restrict__ beta, int K, int d,
 // 60 000 x 128; found by the two-rank parity test of round 2, present since round 1, whose only d = 128 case had one
 // tile per CTA; tools/lr_repeat_check.py reproduces it).  Not located yet; d = 128 runs on the CUDA-core kernel.
 // d in {256, 384, 512} are deterministic and within 4e-6 of the fp64 reference up to 20M rows.
-bool lr_mn_tc_supported(int d, int64_t ld, int K) { return d % 128 == 0 && d >= 256 && d <= 512 && ld == d && K >= 2 && K <= LT_NP; }
+#ifndef LT_MIN_D
+#define LT_MIN_D 256
+#endif
+bool lr_mn_tc_supported(int d, int64_t ld, int K) { return d % 128 == 0 && d >= LT_MIN_D && d <= 512 && ld == d && K >= 2 && K <= LT_NP; }
 
 size_t lr_mn_tc_extra_scratch(int d) { return (size_t)2 * LT_NP * d * sizeof(float) + 2048; }
 
