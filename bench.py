@@ -44,7 +44,7 @@ def parse():
     return ap.parse_args()
 
 
-TRAFFIC_FILE = os.path.join("profiles", "r1_traffic.json")
+TRAFFIC_FILE = os.path.join("profiles", "r2_traffic.json")
 
 
 def measured_traffic(kernel, rows):

@@ -15,24 +15,44 @@ def bind_to_gpu_numa_node(device_index):
     host memory: pages are then placed on that node (first touch) and every rank's host->device copies use its own
     memory controller and PCIe root instead of all ranks sharing node 0 -- which is what held the 4- and 8-GPU
     end-to-end numbers down (identical device times, 1.7x spread in wall time between runs).
-    Returns {"node", "cpus"} or None when the topology cannot be read (single-node hosts, containers without sysfs)."""
+    Returns {"node", "cpus"} or None when the topology cannot be read (single-node hosts, containers without sysfs).
+    Sources, in order: sysfs (`numa_node` of the PCI device), then NVML's ideal-CPU mask for the device."""
     import os
+
+    def _nvml_cpus():
+        import pynvml
+        import torch
+
+        pynvml.nvmlInit()
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = "%08x:%02x:%02x.0" % (getattr(p, "pci_domain_id", 0), p.pci_bus_id, p.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bdf.encode())
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        return [64 * i + b for i, w in enumerate(mask) for b in range(64) if (int(w) >> b) & 1]
 
     try:
         import torch
 
         p = torch.cuda.get_device_properties(device_index)
         bdf = "%04x:%02x:%02x.0" % (getattr(p, "pci_domain_id", 0), p.pci_bus_id, p.pci_device_id)
-        with open("/sys/bus/pci/devices/%s/numa_node" % bdf) as f:
-            node = int(f.read().strip())
-        if node < 0:
-            return None
-        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
-            spec = f.read().strip()
+        node = -1
+        try:
+            with open("/sys/bus/pci/devices/%s/numa_node" % bdf) as f:
+                node = int(f.read().strip())
+        except OSError:
+            pass
         cpus = set()
-        for part in spec.split(","):
-            lo, _, hi = part.partition("-")
-            cpus.update(range(int(lo), int(hi or lo) + 1))
+        if node >= 0:
+            with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+                spec = f.read().strip()
+            for part in spec.split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        else:
+            cpus = set(_nvml_cpus())
+            if not cpus or len(cpus) >= (os.cpu_count() or 1):
+                return None  # no locality information: leave the affinity alone
         allowed = os.sched_getaffinity(0)
         cpus = sorted(cpus & allowed) or sorted(allowed)
         os.sched_setaffinity(0, cpus)
