@@ -81,14 +81,6 @@ __device__ __forceinline__ float tb_row_scale(float xn, float cmax) {
   return __int_as_float(e << 23);
 }
 
-// TB_EPI2 = 1: two-pass epilogue per 32-column chunk (fp16 filter).  The keys of a chunk stay in registers; pass 1
-// takes their minimum m with 3-input min, pass 2 the second smallest as  m + 1 + umin_j (key_j - m - 1)  -- the
-// minimum itself wraps to 0xFFFFFFFF and drops out (keys of a chunk are distinct: they carry their column) -- with
-// the subtraction issued as an integer multiply-add, i.e. on the FMA pipe.  Per score that is 3 FMA-pipe and ~1.45
-// ALU-pipe operations instead of 2 and ~2.7 (the ALU pipe runs at half rate and is what the profile shows busiest).
-#ifndef TB_EPI2
-#define TB_EPI2 0
-#endif
 constexpr int TB_THREADS = 640;
 constexpr int TB_CN_BYTES = 128 * 32;  // the ||c||^2 k-block of a centre tile: 128 centres x 16 halves
 #ifndef TB_REG_CTRL
@@ -456,8 +448,6 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     // fp16 filter: the accumulator holds S^2 * (x . -2c)
     const float inv = H16 ? misc[KM_MISC_INV_SCALE2] : 1.f;
     const float cmax_e = misc[KM_MISC_CMAX];
-    const int one = (int)(ntiles >> 62) + 1;  // 1, but not to the compiler: keeps the multiply-adds below as IMAD
-    (void)one;
     uint32_t it = 0, buf = 0, round = 0, par = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       float b1a = INFINITY, b2a = INFINITY, b1b = INFINITY, b2b = INFINITY;
@@ -488,7 +478,6 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         uint32_t v[2][32];
         tmem_ld32(taddr, v[0]);
         int k1a = 0x7fffffff, k2a = 0x7fffffff, k1b = 0x7fffffff, k2b = 0x7fffffff;
-        int tk1 = 0x7fffffff, tk2 = 0x7fffffff, tl3 = 0x7fffffff;  // TB_EPI2: the tile's best, second, third bound
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           tmem_ld_wait();
@@ -499,38 +488,6 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             // waits for three centre tiles on (hand-off trace: ~14 % of an epilogue warp's time went into t_full).
             tc_fence_before();
             mbar_arrive(&sm->t_empty[cbuf]);
-          }
-          if (TB_EPI2 && H16) {
-            int key[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) key[j] = tb_key(__uint_as_float(v[c & 1][j]), arow, c * 32 + j);
-            // pass 1: the chunk's smallest key
-            int ma = __vimin3_s32(key[0], key[1], key[2]), mb = __vimin3_s32(key[16], key[17], key[18]);
-#pragma unroll
-            for (int j = 3; j < 15; j += 2) {
-              ma = __vimin3_s32(ma, key[j], key[j + 1]);
-              mb = __vimin3_s32(mb, key[16 + j], key[17 + j]);
-            }
-            const int m = __vimin3_s32(ma, mb, min(key[15], key[31]));
-            // pass 2: the second smallest; key - m - 1 as a multiply-add (FMA pipe), unsigned minimum
-            const int nb = -(m + 1);
-            unsigned ua = 0xffffffffu, ub = 0xffffffffu;
-#pragma unroll
-            for (int j = 0; j < 16; j += 2) {
-              unsigned u0, u1, u2, u3;
-              asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(u0) : "r"(key[j]), "r"(one), "r"(nb));
-              asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(u1) : "r"(key[j + 1]), "r"(one), "r"(nb));
-              asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(u2) : "r"(key[16 + j]), "r"(one), "r"(nb));
-              asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(u3) : "r"(key[17 + j]), "r"(one), "r"(nb));
-              ua = __vimin3_u32(ua, u0, u1);
-              ub = __vimin3_u32(ub, u2, u3);
-            }
-            const int sec = (int)min(ua, ub) + m + 1;
-            // chunk (m, sec, third >= sec) into the tile's triple: third of two sorted triples
-            tl3 = min(min(tl3, sec), min(max(tk2, m), max(tk1, sec)));
-            tk2 = __vimin3_s32(tk2, sec, max(tk1, m));
-            tk1 = min(tk1, m);
-            continue;
           }
           const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + c * 32);
           const int jbase = nt * TN + c * 32;
@@ -565,12 +522,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           }
         }
         if (H16) {  // fold the tile's two chains into the running triple; an earlier tile keeps equal keys
-          const int k1 = TB_EPI2 ? tk1 : min(k1a, k1b);
-          const int k2 = TB_EPI2 ? tk2 : min(max(k1a, k1b), min(k2a, k2b));
+          const int k1 = min(k1a, k1b), k2 = min(max(k1a, k1b), min(k2a, k2b));
           // The tile's third smallest key is >= l3: if its two smallest sit in different chains it IS min(k2a, k2b);
           // if one chain holds both, that chain's third is unknown and min(k2a, k2b) = k2 is all that can be said.
-          // (TB_EPI2: chunks of 32 columns play the role of the chains, each with its exact top two.)
-          const int l3 = TB_EPI2 ? tl3 : min(k2a, k2b);
+          const int l3 = min(k2a, k2b);
           // third smallest of the two sorted triples (B1, B2, B3) and (k1, k2, l3)
           B3 = min(min(B3, l3), min(max(B2, k1), max(B1, k2)));
           const int lose = max(B1, k1);             // the larger of the two firsts ...
