@@ -289,6 +289,8 @@ __global__ void __launch_bounds__(NTHREADS, 1)
             lo[p * 4 + 2] = __float_as_uint(to_tf32(v.z - h2)); lo[p * 4 + 3] = __float_as_uint(to_tf32(v.w - h3));
           }
         }
+        // (proxy fence: generic reads of the chunk before its refill by TMA; see kmeans_tcb.cu)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         mbar_arrive(&sm->xs_empty[kc]);                 // staging chunk may be refilled (next tile)
         mbar_wait(&sm->xa_empty[kc], (it & 1) ^ 1);     // previous tile's MMAs are done with this TMEM chunk
         tc_fence_after();

@@ -601,6 +601,11 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             p2[h * 16 + p * 2 + 0] = *reinterpret_cast<const uint32_t*>(&l01);
             p2[h * 16 + p * 2 + 1] = *reinterpret_cast<const uint32_t*>(&l23);
           }
+          // generic-proxy reads of the staging chunk before its refill through the async proxy (TMA): without the
+          // proxy fence the refill may overtake reads still in flight (the arrive only clobbers memory, so the
+          // arithmetic consuming them can be scheduled below it).  Found in the multinomial LR kernel, where it
+          // showed; the same hand-off here never failed a repeatability test, and costs nothing to close.
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           mbar_arrive(&sm->xs_empty[kc]);
         }
         const uint32_t xb = it % XBUFS;

@@ -507,6 +507,12 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
           lo[p * 4 + 0] = __float_as_uint(v.x - __uint_as_float(h0)); lo[p * 4 + 1] = __float_as_uint(v.y - __uint_as_float(h1));
           lo[p * 4 + 2] = __float_as_uint(v.z - __uint_as_float(h2)); lo[p * 4 + 3] = __float_as_uint(v.w - __uint_as_float(h3));
         }
+        // The staging slot is about to be refilled by TMA (async proxy) and was just read through the generic
+        // proxy: the proxy fence orders those reads before the refill.  Without it the refill could overtake reads
+        // still in flight -- ptxas is free to sink the arithmetic that consumes them below the arrive, which only
+        // clobbers memory -- and at d = 128 (four chunks per tile, six slots: the producer is always waiting at the
+        // slot) it did: gradients differed by 3e-3 from run to run as soon as a CTA had three tiles.
+        fence_async_smem();
         mbar_arrive(&sm->xs_empty[slot]);
         if (w8 == 0) LTR(5, tt, 2);
         const uint32_t aslot = g1 % LT_A1_SLOTS, aph = (g1 / LT_A1_SLOTS) & 1;
@@ -561,6 +567,7 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
           *reinterpret_cast<uint4*>(d1 + off) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
           *reinterpret_cast<uint4*>(d2 + off) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
         }
+        fence_async_smem();  // generic reads of the slot before its refill through the async proxy (see split1)
         mbar_arrive(&sm->xs_empty[slot]);
         if (w8 == 0) LTR(5, tt, 8);
       }
@@ -598,13 +605,9 @@ __global__ void lr_mn_prep_kernel(const double* __restrict__ beta, int K, int d,
   }
 }
 
-// d = 128 is NOT taken: with four GEMM1 chunks and a single GEMM2 block per tile the pipeline has a hazard that
-// shows as soon as a CTA gets three or more row tiles (run-to-run differences of 3e-3 in the gradient at
-// 60 000 x 128; found by the two-rank parity test of round 2, present since round 1, whose only d = 128 case had one
-// tile per CTA; tools/lr_repeat_check.py reproduces it).  Not located yet; d = 128 runs on the CUDA-core kernel.
-// d in {256, 384, 512} are deterministic and within 4e-6 of the fp64 reference up to 20M rows.
+// (d = 128 was off this kernel for part of round 2: see the proxy fence in the split warps.)
 #ifndef LT_MIN_D
-#define LT_MIN_D 256
+#define LT_MIN_D 128
 #endif
 bool lr_mn_tc_supported(int d, int64_t ld, int K) { return d % 128 == 0 && d >= LT_MIN_D && d <= 512 && ld == d && K >= 2 && K <= LT_NP; }
 

@@ -165,8 +165,8 @@ def test_two_rank_fits_equal_the_one_rank_fits():
             for key in ("b_pass", "m_pass"):
                 close(pre + key, two[key], one[key], 1e-7, 1e-7 * np.abs(one[key]).max())
             # OWL-QN (multinomial, elastic net): the same bar as the binary L-BFGS fit.  (This comparison is what
-            # exposed the tensor-core kernel's d = 128 hazard in round 2: with it the two runs parted by 1e-3 after
-            # one iteration; d = 128 now runs on the CUDA-core kernel and the histories agree to 1e-9.)
+            # exposed the staging-slot race of the multinomial tensor-core kernel in round 2: with it the two runs
+            # parted by 1e-3 after one iteration; with the fix the histories agree to 1e-9.)
             close(pre + "multinomial objective", two["m_hist"], one["m_hist"], 1e-7)
             close(pre + "multinomial coefficients", two["m_coef"], one["m_coef"], 1e-5,
                   1e-7 * np.abs(one["m_coef"]).max())
