@@ -115,6 +115,16 @@ size_t b2f_kmeans_acc_bytes(int k, int d);
 /* number of doubles in the all-reduce payload at the head of `acc` */
 int64_t b2f_kmeans_payload_len(int k, int d);
 int b2f_kmeans_prepare(const double* centers, int k, int d, void* prep, b2f_stream_t stream);
+/* The same, told the largest row norm of the data the operands will meet (x_norm_max >= max_i ||x_i||, of the scaled
+ * rows when a column scale is used; 0 = unknown = b2f_kmeans_prepare).  With it the fp16 filter scales its operands
+ * so that every score of every row fits one 22-bit key window and lets the tensor core add the rounding constant:
+ * one instruction per score less in its epilogue.  Rows whose norm exceeds the figure (other data at predict time)
+ * are simply handed to the re-check.  b2f_row_norm_max computes it: out is a device float, ZEROED by the caller,
+ * receives max ||x|| rounded up (atomicMax; with several ranks every rank may use its own shard's value).
+ * Same reference call site as above (KMeans.fit).                                                        */
+int b2f_kmeans_prepare_x(const double* centers, int k, int d, double x_norm_max, void* prep, b2f_stream_t stream);
+int b2f_row_norm_max(const float* X, int64_t n, int d, int64_t ld, const float* col_scale, float* out,
+                     b2f_stream_t stream);
 int b2f_kmeans_acc_zero(void* acc, int k, int d, b2f_stream_t stream);
 /* one assignment + accumulate pass over this rank's rows (findClosest + axpy into sums):
  * labels (int32[n]) may be NULL; w (row weights) may be NULL; algo is a B2F_KM_* code.       */

@@ -35,6 +35,8 @@ PROTOTYPES = {
     "b2f_kmeans_acc_bytes": (_sz, [_i32, _i32]),
     "b2f_kmeans_payload_len": (_i64, [_i32, _i32]),
     "b2f_kmeans_prepare": (C.c_int, [_vp, _i32, _i32, _vp, _vp]),
+    "b2f_kmeans_prepare_x": (C.c_int, [_vp, _i32, _i32, _f64, _vp, _vp]),
+    "b2f_row_norm_max": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _vp, _vp]),
     "b2f_kmeans_acc_zero": (C.c_int, [_vp, _i32, _i32, _vp]),
     "b2f_kmeans_step": (C.c_int, [_vp, _i64, _i32, _i64, _vp, _vp, _i32, _vp, _vp, _i32, _vp]),
     "b2f_kmeans_ws_bytes": (_sz, [_i64, _i32, _i32]),

@@ -43,6 +43,7 @@ class CudaLloydEngine:
         self.status_f64 = torch.zeros(2, dtype=torch.float64, device=dev)
         self.launches = 0
         self.fallbacks = 0
+        self._xmax = None
         # low-precision filter pass + pair check + 3xTF32 re-check (B2F_KM_TCH fp16 / B2F_KM_TCB bf16x3; AUTO = TCH)
         # needs a labels buffer and a workspace.  Decided from the SHAPE only (never from this rank's row count):
         # every rank must take the same branches between collectives, also one whose shard is empty.
@@ -67,9 +68,23 @@ class CudaLloydEngine:
         self.centers.copy_(torch.from_numpy(C))
         self._prepare()
 
+    def _x_norm_max(self):
+        """Largest row norm of this shard (of the scaled rows for a view), once: lets the fp16 filter use one key
+        scale for all rows (b2f_kmeans_prepare_x).  Every rank may use its own value: the scale only has to cover the
+        rows this rank's kernels meet."""
+        if self._xmax is None:
+            self._xmax = 0.0
+            if self.use_ws and self.X.n > 0:
+                out = _torch().zeros(1, dtype=_torch().float32, device=self.dev)
+                N.check(self.L.b2f_row_norm_max(N.ptr(self.X.data), self.X.n, self.d, self.X.ld,
+                                                N.ptr(self.col_scale), N.ptr(out), N.stream_ptr()), "b2f_row_norm_max")
+                self._xmax = float(out.item())
+                self.launches += 1
+        return self._xmax
+
     def _prepare(self):
-        N.check(self.L.b2f_kmeans_prepare(N.ptr(self.centers), self.k, self.d, N.ptr(self.prep), N.stream_ptr()),
-                "b2f_kmeans_prepare")
+        N.check(self.L.b2f_kmeans_prepare_x(N.ptr(self.centers), self.k, self.d, self._x_norm_max(), N.ptr(self.prep),
+                                            N.stream_ptr()), "b2f_kmeans_prepare_x")
         self.launches += 1
 
     def step(self, labels=None, exact=False, events=None):

@@ -60,13 +60,26 @@ static inline size_t b2f_align_up(size_t x, size_t a) { return (x + a - 1) / a *
 //                            k-block of the fp16 filter's centre operand (its x side is the constant 2^15), so the
 //                            tensor core adds ||c||^2 and the epilogue does not have to
 //          MISC float[64]    [0] = max_j ||c_j|| rounded up   [1] = max |c_jl|   (float bits, atomicMax)
-//                            [2] = S   [3] = 1 / S^2   (written by the second prepare kernel)            ]
+//                            [2] = S_a, the scale of the x operand   [3] = 1 / (S_a S_b)   [4] = S_b, the scale of
+//                            the centre operand   [5] = max ||x|| the planes were built for (0: unknown)
+//                            [6] = global key scale sc = S_a S_b (0: per-row key scales)
+//                            (written by the second prepare kernel)                                      ]
+// fp16 filter, two modes.  Per-row (max ||x|| unknown): S_a = S_b = S, the accumulator holds S^2 * score and the
+// epilogue scales every score into its row's 22-bit key window (one multiply-add per score).  Global (max ||x||
+// given, b2f_kmeans_prepare_x): S_a S_b = sc is chosen so that sc * |score| < 2^21 for EVERY row, and the same
+// k-block that adds ||c||^2 also adds the magic constant 1.5 * 2^23 (A side 3072, centre side 4096 in column 3 of
+// CNH): the accumulator then holds the key's integer directly and the multiply-add disappears from the epilogue.
 #define KM_CNH_COLS 16
 #define KM_CNH_E1 32768.f
+#define KM_CNH_MA 3072.f   // 1.5 * 2^11: x-side half of the magic constant (always present in the constant block)
+#define KM_CNH_MB 4096.f   // centre-side half (column 3 of CNH; written in global mode only)
 #define KM_MISC_CMAX 0
 #define KM_MISC_CABS 1
 #define KM_MISC_SCALE 2
 #define KM_MISC_INV_SCALE2 3
+#define KM_MISC_SCALE_B 4
+#define KM_MISC_XMAX 5
+#define KM_MISC_SC 6
 struct KmPrepLayout {
   size_t off_c32, off_ch, off_cl, off_cn, off_c64, off_cb1, off_cb2, off_ch16, off_cn64, off_cnh, off_misc, bytes;
 };

@@ -56,25 +56,46 @@ __global__ void km_prepare_kernel(const double* __restrict__ C, int k, int d, fl
 // and data entries up to ~16x the largest |-2c| entry stay finite (rows beyond that are sent to the re-check).
 __global__ void km_prepare_h16_kernel(const double* __restrict__ C, int k, int d, __half* __restrict__ ch16,
                                       const double* __restrict__ cn64, __half* __restrict__ cnh,
-                                      float* __restrict__ misc) {
+                                      float* __restrict__ misc, float xmax) {
   const float cabs = misc[KM_MISC_CABS];
-  int e = 0;
+  const float cmax = misc[KM_MISC_CMAX];
+  int ea = 0, eb = 0;  // S_a = 2^ea (x operand), S_b = 2^eb (centre operand)
+  bool global = false;
   if (cabs > 0.f) {
     int ex;
     frexpf(2.f * cabs, &ex);  // 2 cabs = m * 2^ex, m in [0.5, 1)
-    e = 12 - ex;
-    e = max(-60, min(60, e));
+    ea = eb = max(-60, min(60, 12 - ex));  // per-row mode: both operands on the centres' scale
+    if (xmax > 0.f && xmax < INFINITY && cmax < INFINITY) {
+      // global mode: sc = 2^es with R * sc < 2^21, R >= |score| of every row; split es between the two operands so
+      // that xmax * S_a and 2 cabs * S_b come out alike (their product is below 2^21, so neither can overflow)
+      const float R = fmaf(2.f * xmax, cmax, cmax * cmax) * 1.0001f;
+      int er, ex_x;
+      frexpf(R, &er);          // R < 2^er
+      frexpf(xmax, &ex_x);     // xmax < 2^ex_x
+      const int es = 21 - er;  // sc = 2^es
+      const int a = (es + ex - ex_x) >> 1;  // floor((es + log 2cabs - log xmax) / 2)
+      if (a > -60 && a < 60 && es - a > -60 && es - a < 60) {
+        ea = a;
+        eb = es - a;
+        global = true;
+      }
+    }
   }
-  const float S = exp2f((float)e);
+  const float Sb = exp2f((float)eb);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    misc[KM_MISC_SCALE] = S;
-    misc[KM_MISC_INV_SCALE2] = exp2f((float)(-2 * e));
+    misc[KM_MISC_SCALE] = exp2f((float)ea);
+    misc[KM_MISC_SCALE_B] = Sb;
+    misc[KM_MISC_INV_SCALE2] = exp2f((float)(-(ea + eb)));
+    misc[KM_MISC_XMAX] = global ? xmax : 0.f;
+    misc[KM_MISC_SC] = global ? exp2f((float)(ea + eb)) : 0.f;
   }
+  const float S = Sb;
   const size_t kd = (size_t)k * d;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < kd; i += (size_t)gridDim.x * blockDim.x)
     ch16[i] = __float2half_rn((float)(-2.0 * C[i]) * S);
-  // ||c||^2 * S^2 / 2^15 = h1 + h2 + h3 (fp16 pieces; |c_jl| S <= 2^11 and d <= 128 keep h below 2^14)
-  const double s2 = (double)S * (double)S / (double)KM_CNH_E1;
+  // ||c||^2 * S_a S_b / 2^15 = h1 + h2 + h3 (fp16 pieces; per-row mode: |c_jl| S <= 2^11 and d <= 128 keep h below
+  // 2^14; global mode: ||c||^2 sc < 2^21, h < 2^6); column 3: the centre-side half of the magic constant
+  const double s2 = exp2((double)(ea + eb)) / (double)KM_CNH_E1;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)k * KM_CNH_COLS;
        i += (size_t)gridDim.x * blockDim.x) {
     const int j = (int)(i / KM_CNH_COLS), c = (int)(i % KM_CNH_COLS);
@@ -86,6 +107,8 @@ __global__ void km_prepare_h16_kernel(const double* __restrict__ C, int k, int d
       const __half h2 = __float2half_rn((float)r1);
       const double r2 = r1 - (double)__half2float(h2);
       out = c == 0 ? h1 : c == 1 ? h2 : __float2half_rn((float)r2);
+    } else if (c == 3 && global) {
+      out = __float2half_rn(KM_CNH_MB);
     }
     cnh[i] = out;
   }
@@ -505,7 +528,58 @@ extern "C" int64_t b2f_kmeans_payload_len(int k, int d) {
 }
 
 extern "C" int b2f_kmeans_prepare(const double* centers, int k, int d, void* prep, b2f_stream_t stream) {
+  return b2f_kmeans_prepare_x(centers, k, d, 0.0, prep, stream);
+}
+
+// max_i ||x_i|| (of the rows x * col_scale when a factor is given), fp32 rounded up, atomicMax on the float bits
+__global__ void __launch_bounds__(256) km_row_norm_max_kernel(const float* __restrict__ X, int64_t n, int d, int64_t ld,
+                                                              const float* __restrict__ colscale,
+                                                              unsigned int* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  float best = 0.f;
+  for (int64_t r = warp; r < n; r += nwarps) {
+    const float* xr = X + r * ld;
+    float a = 0.f;
+    for (int c = lane * 4; c < d; c += 128) {
+      float4 x = ldg_stream(reinterpret_cast<const float4*>(xr + c));
+      if (c + 1 >= d) x.y = 0.f;
+      if (c + 2 >= d) x.z = 0.f;
+      if (c + 3 >= d) x.w = 0.f;
+      if (colscale) {
+        x.x = __fmul_rn(x.x, colscale[c]);
+        if (c + 1 < d) x.y = __fmul_rn(x.y, colscale[c + 1]);
+        if (c + 2 < d) x.z = __fmul_rn(x.z, colscale[c + 2]);
+        if (c + 3 < d) x.w = __fmul_rn(x.w, colscale[c + 3]);
+      }
+      a = fmaf(x.x, x.x, a); a = fmaf(x.y, x.y, a); a = fmaf(x.z, x.z, a); a = fmaf(x.w, x.w, a);
+    }
+    a = warp_sum(a);
+    best = fmaxf(best, a);  // NaN rows drop out here; the filter sends them to the re-check anyway
+  }
+  if (lane == 0 && best > 0.f && best < INFINITY)
+    atomicMax(out, __float_as_uint(__fsqrt_ru(best * 1.00001f)));
+}
+
+extern "C" int b2f_row_norm_max(const float* X, int64_t n, int d, int64_t ld, const float* col_scale, float* out,
+                                b2f_stream_t stream) {
+  B2F_REQUIRE(n >= 0 && d > 0 && ld >= d && ld % 4 == 0, "b2f_row_norm_max: need ld >= d, ld %% 4 == 0");
+  B2F_REQUIRE(out, "b2f_row_norm_max: null output");
+  if (n == 0) return B2F_OK;
+  B2F_REQUIRE(X, "b2f_row_norm_max: null pointer");
+  int64_t want = (n + 7) / 8;
+  int64_t cap = (int64_t)b2f_sm_count() * 16;
+  km_row_norm_max_kernel<<<(unsigned)(want < cap ? want : cap), 256, 0, b2f_cs(stream)>>>(
+      X, n, d, ld, col_scale, reinterpret_cast<unsigned int*>(out));
+  B2F_LAUNCH_CHECK();
+  return B2F_OK;
+}
+
+extern "C" int b2f_kmeans_prepare_x(const double* centers, int k, int d, double x_norm_max, void* prep,
+                                    b2f_stream_t stream) {
   B2F_REQUIRE(centers && prep && k > 0 && d > 0, "b2f_kmeans_prepare: bad arguments");
+  B2F_REQUIRE(x_norm_max >= 0.0, "b2f_kmeans_prepare_x: x_norm_max must be >= 0 (0 = unknown)");
   KmPrepLayout L = km_prep_layout(k, d);
   char* p = static_cast<char*>(prep);
   int grid = (k + 7) / 8;
@@ -521,7 +595,7 @@ extern "C" int b2f_kmeans_prepare(const double* centers, int k, int d, void* pre
                           b2f_cs(stream)>>>(centers, k, d, reinterpret_cast<__half*>(p + L.off_ch16),
                                             reinterpret_cast<const double*>(p + L.off_cn64),
                                             reinterpret_cast<__half*>(p + L.off_cnh),
-                                            reinterpret_cast<float*>(p + L.off_misc));
+                                            reinterpret_cast<float*>(p + L.off_misc), (float)x_norm_max);
   B2F_LAUNCH_CHECK();
   return B2F_OK;
 }

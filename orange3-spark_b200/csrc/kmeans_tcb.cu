@@ -82,6 +82,39 @@ __device__ __forceinline__ float tb_row_scale(float xn, float cmax) {
 }
 
 constexpr int TB_THREADS = 640;
+
+// One 32-column chunk of the fp16 filter's integer-key epilogue: running best / second best of two chains.
+// GS (global key scale, b2f_kmeans_prepare_x): the tensor core has already added the magic constant, the
+// accumulator's bit pattern IS the quantised score and a key costs one integer multiply-add; otherwise the score is
+// first scaled into its row's key window (tb_key: one more multiply-add).
+template <bool GS>
+__device__ __forceinline__ void tb_chunk_keys(const uint32_t (&v)[32], float arow, int col0, int& k1a, int& k2a,
+                                              int& k1b, int& k2b);
+template <bool GS>
+__device__ __forceinline__ void tb_chunk_keys(const uint32_t (&v)[32], float arow, int col0, int& k1a, int& k2a,
+                                              int& k1b, int& k2b) {
+#pragma unroll
+  for (int j4 = 0; j4 < 8; ++j4) {
+    const int col = col0 + j4 * 4;
+    int q0, q1, q2, q3;
+    if (GS) {
+      q0 = (int)v[j4 * 4 + 0] * TB_KEYMUL + col;
+      q1 = (int)v[j4 * 4 + 1] * TB_KEYMUL + col + 1;
+      q2 = (int)v[j4 * 4 + 2] * TB_KEYMUL + col + 2;
+      q3 = (int)v[j4 * 4 + 3] * TB_KEYMUL + col + 3;
+    } else {
+      q0 = tb_key(__uint_as_float(v[j4 * 4 + 0]), arow, col);
+      q1 = tb_key(__uint_as_float(v[j4 * 4 + 1]), arow, col + 1);
+      q2 = tb_key(__uint_as_float(v[j4 * 4 + 2]), arow, col + 2);
+      q3 = tb_key(__uint_as_float(v[j4 * 4 + 3]), arow, col + 3);
+    }
+    const int loa = min(q0, q1), hia = max(q0, q1), lob = min(q2, q3), hib = max(q2, q3);
+    k2a = min(k2a, min(hia, max(k1a, loa)));
+    k1a = min(k1a, loa);
+    k2b = min(k2b, min(hib, max(k1b, lob)));
+    k1b = min(k1b, lob);
+  }
+}
 constexpr int TB_CN_BYTES = 128 * 32;  // the ||c||^2 k-block of a centre tile: 128 centres x 16 halves
 #ifndef TB_REG_CTRL
 // what the epilogue warpgroups gain, (EPI - 96) * 256, must be given back first by the others:
@@ -289,7 +322,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       const int r = i >> 1, pc = i & 1;
       uint4 val = make_uint4(0u, 0u, 0u, 0u);
       if (pc == ((r >> 2) & 1)) {  // 32-byte swizzle: address bit 4 ^= bit 7, i.e. chunk ^= (row >> 2) & 1
-        const __half2 ee = __floats2half2_rn(KM_CNH_E1, KM_CNH_E1), e0 = __floats2half2_rn(KM_CNH_E1, 0.f);
+        // halves 0..2 multiply the three ||c||^2 pieces, half 3 the centre-side half of the magic constant (column 3
+        // of CNH, zero unless the planes were prepared with a global key scale)
+        const __half2 ee = __floats2half2_rn(KM_CNH_E1, KM_CNH_E1), e0 = __floats2half2_rn(KM_CNH_E1, KM_CNH_MA);
         val.x = *reinterpret_cast<const uint32_t*>(&ee);
         val.y = *reinterpret_cast<const uint32_t*>(&e0);
       }
@@ -448,6 +483,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     // fp16 filter: the accumulator holds S^2 * (x . -2c)
     const float inv = H16 ? misc[KM_MISC_INV_SCALE2] : 1.f;
     const float cmax_e = misc[KM_MISC_CMAX];
+    const bool gs = H16 && misc[KM_MISC_SC] > 0.f;  // global key scale: keys come straight out of the accumulator
     uint32_t it = 0, buf = 0, round = 0, par = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       float b1a = INFINITY, b2a = INFINITY, b1b = INFINITY, b2b = INFINITY;
@@ -456,7 +492,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       int B1 = 0x7fffffff, B2 = 0x7fffffff, B3 = 0x7fffffff;  // B3: lower bound of the third best key
       int T1 = 0, T2 = 0;                                     // centre tiles of the best and the second best
       float arow = 1.f;
-      if (H16) {
+      if (H16 && !gs) {
         // the split warps finished this row tile before its first MMA could start: the norms are there
         mbar_wait_ns(&sm->n_full[it & 3], (it >> 2) & 1, 32);
         arow = inv * tb_row_scale(sm->xnorm2[it & 3][row_in_tile], cmax_e);
@@ -489,6 +525,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             tc_fence_before();
             mbar_arrive(&sm->t_empty[cbuf]);
           }
+          if (H16) {  // the accumulator holds S_a S_b (x . -2c + ||c||^2), in global mode + the magic constant
+            if (gs) tb_chunk_keys<true>(v[c & 1], arow, c * 32, k1a, k2a, k1b, k2b);
+            else tb_chunk_keys<false>(v[c & 1], arow, c * 32, k1a, k2a, k1b, k2b);
+          }
           const float4* cn4 = reinterpret_cast<const float4*>(cn + nt * TN + c * 32);
           const int jbase = nt * TN + c * 32;
 #pragma unroll
@@ -496,19 +536,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
 #ifdef TB_EXP_NOMATH  // timing experiment: results invalid
             if (j4 > 0) continue;
 #endif
-            if (H16) {  // the accumulator already holds S^2 (x . -2c + ||c||^2)
-              const int col = c * 32 + j4 * 4;
-              const int q0 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 0]), arow, col);
-              const int q1 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 1]), arow, col + 1);
-              const int q2 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 2]), arow, col + 2);
-              const int q3 = tb_key(__uint_as_float(v[c & 1][j4 * 4 + 3]), arow, col + 3);
-              const int loa = min(q0, q1), hia = max(q0, q1), lob = min(q2, q3), hib = max(q2, q3);
-              k2a = min(k2a, min(hia, max(k1a, loa)));
-              k1a = min(k1a, loa);
-              k2b = min(k2b, min(hib, max(k1b, lob)));
-              k1b = min(k1b, lob);
-              continue;
-            }
+            if (H16) continue;  // (integer keys: handled per chunk above)
             const float4 cv = __ldg(cn4 + j4);
             const float s0 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 0]), inv, cv.x);  // inv is a power of two
             const float s1 = fmaf(__uint_as_float(v[c & 1][j4 * 4 + 1]), inv, cv.y);
@@ -564,6 +592,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     const uint32_t lane_addr = (uint32_t)(w4 * 32) << 16;
     const float S = H16 ? misc[KM_MISC_SCALE] : 1.f;
     const float xlim = 65504.f / S;  // entries beyond this overflow fp16 after scaling
+    // global key scale: a row longer than the norm the planes were built for may leave the key window
+    const float xn_lim = (H16 && misc[KM_MISC_SC] > 0.f) ? misc[KM_MISC_XMAX] * misc[KM_MISC_XMAX] * 1.0001f : INFINITY;
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       float xn = 0.f, amax = 0.f;
@@ -623,7 +653,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
       // four slots: the split warps run up to two tiles ahead of the MMAs, which run ahead of the finish warps
       mbar_wait_ns(&sm->n_empty[it & 3], ((it >> 2) & 1) ^ 1, 128);
-      sm->xnorm2[it & 3][r] = (H16 && !(amax <= xlim)) ? INFINITY : xn;
+      sm->xnorm2[it & 3][r] = (H16 && !(amax <= xlim && xn <= xn_lim)) ? INFINITY : xn;
       mbar_arrive(&sm->n_full[it & 3]);
     }
   } else if (warp < W_XPROD) {
@@ -633,8 +663,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     const int w4 = warp - W_FIN0;
     const int row_in_tile = w4 * 32 + lane;
     const float cmax = misc[KM_MISC_CMAX];
-    const float tau0 = H16 ? kappa0 / misc[KM_MISC_SCALE] : 0.f;  // fp16 underflow term of the bound
+    // fp16 underflow term of the bound: sqrt(d) eta (||x|| / S_b + ||-2c|| / S_a)
+    const float tau0a = H16 ? kappa0 / misc[KM_MISC_SCALE] : 0.f, tau0b = H16 ? kappa0 / misc[KM_MISC_SCALE_B] : 0.f;
     const float inv_s2 = H16 ? misc[KM_MISC_INV_SCALE2] : 0.f;     // (read once: there is no L1 behind these loads)
+    const float sc_glob = H16 ? misc[KM_MISC_SC] : 0.f;            // > 0: one key scale for every row
     double cost = 0.0;
     unsigned long long nrows = 0;
     float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
@@ -686,17 +718,21 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       // 2 * tau for this row: operand rounding (~ ||x|| max||c||), fp16 underflow, and the fp32 roundings of ||c||^2
       // itself and of the final add (~ max||c||^2: matters only for rows much closer to the origin than the centres)
       // (fp16 filter: ||c||^2 enters as three fp16 pieces times 2^15; their underflow adds 3 * 2^-10 / S^2)
-      const float tau2 = kappa2 * xl * cmax + tau0 * (xl + 2.f * cmax) + 3.6e-7f * cmax * cmax +
+      const float tau2 = kappa2 * xl * cmax + tau0b * xl + tau0a * 2.f * cmax + 3.6e-7f * cmax * cmax +
                          (H16 ? 5.9e-3f * inv_s2 : 0.f);
       const int64_t row = tile * TM + row_in_tile;
       const bool live = row < n;
       bool certain = (b2 - b1) > tau2;  // false for NaN as well
       bool pair_ok = false;  // uncertain, but every centre other than the best two is out of reach
       if (H16) {
-        const float sc = tb_row_scale(xn, cmax);
+        // key units per score unit, and what the keys themselves may be off by: per-row scale: one rounding each
+        // (2.5 units for a difference); global scale: the tensor core TRUNCATES when it adds -- 8 accumulations at up
+        // to 1/4 unit, then the k-block with the magic constant, whose five addends are aligned to the constant --
+        // <= 7 units per key, 20 for a difference with room to spare (tau2 * sc is in the thousands)
+        const float sc = sc_glob > 0.f ? sc_glob : tb_row_scale(xn, cmax);
         const float arow = inv_s2 * sc;
-        const float thr = fmaf(tau2, sc, 2.5f);
-        const bool usable = arow > 0.f && arow < INFINITY;
+        const float thr = fmaf(tau2, sc, sc_glob > 0.f ? 20.f : 2.5f);
+        const bool usable = arow > 0.f && arow < INFINITY && xn < INFINITY;
         certain = gap_units > thr && usable;
         pair_ok = !certain && usable && pairs != nullptr && gap3_units > thr && i2 >= 0 && i2 < k && i2 != i1;
       }

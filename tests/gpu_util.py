@@ -23,23 +23,36 @@ def upload_matrix(Xh):
     return X, d, ld
 
 
-def kmeans_state(C, k, d):
+def row_norm_max(X, n, d, ld, col_scale=None):
+    """max ||x|| over the rows (of x * col_scale), as b2f_row_norm_max reports it (fp32, rounded up)."""
+    out = torch.zeros(1, dtype=torch.float32, device=dev())
+    N.check(N.lib().b2f_row_norm_max(N.ptr(X), n, d, ld, N.ptr(col_scale), N.ptr(out), stream()), "row_norm_max")
+    return float(out.item())
+
+
+def kmeans_state(C, k, d, xmax=0.0):
+    """xmax > 0: operands prepared with a global key scale for rows up to that norm (b2f_kmeans_prepare_x)."""
     L = N.lib()
     cen = torch.from_numpy(np.ascontiguousarray(C, dtype=np.float64)).to(dev())
     prep = torch.empty(L.b2f_kmeans_prep_bytes(k, d), dtype=torch.uint8, device=dev())
     acc = torch.empty(L.b2f_kmeans_acc_bytes(k, d), dtype=torch.uint8, device=dev())
-    N.check(L.b2f_kmeans_prepare(N.ptr(cen), k, d, N.ptr(prep), stream()), "prepare")
+    N.check(L.b2f_kmeans_prepare_x(N.ptr(cen), k, d, float(xmax), N.ptr(prep), stream()), "prepare")
     N.check(L.b2f_kmeans_acc_zero(N.ptr(acc), k, d, stream()), "acc_zero")
     return cen, prep, acc
 
 
 def kmeans_step_raw(X, n, d, ld, C, algo, w=None, want_labels=True, ws_bytes=None, info=None, use_ws=False,
-                    col_scale=None):
+                    col_scale=None, global_scale=True, xmax_override=None):
     """One b2f_kmeans_step (or _step_ws for B2F_KM_TCB / B2F_KM_TCH, or any algo with use_ws; _step_scaled with a
-    column scale) + fold.  Returns labels, sums[k,d], counts[k], cost, nrows (host)."""
+    column scale) + fold.  Returns labels, sums[k,d], counts[k], cost, nrows (host).
+    global_scale: prepare the operands with the data's largest row norm (what the fit does); False = the per-row key
+    scales of a plain b2f_kmeans_prepare (what predict on unseen data uses)."""
     L = N.lib()
     k = C.shape[0]
-    cen, prep, acc = kmeans_state(C, k, d)
+    xmax = row_norm_max(X, n, d, ld, col_scale) if (global_scale and n > 0) else 0.0
+    if xmax_override is not None:
+        xmax = xmax_override
+    cen, prep, acc = kmeans_state(C, k, d, xmax)
     labels = torch.full((n,), -1, dtype=torch.int32, device=dev()) if want_labels else None
     if algo in (N.KM_TCB, N.KM_TCH) or use_ws or col_scale is not None:
         wsb = int(L.b2f_kmeans_ws_bytes(n, k, d)) if ws_bytes is None else ws_bytes

@@ -227,6 +227,50 @@ def test_scaled_view_is_not_materialised_by_the_kmeans_pipeline():
     assert view._copy is None and np.isfinite(m2.summary.trainingCost)
 
 
+@pytest.mark.parametrize("n,d,k", [(5000, 128, 256), (30000, 64, 256), (4099, 128, 1024)])
+def test_fp16_filter_with_per_row_key_scales_matches_oracle(n, d, k):
+    """Operands prepared WITHOUT the data's largest row norm (plain b2f_kmeans_prepare, what predict on unseen data
+    uses): the epilogue scales every score into its row's own key window.  Same bar as the global-scale default."""
+    N, G = _imports()
+    Xh = synth.mixture(n, 0, d, SEED, k, 2.0)
+    C = Xh[np.random.default_rng(n + d + k).choice(n, size=k, replace=False)].astype(np.float64)
+    X, _, ld = G.upload_matrix(Xh)
+    info = {}
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCH, info=info, global_scale=False)
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
+    assert nrows == n and counts.sum() == n
+    assert not ((labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)).any()
+    _, rcost, rsums, rcounts = oracle.kmeans_step(Xh.astype(np.float64), C)
+    assert cost == pytest.approx(rcost, rel=1e-5)
+    # the two modes quantise differently but certify alike: about the same number of uncertain rows
+    info_g = {}
+    lab_g = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCH, info=info_g)[0]
+    assert np.array_equal(lab_g, labels) or not ((lab_g != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)).any()
+    assert abs(info_g["uncertain"] - info["uncertain"]) <= 0.1 * max(info["uncertain"], 50)
+
+
+def test_rows_longer_than_the_declared_norm_are_rechecked_not_trusted():
+    """Global key scale built for rows up to HALF the data's largest norm: longer rows may leave the 22-bit key
+    window, so the filter must hand every one of them to the re-check -- and the labels must still be the oracle's."""
+    N, G = _imports()
+    n, d, k = 20000, 128, 256
+    Xh = synth.mixture(n, 0, d, SEED + 4, k, 2.0)
+    Xh[::7] *= np.float32(3.0)  # a seventh of the rows three times as long
+    C = synth.mixture_centers(d, SEED + 4, k, 2.0).astype(np.float64)
+    X, _, ld = G.upload_matrix(Xh)
+    norms = np.sqrt((Xh.astype(np.float64) ** 2).sum(1))
+    limit = 0.5 * norms.max()
+    info = {}
+    labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, N.KM_TCH, info=info, xmax_override=limit,
+                                                          ws_bytes=int(N.lib().b2f_kmeans_ws_bytes(8 * n, k, d)))
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(Xh.astype(np.float64), C, return_second=True)
+    assert nrows == n and counts.sum() == n
+    assert info["listed"] >= int((norms > limit * 1.001).sum())  # every long row went to the 3xTF32 re-check
+    assert not ((labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)).any()
+    _, rcost, _, rcounts = oracle.kmeans_step(Xh.astype(np.float64), C)
+    assert cost == pytest.approx(rcost, rel=1e-5)
+
+
 def _fp64_sums_from_labels(X, labels, k, d, col_scale=None, chunk=2_000_000):
     """Test-side reference: sums[k, d] and counts re-accumulated in fp64 on the device from the labels the step
     produced (torch.index_add_ in double; independent of every kernel of the library)."""
