@@ -59,6 +59,10 @@ __global__ void km_prepare_h16_kernel(const double* __restrict__ C, int k, int d
                                       float* __restrict__ misc, float xmax) {
   const float cabs = misc[KM_MISC_CABS];
   const float cmax = misc[KM_MISC_CMAX];
+  // The key window is sized for rows up to 8 max||c||: a few outliers far beyond every centre must not coarsen the
+  // quantisation for everybody else (one key unit is R / 2^21); longer rows are flagged by the split warps and go to
+  // the re-check like rows whose entries overflow fp16.
+  xmax = fminf(xmax, 8.f * cmax);
   int ea = 0, eb = 0;  // S_a = 2^ea (x operand), S_b = 2^eb (centre operand)
   bool global = false;
   if (cabs > 0.f) {

@@ -16,6 +16,8 @@ ap.add_argument("--d", type=int, default=128)
 ap.add_argument("--k", type=int, default=1024)
 ap.add_argument("--algo", type=int, default=2)
 ap.add_argument("--reps", type=int, default=5)
+ap.add_argument("--per-row", action="store_true", help="plain b2f_kmeans_prepare (per-row key scales) instead of "
+                                                         "b2f_kmeans_prepare_x with the data's largest row norm")
 ap.add_argument("--predict", action="store_true", help="labels only (no accumulation)")
 ap.add_argument("--predict-ws", action="store_true", help="labels only through the certainty pipeline (filter pass "
                                                             "without accumulation)")
@@ -29,7 +31,17 @@ idx = torch.from_numpy(np.random.default_rng(0).choice(a.n, a.k, replace=False))
 C = X[idx].double().contiguous()
 prep = torch.empty(L.b2f_kmeans_prep_bytes(a.k, a.d), dtype=torch.uint8, device=dev)
 acc = torch.empty(L.b2f_kmeans_acc_bytes(a.k, a.d), dtype=torch.uint8, device=dev)
-N.check(L.b2f_kmeans_prepare(N.ptr(C), a.k, a.d, N.ptr(prep), N.stream_ptr()), "prep")
+xm = torch.zeros(1, dtype=torch.float32, device=dev)
+if not a.per_row:
+    N.check(L.b2f_row_norm_max(N.ptr(X), a.n, a.d, a.d, None, N.ptr(xm), N.stream_ptr()), "row_norm_max")
+XMAX = float(xm.item())
+
+
+def prepare():
+    N.check(L.b2f_kmeans_prepare_x(N.ptr(C), a.k, a.d, XMAX, N.ptr(prep), N.stream_ptr()), "prep")
+
+
+prepare()
 lab = torch.empty(a.n, dtype=torch.int32, device=dev)
 wsb = int(L.b2f_kmeans_ws_bytes(a.n, a.k, a.d))
 ws = torch.zeros(wsb, dtype=torch.uint8, device=dev)
@@ -42,7 +54,7 @@ for i in range(a.lloyd):
     N.check(L.b2f_kmeans_fold(N.ptr(acc), a.k, a.d, N.stream_ptr()), "fold")
     N.check(L.b2f_kmeans_finalize(N.ptr(acc), a.k, a.d, 0.0, N.ptr(C), N.ptr(status), N.ptr(status_f64),
                                   N.stream_ptr()), "finalize")
-    N.check(L.b2f_kmeans_prepare(N.ptr(C), a.k, a.d, N.ptr(prep), N.stream_ptr()), "prep")
+    prepare()
 ts = []
 for i in range(a.reps + 2):
     N.check(L.b2f_kmeans_acc_zero(N.ptr(acc), a.k, a.d, N.stream_ptr()), "zero")
