@@ -346,10 +346,18 @@ def e2e_leg(args, torch, Xt, C0, n, d, k, comm, ColumnarFrame, VectorAssembler, 
     comm.all_reduce_max(t)
     dt = float(t.item())
     assert len(centers) == k and model.summary.numIter == iters
+    hist = model.summary.costHistory
+    # full-size invariants: the Lloyd cost never increases, every row is in exactly one cluster
+    monotone = all(b <= a * (1.0 + 1e-7) for a, b in zip(hist, hist[1:]))
+    sizes = torch.tensor([float(sum(model.summary.clusterSizes))], dtype=torch.float64, device=Xt.device)
+    rows = torch.tensor([float(n)], dtype=torch.float64, device=Xt.device)
+    comm.all_reduce_sum(rows)
     scale = n / float(n_full)  # 1.0 unless host RAM forced a smaller e2e sample
     return {"value": iters / dt * scale, "unit": "iter/s", "rows_used": n, "rows_full": n_full,
             "host_ram_limited": n != n_full, "h2d_bytes_per_step": n * d * 4 / iters,
             "d2h_bytes_per_step": (k * d * 8 + 24 * iters) / iters, "iterations": iters, "seconds": dt,
+            "check": {"cost_non_increasing_over_the_fit": bool(monotone), "cost_first": hist[0], "cost_last": hist[-1],
+                      "cluster_sizes_sum_to_rows": bool(float(sizes.item()) == float(rows.item()))},
             "what": "VectorAssembler.transform(host pinned columns) + KMeans.fit(maxIter=20, tol=0) + clusterCenters(); "
                     "the one H2D of X is amortised over the fit's 20 iterations"}
 

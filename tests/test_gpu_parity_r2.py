@@ -349,6 +349,38 @@ def test_full_size_accumulation_matches_fp64_reaccumulation(n, d, k, comps, scal
     assert float(p[kd + k].item()) == pytest.approx(ref_cost, rel=1e-5)
 
 
+def test_full_size_labels_of_the_filter_pipeline_equal_the_3xtf32_pipeline():
+    """20M x 128, k = 1024: the fp16 filter pipeline (filter, pair check, re-check, fp64 tail) and the independent
+    3xTF32 pipeline (3xTF32 scores with their own certainty test, fp64 tail) both claim fp64-exact labels, by
+    different arithmetic; at a size the oracle cannot reach they must give the SAME label for every row, the same
+    counts, and costs equal to 1e-6."""
+    N, G = _imports()
+    L = N.lib()
+    n, d, k = 20_000_000, 128, 1024
+    free, _ = torch.cuda.mem_get_info()
+    if free < n * d * 4 * 1.8:
+        pytest.skip("not enough free device memory for the full-size check")
+    X = torch.empty((n, d), dtype=torch.float32, device=G.dev())
+    N.check(L.b2f_synth_mixture(N.ptr(X), n, 0, d, d, SEED, k, 2.0, None, G.stream()), "synth")
+    idx = torch.from_numpy(np.random.default_rng(4).choice(n, size=k, replace=False)).to(G.dev())
+    C = X[idx, :].double().cpu().numpy()
+    C[17] = C[900] + 1e-4  # a near-duplicate pair: a band of torn rows on top of the natural ones
+    out = {}
+    for name, algo in (("filter", N.KM_TCH), ("tc3", N.KM_TC3)):
+        info = {}
+        labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, d, C, algo, use_ws=True, info=info)
+        assert nrows == n and counts.sum() == n, name
+        out[name] = (labels, counts, cost, info)
+    lf, lt = out["filter"][0], out["tc3"][0]
+    diff = int((lf != lt).sum())
+    print("\nfull-size label agreement: %d of %d rows differ; filter: %s; 3xTF32: %s" % (diff, n, out["filter"][3],
+                                                                                       out["tc3"][3]))
+    assert diff == 0
+    assert np.array_equal(out["filter"][1], out["tc3"][1])
+    assert out["filter"][2] == pytest.approx(out["tc3"][2], rel=1e-6)
+    assert out["filter"][3]["pairs"] > n // 200 and out["tc3"][3]["exact"] > 0
+
+
 def test_full_size_multinomial_gradient_matches_fp64_reference():
     """cfg-4 size (20M x 512, 20 classes): the tensor-core pass keeps G^T in an fp32 tensor-memory accumulator for
     the CTA's whole life (~135 000 rows) and forms the products from bf16 pieces.  Reference: fp64 softmax and fp64
