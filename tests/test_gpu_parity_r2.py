@@ -353,7 +353,7 @@ def test_full_size_labels_of_the_filter_pipeline_equal_the_3xtf32_pipeline():
     """20M x 128, k = 1024: the fp16 filter pipeline (filter, pair check, re-check, fp64 tail) and the independent
     3xTF32 pipeline (3xTF32 scores with their own certainty test, fp64 tail) both claim fp64-exact labels, by
     different arithmetic; at a size the oracle cannot reach they must give the SAME label for every row, the same
-    counts, and costs equal to 1e-6."""
+    counts, and costs equal to 1e-5 (the 3xTF32 kernel forms its cost per row in fp32)."""
     N, G = _imports()
     L = N.lib()
     n, d, k = 20_000_000, 128, 1024
@@ -377,7 +377,7 @@ def test_full_size_labels_of_the_filter_pipeline_equal_the_3xtf32_pipeline():
                                                                                        out["tc3"][3]))
     assert diff == 0
     assert np.array_equal(out["filter"][1], out["tc3"][1])
-    assert out["filter"][2] == pytest.approx(out["tc3"][2], rel=1e-6)
+    assert out["filter"][2] == pytest.approx(out["tc3"][2], rel=1e-5)
     assert out["filter"][3]["pairs"] > n // 200 and out["tc3"][3]["exact"] > 0
 
 
