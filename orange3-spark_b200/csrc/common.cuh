@@ -105,7 +105,9 @@ static inline KmPrepLayout km_prep_layout(int k, int d) {
 // acc:   [ payload double[k*d + k + 2] = sums | counts | cost | nrows
 //          rep     float[KM_REPLICAS * k * d]   fp32 replicas written with red.global.add
 //          cnt32   unsigned long long[k]        integer counts (unweighted fast path)        ]
+#ifndef KM_REPLICAS
 #define KM_REPLICAS 4
+#endif
 struct KmAccLayout {
   size_t off_payload, off_rep, off_cnt, bytes;
   size_t payload_len;

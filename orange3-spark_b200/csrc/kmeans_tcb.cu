@@ -82,6 +82,19 @@ __device__ __forceinline__ float tb_row_scale(float xn, float cmax) {
 }
 
 constexpr int TB_THREADS = 640;
+// Rows per centre are counted in shared memory (one int per centre behind SmemB, added to the global counters once at
+// the end of the kernel) up to this many centres; beyond it the counters would cost a centre stage.
+constexpr int TB_CNT_SMEM_MAX = 1024;
+static inline int tcb_cnt_smem_bytes(int k) { return k <= TB_CNT_SMEM_MAX ? k * 4 : 0; }
+// RFS ("reduce from staging", d = 64 only): the fp32 staging area holds TB_NX whole row tiles (32 KB each at d = 64)
+// instead of one, a tile stays there until its labels exist, and the finish warps add each certain row straight from
+// it with two TMA tensor reductions (one per 128-byte chunk; the engine undoes the 128B swizzle) into the replica
+// row of its label: no second read of X from L2, no row slots, no copy batches.  At d = 64 a row tile has only two
+// centre tiles and the accumulation is most of the step (pipeline without it: 10.9 ms per 100M rows, with it 24-25).
+#ifndef TB_NX_V
+#define TB_NX_V 4
+#endif
+constexpr int TB_NX = TB_NX_V;
 
 // One 32-column chunk of the fp16 filter's integer-key epilogue: running best / second best of two chains.
 // GS (global key scale, b2f_kmeans_prepare_x): the tensor core has already added the magic constant, the
@@ -150,7 +163,7 @@ constexpr int W_FIN0 = 12;   // warps 12-15 finish
 constexpr int W_XPROD = 16, W_MMA = 17, W_BPROD = 18, W_ALLOC = 19;  // W_ALLOC: TMEM allocator + second MMA issuer
 
 struct SmemB {
-  uint64_t xs_full[4], xs_empty[4];  // fp32 staging, per 32-float chunk
+  uint64_t xs_full[8], xs_empty[4];  // fp32 staging, per 32-float chunk (RFS: xs_full[slot * KC + kc], xs_empty[slot])
   uint64_t xa_full[2], xa_empty[2];  // TMEM operand, per row-tile buffer
   uint64_t b_full[4], b_empty[4];    // centre-operand stages (a stage = one whole centre tile)
   uint64_t t_full[3], t_empty[3];    // accumulators
@@ -261,10 +274,11 @@ struct TbAcc {
   }
 };
 
-template <int MODE, bool TRACE, bool SCALED>
+template <int MODE, bool TRACE, bool SCALED, bool RFS>
 __global__ void __launch_bounds__(TB_THREADS, 1)
     km_tcb_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c1,
-                  const __grid_constant__ CUtensorMap map_c2, const float* __restrict__ X, int64_t n, int d,
+                  const __grid_constant__ CUtensorMap map_c2, const __grid_constant__ CUtensorMap map_rep,
+                  const float* __restrict__ X, int64_t n, int d,
                   int64_t ld, const float* __restrict__ colscale, const float* __restrict__ cn,
                   const float* __restrict__ misc, float kappa2, float kappa0, int k, int nstages,
                   double* __restrict__ payload, float* __restrict__ rep, unsigned long long* __restrict__ cnt,
@@ -283,20 +297,25 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   const int KC = d / 32;  // fp32 staging chunks
   const int KA = d / 64;  // 64-k atoms of the 16-bit operands
   uint8_t* xs = smem_raw;
-  uint8_t* stages = xs + (size_t)KC * CHUNK_BYTES;
+  uint8_t* stages = xs + (size_t)(RFS ? TB_NX : 1) * KC * CHUNK_BYTES;
   // fp16: constant x-side k-block (128 rows x 16 halves, 32-byte swizzle; halves 0..2 of every row = 2^15)
   uint8_t* aconst = stages + (size_t)nstages * TB_TILE_BYTES;
   // fp16: row buffers of the finish warps: 4 warps x 2 slots x TB_FX_ROWS rows of d floats
   uint8_t* fxbuf = aconst + (H16 ? TB_CN_BYTES : 0);
-  SmemB* sm = reinterpret_cast<SmemB*>(fxbuf + (H16 ? TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4 : 0));
+  SmemB* sm = reinterpret_cast<SmemB*>(fxbuf + ((H16 && !RFS) ? TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4 : 0));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t ntiles = (n + TM - 1) / TM;
   const int NT = k / TN;
+  int* cnt_s = reinterpret_cast<int*>(sm + 1);  // k <= TB_CNT_SMEM_MAX: per-centre row counts of this CTA
+  const bool cnt_smem = k <= TB_CNT_SMEM_MAX;
+  if (cnt_smem)
+    for (int i = threadIdx.x; i < k; i += TB_THREADS) cnt_s[i] = 0;
 
   if (threadIdx.x == 0) {
     for (int c = 0; c < 4; ++c) {
       mbar_init(&sm->xs_full[c], 1);
+      mbar_init(&sm->xs_full[4 + c], 1);
       mbar_init(&sm->xs_empty[c], EPI_THREADS);
       mbar_init(&sm->b_full[c], 1);
       mbar_init(&sm->b_empty[c], 1);
@@ -356,6 +375,16 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     if (lane == 0) {
       uint32_t it = 0;
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        if (RFS) {  // ring of TB_NX whole tiles; a slot comes back from the finish warps (their reductions have read it)
+          const uint32_t slot = it % TB_NX;
+          mbar_wait_ns(&sm->xs_empty[slot], ((it / TB_NX) & 1) ^ 1, 128);
+          for (int kc = 0; kc < KC; ++kc) {
+            mbar_expect_tx(&sm->xs_full[slot * KC + kc], (uint32_t)CHUNK_BYTES);
+            tma_load_2d_hint(xs + (size_t)(slot * KC + kc) * CHUNK_BYTES, &map_x, kc * 32, (int)(tile * TM),
+                             &sm->xs_full[slot * KC + kc], L2_EVICT_FIRST);
+          }
+          continue;
+        }
         for (int kc = 0; kc < KC; ++kc) {
           mbar_wait_ns(&sm->xs_empty[kc], (it & 1) ^ 1, 128);
           mbar_expect_tx(&sm->xs_full[kc], (uint32_t)CHUNK_BYTES);
@@ -603,8 +632,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int kc = 2 * a + h;
-          mbar_wait_ns(&sm->xs_full[kc], it & 1, 64);
-          const uint8_t* src = xs + (size_t)kc * CHUNK_BYTES + (size_t)r * 128;
+          const uint32_t xslot = RFS ? (it % TB_NX) * KC + kc : kc;
+          mbar_wait_ns(&sm->xs_full[xslot], RFS ? ((it / TB_NX) & 1) : (it & 1), 64);
+          const uint8_t* src = xs + (size_t)xslot * CHUNK_BYTES + (size_t)r * 128;
 #pragma unroll
           for (int p = 0; p < 8; ++p) {
             float4 v = *reinterpret_cast<const float4*>(src + ((p ^ (r & 7)) << 4));
@@ -636,7 +666,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           // arithmetic consuming them can be scheduled below it).  Found in the multinomial LR kernel, where it
           // showed; the same hand-off here never failed a repeatability test, and costs nothing to close.
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-          mbar_arrive(&sm->xs_empty[kc]);
+          if (!RFS) mbar_arrive(&sm->xs_empty[kc]);  // (RFS: the finish warps hand the whole tile back)
         }
         const uint32_t xb = it % XBUFS;
         if (w4 == 0) TR(9, 1 + 3 * a);
@@ -742,8 +772,20 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       // The copies of the first two batches of certain rows go out NOW: the list appends below are atomics whose
       // return value is an L2 round trip (~94 % of the warp-tiles have a pair row at cfg 2), and that wait then
       // overlaps the copies instead of preceding them.
+      if (RFS) {
+        // The row tile is still in its staging slot: two tensor reductions per certain row, straight from the
+        // (swizzled) chunks into the replica row of the label.  The slot goes back to the producer after the list
+        // appends below, whose atomics' round trip covers the engine's read of the source.
+        if (accumulate && my_lab >= 0) {
+          const uint32_t slot = it % TB_NX;
+          const int rrow = (int)(blockIdx.x % KM_REPLICAS) * k + my_lab;
+          for (int kc = 0; kc < KC; ++kc)
+            tma_reduce_add_2d(&map_rep, kc * 32, rrow, xs + (size_t)(slot * KC + kc) * CHUNK_BYTES + (size_t)row_in_tile * 128);
+        }
+        bulk_commit();
+      }
       TbAcc acc_rows;
-      if (H16 && accumulate) {
+      if (H16 && accumulate && !RFS) {
         acc_rows.X = X; acc_rows.n = n; acc_rows.ld = ld; acc_rows.r0 = r0; acc_rows.d = d; acc_rows.lane = lane;
         acc_rows.myrep = myrep;
         acc_rows.mybuf = fxbuf + (size_t)w4 * 2 * TB_FX_ROWS * d * 4;
@@ -779,11 +821,15 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         }
       }
       if (w4 == 0) TR(10, 2);
+      if (RFS) {
+        bulk_wait_read<0>();
+        mbar_arrive(&sm->xs_empty[it % TB_NX]);
+      }
       if (!accumulate) continue;
       // bf16x3: squared distance to the chosen centre.  fp16: ||x||^2 only -- the remaining part of the cost,
       // sum_j (n_j ||c_j||^2 - 2 c_j . S_j), is added exactly from the sums (tcb_cost_terms_kernel)
       const float my_sc = H16 ? xn : fmaxf(xn + b1, 0.f);
-      if (H16) acc_rows.finish(fxc);
+      if (H16 && !RFS) acc_rows.finish(fxc);
       // TB_FIN_ROWS rows in flight per warp: the re-reads come from L2 (~800 cycles each way under load) and this
       // loop, not the epilogue, set the pace of the whole kernel at 8 rows in flight (hand-off trace)
       for (int g = 0; g < (H16 ? 0 : 32); g += TB_FIN_ROWS) {
@@ -805,7 +851,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
       if (my_lab >= 0) {
         cost += (double)my_sc;
-        atomicAdd(cnt + my_lab, 1ull);
+        // (measured at k = 256, 40M rows: one global count atomic per row cost 2.7 ms of a 10.2 ms step -- 256 hot
+        // addresses -- against 1.6 ms for the row sums themselves)
+        if (cnt_smem) atomicAdd(&cnt_s[my_lab], 1);
+        else atomicAdd(cnt + my_lab, 1ull);
         ++nrows;
       }
       if (w4 == 0) TR(10, 3);
@@ -824,6 +873,11 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   }
   tc_fence_before();
   __syncthreads();
+  if (accumulate && cnt_smem)
+    for (int i = threadIdx.x; i < k; i += TB_THREADS) {
+      const int c = cnt_s[i];
+      if (c) atomicAdd(cnt + i, (unsigned long long)c);
+    }
   if (warp == W_ALLOC) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TB_TMEM_COLS)
                  : "memory");
@@ -1006,14 +1060,22 @@ static int tcb_cap_from_bytes(size_t bytes, int d) {
 static int tcb_tile_bytes(int d, int filter) {
   return filter == KM_FILTER_FP16 ? (d / 64) * CHUNK_BYTES + TB_CN_BYTES : (d / 64) * tb_stage_bytes<KM_FILTER_BF16X3>();
 }
-static int km_tcb_stages(int d, int filter) {
-  const int fx_bytes = TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4;  // row slots of the finish warps (fp16 filter)
+static bool tcb_rfs(int d, int filter) {
+#ifdef B2F_DEV
+  if (getenv("B2F_TC_NO_RFS")) return false;
+#endif
+  return filter == KM_FILTER_FP16 && d == 64;
+}
+static int km_tcb_stages(int k, int d, int filter) {
+  const bool rfs = tcb_rfs(d, filter);
+  // row slots of the finish warps (fp16 filter; none when they reduce from the staging ring)
+  const int fx_bytes = rfs ? 0 : TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4;
   int budget_kb = 227, cap = 4;
 #ifdef B2F_DEV  // dev knobs of the timing experiments; not in the product build
   if (filter == KM_FILTER_FP16 && getenv("B2F_TC_SMEM_KB")) budget_kb = atoi(getenv("B2F_TC_SMEM_KB"));
   if (getenv("B2F_TC_STAGES")) cap = atoi(getenv("B2F_TC_STAGES"));
 #endif
-  const int left = budget_kb * 1024 - (int)sizeof(SmemB) - 64 - (d / 32) * CHUNK_BYTES -
+  const int left = budget_kb * 1024 - (int)sizeof(SmemB) - tcb_cnt_smem_bytes(k) - 64 - (rfs ? TB_NX : 1) * (d / 32) * CHUNK_BYTES -
                    (filter == KM_FILTER_FP16 ? TB_CN_BYTES + fx_bytes : 0);
   // a stage holds one centre tile: d / 64 atoms, fp16: + the ||c||^2 block
   int s = left / tcb_tile_bytes(d, filter);
@@ -1024,7 +1086,8 @@ bool km_tcb_supported(int k, int d, int64_t ld) {
   if (d != 64 && d != 128) return false;  // whole 64-k atoms, X hi/lo pairs fit the tensor memory budget
   if (k % TN != 0 || k < TN) return false;
   if (ld % 4 != 0) return false;
-  return km_tcb_stages(d, KM_FILTER_BF16X3) >= 2 && km_tcb_stages(d, KM_FILTER_FP16) >= 2 && km_tc_supported(k, d, ld);
+  return km_tcb_stages(k, d, KM_FILTER_BF16X3) >= 2 && km_tcb_stages(k, d, KM_FILTER_FP16) >= 2 &&
+         km_tc_supported(k, d, ld);
 }
 
 size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
@@ -1032,9 +1095,9 @@ size_t km_tcb_ws_bytes(int64_t n, int k, int d) {
   return tcb_ws_layout(tcb_cap_for_rows(n), d).bytes;
 }
 
-template <int MODE, bool SCALED>
+template <int MODE, bool SCALED, bool RFS>
 static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const CUtensorMap& mx, const CUtensorMap& m1,
-                             const CUtensorMap& m2, const float* X, int64_t n, int d, int64_t ld, const float* colscale,
+                             const CUtensorMap& m2, const CUtensorMap& mr, const float* X, int64_t n, int d, int64_t ld, const float* colscale,
                              const float* cn, const float* misc, float kappa2, float kappa0, int k, int nstages,
                              double* payload, float* rep, unsigned long long* cnt, int32_t* labels, int accumulate,
                              TcbWs* hdr, int32_t* amb_idx, int cap, int4* pairs, int pcap) {
@@ -1045,9 +1108,9 @@ static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const C
   if (trace_path) {
     B2F_CUDA(cudaMalloc(&trace, trace_bytes));
     B2F_CUDA(cudaMemsetAsync(trace, 0, trace_bytes, stream));
-    auto kern = km_tcb_kernel<MODE, true, SCALED>;
+    auto kern = km_tcb_kernel<MODE, true, SCALED, RFS>;
     B2F_CUDA(b2f_smem_attr(kern, smem));
-    kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
+    kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, mr, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
                                              payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, trace);
     B2F_LAUNCH_CHECK();
     std::vector<unsigned long long> host(trace_bytes / sizeof(unsigned long long));
@@ -1061,9 +1124,9 @@ static int tcb_launch_filter(int grid, size_t smem, cudaStream_t stream, const C
     return B2F_OK;
   }
 #endif
-  auto kern = km_tcb_kernel<MODE, false, SCALED>;
+  auto kern = km_tcb_kernel<MODE, false, SCALED, RFS>;
   B2F_CUDA(b2f_smem_attr(kern, smem));
-  kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
+  kern<<<grid, TB_THREADS, smem, stream>>>(mx, m1, m2, mr, X, n, d, ld, colscale, cn, misc, kappa2, kappa0, k, nstages,
                                            payload, rep, cnt, labels, accumulate, hdr, amb_idx, cap, pairs, pcap, trace);
   B2F_LAUNCH_CHECK();
   return B2F_OK;
@@ -1120,8 +1183,9 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
   int4* pairs = reinterpret_cast<int4*>(wp + W.off_pairs);
   float* Xamb = reinterpret_cast<float*>(wp + W.off_x);
   const bool h16 = filter == KM_FILTER_FP16;
-  const int fx_bytes = TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4;
-  const int nstages = km_tcb_stages(d, filter);
+  const bool rfs = tcb_rfs(d, filter);
+  const int fx_bytes = rfs ? 0 : TB_FX_WARPS * 2 * TB_FX_ROWS * d * 4;
+  const int nstages = km_tcb_stages(k, d, filter);
   B2F_REQUIRE(nstages >= 2, "b2f_kmeans (filter path): k = %d, d = %d does not fit in shared memory", k, d);
   CUtensorMap mx, m1, m2;
   int rc;
@@ -1156,8 +1220,14 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
 #ifdef B2F_DEV
   if (getenv("B2F_TC_DBG") && (atoi(getenv("B2F_TC_DBG")) & 4)) acc_main = false;  // results invalid when set
 #endif
-  const size_t smem = (size_t)(d / 32) * CHUNK_BYTES + (size_t)nstages * tcb_tile_bytes(d, filter) +
-                      (h16 ? TB_CN_BYTES + fx_bytes : 0) + sizeof(SmemB) + 64;
+  // RFS: the replicas as ONE [KM_REPLICAS * k, d] tensor, boxes of one row x 32 floats in the staging swizzle
+  CUtensorMap mr = mx;
+  if (rfs && rep &&
+      (rc = make_map_2d(&mr, rep, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (uint64_t)KM_REPLICAS * k, (uint64_t)d, (uint64_t)d,
+                        1)) != B2F_OK)
+    return rc;
+  const size_t smem = (size_t)(rfs ? TB_NX : 1) * (d / 32) * CHUNK_BYTES + (size_t)nstages * tcb_tile_bytes(d, filter) +
+                      (h16 ? TB_CN_BYTES + fx_bytes : 0) + sizeof(SmemB) + tcb_cnt_smem_bytes(k) + 64;
   const int64_t ntiles = (n + TM - 1) / TM;
   int grid = b2f_sm_count();
   if ((int64_t)grid > ntiles) grid = (int)ntiles;
@@ -1169,14 +1239,13 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
     // the raw sums are folded through the scale right after the kernel, so everything downstream sees scaled sums
     if (acc_main && colscale && (rc = km_fold_scaled(acc, k, d, nullptr, stream)) != B2F_OK) return rc;
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, -1.0);
-    if (colscale)
-      rc = tcb_launch_filter<KM_FILTER_FP16, true>(grid, smem, stream, mx, m1, m2, X, n, d, ld, colscale, cn, misc, kappa2,
-                                                   kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
-                                                   amb_idx, cap, pairs, cap);
-    else
-      rc = tcb_launch_filter<KM_FILTER_FP16, false>(grid, smem, stream, mx, m1, m2, X, n, d, ld, nullptr, cn, misc, kappa2,
-                                                    kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
-                                                    amb_idx, cap, pairs, cap);
+#define TCB_H16(SC, RF)                                                                                              \
+  tcb_launch_filter<KM_FILTER_FP16, SC, RF>(grid, smem, stream, mx, m1, m2, mr, X, n, d, ld, colscale, cn, misc, kappa2, \
+                                            kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,     \
+                                            amb_idx, cap, pairs, cap)
+    if (colscale) rc = rfs ? TCB_H16(true, true) : TCB_H16(true, false);
+    else rc = rfs ? TCB_H16(false, true) : TCB_H16(false, false);
+#undef TCB_H16
     if (rc != B2F_OK) return rc;
     if (acc_main && colscale && (rc = km_fold_scaled(acc, k, d, colscale, stream)) != B2F_OK) return rc;
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, 1.0);
@@ -1185,7 +1254,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
                                                                  labels, hdr, pairs, cap, accumulate ? 1 : 0);
     B2F_LAUNCH_CHECK();
   } else {
-    rc = tcb_launch_filter<KM_FILTER_BF16X3, false>(grid, smem, stream, mx, m1, m2, X, n, d, ld, nullptr, cn, misc, kappa2,
+    rc = tcb_launch_filter<KM_FILTER_BF16X3, false, false>(grid, smem, stream, mx, m1, m2, mr, X, n, d, ld, nullptr, cn, misc, kappa2,
                                                     kappa0, k, nstages, payload, rep, cnt, labels, acc_main ? 1 : 0, hdr,
                                                     amb_idx, cap, nullptr, 0);
     if (rc != B2F_OK) return rc;

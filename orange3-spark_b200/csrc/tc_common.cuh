@@ -110,6 +110,12 @@ __device__ __forceinline__ void bulk_reduce_add_f32(float* dst, const void* src_
                "r"(smem_u32(src_smem)), "r"(bytes)
                : "memory");
 }
+// one box of a tensor map: global[map, {c0, c1}] += shared box (fp32 add; the engine undoes the map's swizzle)
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, int c0, int c1, const void* src_smem) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
+               "r"(smem_u32(src_smem)), "r"(c0), "r"(c1)
+               : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all but the newest N groups of this thread have finished READING their shared-memory source
 template <int N> __device__ __forceinline__ void bulk_wait_read() {
