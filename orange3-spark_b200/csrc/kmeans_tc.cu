@@ -33,7 +33,7 @@ struct Smem {
   uint64_t b_full[8], b_empty[8];
   uint64_t t_full[2], t_empty[2];
   uint64_t a_full[2], a_empty[2];  // epilogue -> accumulate hand-off (labels / scores of one row tile)
-  uint64_t n_full[2];              // split -> epilogue: squared row norms (only used by the certainty test)
+  uint64_t n_full[2], n_empty[2];  // split -> epilogue: squared row norms (only used by the certainty test)
   uint32_t tmem_base;
   int lab[2][TM];                  // label, or -1 for a row handed to the exact re-check
   float score[2][TM];
@@ -80,6 +80,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       mbar_init(&sm->a_full[b], EPI_THREADS);
       mbar_init(&sm->a_empty[b], EPI_THREADS);
       mbar_init(&sm->n_full[b], EPI_THREADS);
+      mbar_init(&sm->n_empty[b], EPI_THREADS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -241,6 +242,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         // (second term: fp32 roundings of ||c||^2 and of the final add, relevant for rows near the origin)
         const float cmx = *rck.cmax;
         const float tau2 = rck.kappa2 * sqrtf(sm->xnorm2[it & 1][row_in_tile]) * cmx + 3.6e-7f * cmx * cmx;
+        mbar_arrive(&sm->n_empty[it & 1]);
         certain = (b2 - b1) > tau2;
         const bool list_it = row < n && !certain;
         const unsigned m = __ballot_sync(0xffffffffu, list_it);
@@ -300,6 +302,12 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         tc_fence_before();
         mbar_arrive(&sm->xa_full[kc]);
       }
+      // The slot is read by the epilogue's certainty test AFTER it has released the tile's last accumulator, and
+      // nothing else holds the split warps back from being two row tiles ahead by then (one centre tile per row
+      // tile: wide open; more: a short window).  Without this wait the norms of tile it - 2 could be overwritten
+      // and n_full run two phases ahead of its waiter, whose parity wait then never returns (seen as a time-out
+      // at k = 128 with a few row tiles per CTA).
+      if (rck.count) mbar_wait(&sm->n_empty[it & 1], ((it >> 1) & 1) ^ 1);
       sm->xnorm2[it & 1][r] = xn;  // read by the epilogue's certainty test after this tile's last centre tile
       mbar_arrive(&sm->n_full[it & 1]);
     }

@@ -95,6 +95,11 @@ static inline int tcb_cnt_smem_bytes(int k) { return k <= TB_CNT_SMEM_MAX ? k * 
 #define TB_NX_V 4
 #endif
 constexpr int TB_NX = TB_NX_V;
+// Tried on top of it and not kept: a per-CTA [k, d] fp32 table of the sums in shared memory for k * d <= 16K (finish
+// warp w owns the centres with label % 4 == w and adds their rows with plain loads / stores, no atomics, nothing per
+// row to L2): 11.3 ms per 40M rows at k = 256 against 7.9 ms with the tensor reductions -- the table walk (a ballot
+// scan of the tile's 128 labels plus ~32 dependent load-add-store rounds per warp and tile) costs the finish warps
+// more than handing the rows to the copy engine does.
 
 // One 32-column chunk of the fp16 filter's integer-key epilogue: running best / second best of two chains.
 // GS (global key scale, b2f_kmeans_prepare_x): the tensor core has already added the magic constant, the
@@ -311,6 +316,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   const bool cnt_smem = k <= TB_CNT_SMEM_MAX;
   if (cnt_smem)
     for (int i = threadIdx.x; i < k; i += TB_THREADS) cnt_s[i] = 0;
+  // k <= 128 * nstages: every centre tile has a stage of its own -- loaded once, never released, instead of once per
+  // row tile (at k = 256, d = 64 that was 40 KB of L2 reads per 32 KB row tile)
+  const bool bres = NT <= nstages;
 
   if (threadIdx.x == 0) {
     for (int c = 0; c < 4; ++c) {
@@ -399,8 +407,9 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     if (lane == 0) {
       uint32_t s = 0, ph = 0, it = 0;
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        if (bres && it > 0) break;  // resident centre tiles: one load each for the whole kernel
         for (int nt = 0; nt < NT; ++nt) {
-          mbar_wait_ns(&sm->b_empty[s], ph ^ 1, 64);
+          if (!bres) mbar_wait_ns(&sm->b_empty[s], ph ^ 1, 64);
           if (nt < 8) TR(11, nt);
           mbar_expect_tx(&sm->b_full[s], (uint32_t)(KA * TB_STAGE_BYTES + (H16 ? TB_CN_BYTES : 0)));
           for (int a = 0; a < KA; ++a) {
@@ -440,7 +449,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         const bool mine = gpar == mp;
         const bool very_first = (it == 0 && nt == 0);
         gpar ^= 1u;
-        const uint32_t cbuf = buf, cround = round, cstage = stage, cbphase = bphase;
+        // (resident centre tiles: tile nt sits in stage nt, whose barrier completed its only phase long ago)
+        const uint32_t cbuf = buf, cround = round, cstage = bres ? (uint32_t)nt : stage, cbphase = bres ? 0u : bphase;
         if (++stage == (uint32_t)nstages) {
           stage = 0;
           bphase ^= 1;
@@ -491,7 +501,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             tc_mma_f16_ss(tmem_d, desc_sw32 | (uint64_t)(smem_u32(aconst) >> 4),
                           desc_sw32 | (uint64_t)(st_a + cstage * ((uint32_t)TB_TILE_BYTES >> 4) + KA * stage16), IDESC_FP16, 1u);
           mbar_arrive(&sm->tok[mp]);  // batch is in the queue: the other warp may issue the next tile
-          tc_commit(&sm->b_empty[cstage]);
+          if (!bres) tc_commit(&sm->b_empty[cstage]);
           if (nt == NT - 1) tc_commit(&sm->xa_empty[xb]);
           tc_commit(&sm->t_full[cbuf]);
         }

@@ -53,6 +53,34 @@ def test_tc3_with_workspace_certifies_its_labels():
     assert cost == pytest.approx(rcost, rel=1e-5)
 
 
+@pytest.mark.parametrize("d", [64, 128])
+def test_one_centre_tile_many_row_tiles_per_cta(d):
+    """k = 128 (ONE centre tile per row tile) with eight row tiles per CTA, through the 3xTF32 kernel WITH its
+    certainty test: nothing but the row-norm hand-off then keeps its split warps from running two row tiles ahead of
+    the epilogue, and that hand-off once had no back-pressure (the kernel timed out in a barrier wait from ~4 row
+    tiles per CTA on).  Also through the filter pipeline, whose re-check pass is the same kernel."""
+    N, G = _imports()
+    k = 128
+    n = 148 * 128 * 8 + 77
+    Xh = synth.mixture(n, 0, d, SEED + 21, 32, 2.0)
+    C = Xh[np.random.default_rng(5).choice(n, size=k, replace=False)].astype(np.float64)
+    C[64:] = C[:64] + 1e-4  # every row is torn between a centre and its shifted copy: all of them get re-checked
+    X, _, ld = G.upload_matrix(Xh)
+    X64 = Xh.astype(np.float64)
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(X64, C, return_second=True)
+    _, rcost, rsums, rcounts = oracle.kmeans_step(X64, C)
+    big = int(N.lib().b2f_kmeans_ws_bytes(6 * n, k, d))  # lists with room for every row
+    for algo, use_ws in ((N.KM_TC3, True), (N.KM_TCB, False), (N.KM_TCH, False)):
+        info = {}
+        labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, algo, use_ws=use_ws, info=info,
+                                                              ws_bytes=big)
+        assert nrows == n and counts.sum() == n
+        assert not ((labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)).any()
+        assert cost == pytest.approx(rcost, rel=1e-5)
+        if algo == N.KM_TCB:  # no pair check in the bf16x3 filter: every row goes through the re-check kernel
+            assert info["rechecked"] > n // 2
+
+
 @pytest.mark.parametrize("filt", ["TCB", "TCH"])
 def test_fit_driven_through_the_exact_fallback_matches_oracle(filt):
     """A workspace far too small for the uncertain rows: every pass of the fit overflows its lists, lloyd() redoes
