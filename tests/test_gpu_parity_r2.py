@@ -81,6 +81,37 @@ def test_one_centre_tile_many_row_tiles_per_cta(d):
             assert info["rechecked"] > n // 2
 
 
+@pytest.mark.parametrize("d,k", [(32, 128), (96, 256), (64, 384), (128, 640), (64, 1024), (128, 256), (64, 256)])
+def test_six_row_tiles_per_cta_across_shapes(d, k):
+    """The barrier rings of the tensor-core kernels only wrap with several row tiles per CTA, which the small parity
+    shapes (one or two tiles per CTA) never reach: one step of every tensor-core path at ~114 000 rows, odd and even
+    numbers of centre tiles, against the oracle."""
+    N, G = _imports()
+    n = 148 * 128 * 6 + 5
+    Xh = synth.mixture(n, 0, d, SEED + 31 + d + k, 24, 2.0)
+    C = Xh[np.random.default_rng(d + k).choice(n, size=k, replace=False)].astype(np.float64)
+    X, _, ld = G.upload_matrix(Xh)
+    X64 = Xh.astype(np.float64)
+    ref_lab, ref_d, ref_second = oracle.kmeans_assign(X64, C, return_second=True)
+    _, rcost, rsums, rcounts = oracle.kmeans_step(X64, C)
+    big = int(N.lib().b2f_kmeans_ws_bytes(6 * n, k, d))
+    runs = [(N.KM_TC3, False), (N.KM_TC3, True)]
+    if d in (64, 128):
+        runs += [(N.KM_TCB, False), (N.KM_TCH, False)]
+    sc = np.abs(rsums).max()
+    for algo, use_ws in runs:
+        labels, sums, counts, cost, nrows = G.kmeans_step_raw(X, n, d, ld, C, algo, use_ws=use_ws, ws_bytes=big)
+        assert nrows == n and counts.sum() == n
+        bad = (labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second)
+        if algo == N.KM_TC3 and not use_ws:  # no certainty test: 3xTF32 labels, a wider tie band
+            bad = (labels != ref_lab) & ~G.allowed_label_mismatch(ref_d, ref_second, rel=1e-5)
+        assert not bad.any()
+        assert cost == pytest.approx(rcost, rel=1e-5)
+        if not (labels != ref_lab).any():
+            np.testing.assert_array_equal(counts, rcounts)
+            np.testing.assert_allclose(sums, rsums, rtol=1e-5, atol=1e-5 * sc)
+
+
 @pytest.mark.parametrize("filt", ["TCB", "TCH"])
 def test_fit_driven_through_the_exact_fallback_matches_oracle(filt):
     """A workspace far too small for the uncertain rows: every pass of the fit overflows its lists, lloyd() redoes
