@@ -23,27 +23,36 @@ __device__ __forceinline__ float load_as_f32(const void* p, int dtype, int64_t i
 // scalar loads, ran at 0.45 of the HBM peak; 128 x 32 tiles with 16-byte loads but 128-byte row pieces at 0.58.)
 // Shared-memory tile [32][128] floats, swizzled at 16-byte granularity with the row group as key: the four scalars a
 // lane scatters and the 16-byte reads of the output phase are both conflict-free without padding.
-#define PK4_ROWS 32
-#define PK4_COLS 128
-__device__ __forceinline__ int pk4_slot(int row, int col) {  // float index of (row, col) in the swizzled tile
-  return row * PK4_COLS + ((((col >> 2) ^ ((row >> 2) & 7)) << 2) | (col & 3));
+// 64 x 64 tiles (16 KB) whatever the width; a 128-column matrix is two column tiles.  Measured, device columns ->
+// row-major, read + write: 32 x 128 tiles 4.2 TB/s at d = 128 and, half of the threads without a column, 2.7 at d = 64;
+// 64 x 64 tiles 4.9 / 4.8 (256 contiguous bytes per column and tile instead of 128); 64 x 128 tiles (32 KB, fewer
+// resident CTAs) 3.9.  The next tile's loads are issued before the current tile's stores (+4 %).
+#define PK4_ROWS 64
+#define PK4_TILE (PK4_ROWS * 64)
+template <int COLS> __device__ __forceinline__ int pk4_slot(int row, int col) {  // float index of (row, col), swizzled
+  return row * COLS + ((((col >> 2) ^ ((row >> 2) & 7)) << 2) | (col & 3));
 }
+template <int COLS>
 __device__ __forceinline__ void pack_columns_f32_body(float* tile, const void* const* __restrict__ cols, int d, int64_t n,
                                                       float* __restrict__ X, int64_t ld, int32_t* bad_flag) {
+  constexpr int ROWS = PK4_ROWS;
+  constexpr int RG = ROWS / 4;           // groups of four rows: 16 lanes along the rows of one column
+  constexpr int CPW = 32 / RG;           // columns one warp instruction covers: 2
+  constexpr int LPR = COLS / 4;          // lanes per output row (one float4 each): 32 | 16
+  constexpr int NLD = COLS / (8 * CPW);  // 16-byte loads per thread and tile: 8 | 4
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int rg = lane & 7, cq = lane >> 3;  // row group (4 rows) and column within the warp's group of four
-  const int64_t row_tiles = (n + PK4_ROWS - 1) / PK4_ROWS;
-  const int col_tiles = (int)((ld + PK4_COLS - 1) / PK4_COLS);
+  const int rg = lane % RG, cq = lane / RG;
+  const int64_t row_tiles = (n + ROWS - 1) / ROWS;
+  const int col_tiles = (int)((ld + COLS - 1) / COLS);
   const int64_t tiles = row_tiles * col_tiles;
   bool bad = false;
-  for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
-    const int64_t r0 = (t / col_tiles) * PK4_ROWS;
-    const int c0 = (int)(t % col_tiles) * PK4_COLS;
-    const int64_t r = r0 + rg * 4;
-    float4 v[4];
+  float4 v[NLD];
+  auto load_tile = [&](int64_t t) {  // this thread's 16-byte loads of tile t, all in flight together
+    const int64_t r = (t / col_tiles) * ROWS + rg * 4;
+    const int c0 = (int)(t % col_tiles) * COLS;
 #pragma unroll
-    for (int cc = 0; cc < 4; ++cc) {  // all four loads of this thread in flight before the first store
-      const int c = c0 + (warp * 4 + cc) * 4 + cq;
+    for (int cc = 0; cc < NLD; ++cc) {
+      const int c = c0 + (warp * NLD + cc) * CPW + cq;
       v[cc] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (c < d) {
         const float* p = static_cast<const float*>(cols[c]);
@@ -56,23 +65,31 @@ __device__ __forceinline__ void pack_columns_f32_body(float* tile, const void* c
         }
       }
     }
+  };
+  if ((int64_t)blockIdx.x < tiles) load_tile(blockIdx.x);
+  for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const int64_t r0 = (t / col_tiles) * ROWS;
+    const int c0 = (int)(t % col_tiles) * COLS;
 #pragma unroll
-    for (int cc = 0; cc < 4; ++cc) {
-      const int cl = (warp * 4 + cc) * 4 + cq;
+    for (int cc = 0; cc < NLD; ++cc) {
+      const int cl = (warp * NLD + cc) * CPW + cq;
       bad |= isnan(v[cc].x) | isnan(v[cc].y) | isnan(v[cc].z) | isnan(v[cc].w);
-      tile[pk4_slot(rg * 4 + 0, cl)] = v[cc].x;
-      tile[pk4_slot(rg * 4 + 1, cl)] = v[cc].y;
-      tile[pk4_slot(rg * 4 + 2, cl)] = v[cc].z;
-      tile[pk4_slot(rg * 4 + 3, cl)] = v[cc].w;
+      tile[pk4_slot<COLS>(rg * 4 + 0, cl)] = v[cc].x;
+      tile[pk4_slot<COLS>(rg * 4 + 1, cl)] = v[cc].y;
+      tile[pk4_slot<COLS>(rg * 4 + 2, cl)] = v[cc].z;
+      tile[pk4_slot<COLS>(rg * 4 + 3, cl)] = v[cc].w;
     }
     __syncthreads();
+    // the next tile's loads go out before this tile's stores: reads stay in flight through the store phase
+    if (t + gridDim.x < tiles) load_tile(t + gridDim.x);
 #pragma unroll
-    for (int rr = 0; rr < PK4_ROWS / 8; ++rr) {  // a warp writes one row (512 B) per instruction
-      const int rl = warp + rr * 8;
-      const int c4 = lane * 4;
+    for (int rr = 0; rr < ROWS * LPR / 256; ++rr) {  // a warp writes 512 contiguous bytes (one or two rows) per instruction
+      const int rl = (warp * 32 + lane) / LPR + rr * (256 / LPR);
+      const int c4 = (lane % LPR) * 4;
       const int64_t row = r0 + rl;
       if (row < n && c0 + c4 < ld)
-        *reinterpret_cast<float4*>(X + row * ld + c0 + c4) = *reinterpret_cast<const float4*>(tile + pk4_slot(rl, c4));
+        *reinterpret_cast<float4*>(X + row * ld + c0 + c4) =
+            *reinterpret_cast<const float4*>(tile + pk4_slot<COLS>(rl, c4));
     }
     __syncthreads();
   }
@@ -84,13 +101,13 @@ __device__ __forceinline__ void pack_columns_f32_body(float* tile, const void* c
 __global__ void __launch_bounds__(256) pack_columns_kernel(const void* const* __restrict__ cols,
                                                            const int32_t* __restrict__ dtypes, int d, int64_t n,
                                                            float* __restrict__ X, int64_t ld, int32_t* bad_flag) {
-  __shared__ __align__(16) float tile[PK4_ROWS * PK4_COLS];  // 16 KB; the generic path uses it as [64][33]
+  __shared__ __align__(16) float tile[PK4_TILE];  // 32 KB; the generic path uses it as [64][33]
   // all columns fp32 and 16-byte aligned -> the 16-byte-load path (decided per CTA, the same everywhere)
   int ok = 1;
   for (int c = threadIdx.x; c < d; c += 256)
     ok &= (dtypes[c] == B2F_F32) && ((reinterpret_cast<uintptr_t>(cols[c]) & 15) == 0);
   if (__syncthreads_and(ok)) {
-    pack_columns_f32_body(tile, cols, d, n, X, ld, bad_flag);
+    pack_columns_f32_body<64>(tile, cols, d, n, X, ld, bad_flag);
     return;
   }
   float (*gt)[PK_COLS + 1] = reinterpret_cast<float (*)[PK_COLS + 1]>(tile);

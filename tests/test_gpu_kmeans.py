@@ -54,6 +54,34 @@ def test_pack_columns_matches_vector_assembler(n):
     assert np.array_equal(Xd.data.cpu().numpy(), got)
 
 
+@pytest.mark.parametrize("d", [3, 60, 64, 100, 128, 200])
+def test_pack_columns_all_fp32_device_columns(d):
+    """Device-resident fp32 columns take the 16-byte-load tiles of pack_columns_kernel (64 x 64 for matrices of at most
+    64 columns, 32 x 128 beyond): ragged row counts, ragged column counts, the NaN flag, and a column whose pointer is
+    not 16-byte aligned (the whole call then uses the scalar tiles)."""
+    N, G = _imports()
+    from b200fit.feature import pack_columns
+
+    rng = np.random.default_rng(d)
+    for n in (1, 31, 4099, 70001):
+        cols = [rng.normal(size=n).astype(np.float32) for _ in range(d)]
+        want = oracle.assemble(cols).astype(np.float32).reshape(n, d)
+        dcols = [torch.from_numpy(c).to(G.dev()) for c in cols]
+        X = pack_columns(dcols)
+        got = X.data.cpu().numpy()
+        assert X.n == n and X.d == d and X.ld % 4 == 0
+        assert np.array_equal(got[:, :d], want) and (got[:, d:] == 0).all()
+        if n > 40:
+            shifted = torch.empty(n + 1, dtype=torch.float32, device=G.dev())
+            shifted[1:].copy_(dcols[d // 2])
+            dcols[d // 2] = shifted[1:]  # data_ptr % 16 == 4
+            assert np.array_equal(pack_columns(dcols).data.cpu().numpy()[:, :d], want)
+            dcols[d - 1] = dcols[d - 1].clone()
+            dcols[d - 1][n - 2] = float("nan")
+            with pytest.raises(ValueError):
+                pack_columns(dcols)
+
+
 def test_pack_columns_chunked_host_pipeline_and_nan_policy():
     N, G = _imports()
     from b200fit.feature import pack_columns
