@@ -81,6 +81,55 @@ __device__ __forceinline__ float tb_row_scale(float xn, float cmax) {
   return __int_as_float(e << 23);
 }
 
+// ---- "grid minima" epilogue of the fp16 filter (TB_GRID) -------------------------------------------------------
+// The ALU pipe (min / max, 16 lanes per clock) is what bounds the filter kernel, and a running (best, second best)
+// over the scores costs 2.5 of its operations per score plus a multiply-add for the key.  Instead every score falls
+// into two classes whose minima are all that is kept:
+//   M-class  = the 16 consecutive centres it belongs to (a half of a 32-column accumulator chunk)
+//   A-class  = its position in them, column mod 16 (16 running minima per row, over all centre tiles)
+// one 3-input min per two scores for each (0.5 + 0.5 operations per score, no key arithmetic per score).  Two
+// different centres never share both classes, so a centre that is hidden behind a smaller one in one class is the
+// minimum of its class in the other: with the three smallest class minima of either kind,
+//   second best score  = min(second smallest M-minimum, second smallest A-minimum),
+//   every centre within thr of the best lies in (M-classes with minimum within thr) x (A-classes likewise),
+// which certifies a row (one candidate) or hands at most four candidate centres to the fp64 check (third smallest
+// minimum of either kind out of reach).  Class ids ride in the low bits of the class minima only (16 + 8 multiply-adds
+// per centre tile and row instead of 128); keys are relative to TB_QBASE so that value = key >> bits, no wrap.
+#ifndef TB_GRID
+#define TB_GRID 1
+#endif
+constexpr int TB_QBASE = 0x4B000000;  // bit pattern of 2^23: quantised scores are TB_QBASE + [0, 2^23)
+__device__ __forceinline__ int tb_min3(int a, int b, int c) { return min(min(a, b), c); }
+// smallest of 16 consecutive entries of a chunk (8 operations)
+__device__ __forceinline__ int tb_min16(const int* q) {
+  const int a = tb_min3(q[0], q[1], q[2]), b = tb_min3(q[3], q[4], q[5]), c = tb_min3(q[6], q[7], q[8]);
+  const int e = tb_min3(q[9], q[10], q[11]), f = tb_min3(q[12], q[13], q[14]);
+  return min(tb_min3(a, b, c), tb_min3(e, f, q[15]));
+}
+// three smallest, sorted, of two sorted triples (7 operations)
+__device__ __forceinline__ void tb_merge3(int& x1, int& x2, int& x3, int y1, int y2, int y3) {
+  const int t3 = min(tb_min3(x3, y3, max(x2, y1)), max(x1, y2));
+  const int t2 = tb_min3(max(x1, y1), x2, y2);
+  x1 = min(x1, y1);
+  x2 = t2;
+  x3 = t3;
+}
+// three smallest, sorted, of eight values (25 operations)
+__device__ __forceinline__ void tb_top3_of8(const int* x, int& t1, int& t2, int& t3) {
+  int c[2][3];
+#pragma unroll
+  for (int g = 0; g < 2; ++g) {
+    const int a1 = min(x[4 * g], x[4 * g + 1]), a2 = max(x[4 * g], x[4 * g + 1]);
+    const int b1 = min(x[4 * g + 2], x[4 * g + 3]), b2 = max(x[4 * g + 2], x[4 * g + 3]);
+    const int t = max(a1, b1), u = min(a2, b2);
+    c[g][0] = min(a1, b1);
+    c[g][1] = min(t, u);
+    c[g][2] = max(t, u);
+  }
+  t1 = c[0][0]; t2 = c[0][1]; t3 = c[0][2];
+  tb_merge3(t1, t2, t3, c[1][0], c[1][1], c[1][2]);
+}
+
 constexpr int TB_THREADS = 640;
 // Rows per centre are counted in shared memory (one int per centre behind SmemB, added to the global counters once at
 // the end of the kernel) up to this many centres; beyond it the counters would cost a centre stage.
@@ -182,9 +231,13 @@ struct SmemB {
   int p_i1[2][2][TM];                    // index of the best
   int p_b3[2][2][TM];                    // fp16 filter: lower bound of the third best key; index of the second best
   int p_i2[2][2][TM];
+  int p_a3[2][2][TM];                    // TB_GRID: third smallest A-class minimum (low 4 bits: class of the smallest)
   alignas(16) float cscale[TM];          // scaled pass: per-column factor (StandardScaler fold), d <= 128 entries
                                          // (read as float4: the 4-byte tmem_base above breaks the natural alignment)
 };
+
+// (d = 128, k = 1024, fp16 filter: three centre stages fit beside everything else only up to this size)
+static_assert(sizeof(SmemB) <= 15296, "SmemB grew: the fp16 filter loses a centre stage at d = 128");
 
 struct TcbWs {  // header of the caller-provided workspace (the first four ints are documented in b200fit.h)
   int count;    // rows appended to the re-check list (may exceed cap: the excess is dropped)
@@ -530,6 +583,10 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       // integer-key path (fp16 filter): running best / second best keys and the centre tile of the best
       int B1 = 0x7fffffff, B2 = 0x7fffffff, B3 = 0x7fffffff;  // B3: lower bound of the third best key
       int T1 = 0, T2 = 0;                                     // centre tiles of the best and the second best
+      bool got = false;  // this warp had a centre tile of this row tile (not a given at k = 128)
+      int A[16];  // TB_GRID: running minimum of every A-class (column mod 16) over this warp's centre tiles
+#pragma unroll
+      for (int p = 0; p < 16; ++p) A[p] = 0x7fffffff;
       float arow = 1.f;
       if (H16 && !gs) {
         // the split warps finished this row tile before its first MMA could start: the norms are there
@@ -545,6 +602,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           round ^= 1;
         }
         if (!mine) continue;
+        got = true;
         if (nt < 8) TR(1 + warp, 3 * nt);
         mbar_wait_ns(&sm->t_full[cbuf], cround, 20);
         tc_fence_after();
@@ -553,6 +611,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         uint32_t v[2][32];
         tmem_ld32(taddr, v[0]);
         int k1a = 0x7fffffff, k2a = 0x7fffffff, k1b = 0x7fffffff, k2b = 0x7fffffff;
+        int hm[8];  // TB_GRID: minima of the tile's eight M-classes (16 consecutive centres each)
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           tmem_ld_wait();
@@ -564,7 +623,19 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             tc_fence_before();
             mbar_arrive(&sm->t_empty[cbuf]);
           }
-          if (H16) {  // the accumulator holds S_a S_b (x . -2c + ||c||^2), in global mode + the magic constant
+          if (H16 && TB_GRID) {
+            // quantised scores as integers: the accumulator's own bit pattern (global key scale: the tensor core has
+            // added the magic constant), else one multiply-add into this row's key window
+            int* qv = reinterpret_cast<int*>(v[c & 1]);
+            if (!gs) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) qv[j] = __float_as_int(fmaf(__int_as_float(qv[j]), arow, TB_MAGIC));
+            }
+#pragma unroll
+            for (int p = 0; p < 16; ++p) A[p] = tb_min3(A[p], qv[p], qv[p + 16]);
+            hm[2 * c] = tb_min16(qv);
+            hm[2 * c + 1] = tb_min16(qv + 16);
+          } else if (H16) {  // the accumulator holds S_a S_b (x . -2c + ||c||^2), in global mode + the magic constant
             if (gs) tb_chunk_keys<true>(v[c & 1], arow, c * 32, k1a, k2a, k1b, k2b);
             else tb_chunk_keys<false>(v[c & 1], arow, c * 32, k1a, k2a, k1b, k2b);
           }
@@ -589,10 +660,16 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           }
         }
         if (H16) {  // fold the tile's two chains into the running triple; an earlier tile keeps equal keys
-          const int k1 = min(k1a, k1b), k2 = min(max(k1a, k1b), min(k2a, k2b));
+          int k1 = min(k1a, k1b), k2 = min(max(k1a, k1b), min(k2a, k2b));
           // The tile's third smallest key is >= l3: if its two smallest sit in different chains it IS min(k2a, k2b);
           // if one chain holds both, that chain's third is unknown and min(k2a, k2b) = k2 is all that can be said.
-          const int l3 = min(k2a, k2b);
+          int l3 = min(k2a, k2b);
+          if (TB_GRID) {  // keys of the eight M-class minima: value * 8 + class, then their three smallest (exact)
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              hm[j] = (int)((uint32_t)hm[j] * 8u + ((uint32_t)j - (uint32_t)TB_QBASE * 8u));
+            tb_top3_of8(hm, k1, k2, l3);
+          }
           // third smallest of the two sorted triples (B1, B2, B3) and (k1, k2, l3)
           B3 = min(min(B3, l3), min(max(B2, k1), max(B1, k2)));
           const int lose = max(B1, k1);             // the larger of the two firsts ...
@@ -609,7 +686,27 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       const bool a_wins = (b1a < b1b) || (b1a == b1b && i1a < i1b);
       const uint32_t ab = it & 1;
       mbar_wait_ns(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1, 64);
-      if (H16) {
+      if (H16 && TB_GRID) {
+        // the three smallest A-class minima (keys: value * 16 + class); a warp without a centre tile (k = 128)
+        // hands over INT_MAX everywhere
+        int a1 = 0x7fffffff, a2 = 0x7fffffff, a3 = 0x7fffffff;
+        if (got) {
+#pragma unroll
+          for (int p = 0; p < 16; ++p) A[p] = (int)((uint32_t)A[p] * 16u + ((uint32_t)p - (uint32_t)TB_QBASE * 16u));
+          int y1, y2, y3;
+          tb_top3_of8(A, a1, a2, a3);
+          tb_top3_of8(A + 8, y1, y2, y3);
+          tb_merge3(a1, a2, a3, y1, y2, y3);
+        }
+        sm->p_b1[ab][half][row_in_tile] = __int_as_float(B1);
+        sm->p_b2[ab][half][row_in_tile] = __int_as_float(B2);
+        sm->p_b3[ab][half][row_in_tile] = B3;
+        // first centres of the best and the second best M-class (k <= 65536)
+        sm->p_i1[ab][half][row_in_tile] =
+            (int)((uint32_t)(T1 * TN + (B1 & 7) * 16) | ((uint32_t)(T2 * TN + (B2 & 7) * 16) << 16));
+        sm->p_i2[ab][half][row_in_tile] = a2;
+        sm->p_a3[ab][half][row_in_tile] = (a3 & ~15) | (a1 & 15);
+      } else if (H16) {
         sm->p_b1[ab][half][row_in_tile] = __int_as_float(B1);
         sm->p_b2[ab][half][row_in_tile] = __int_as_float(B2);
         sm->p_i1[ab][half][row_in_tile] = T1 * TN + tb_key_col(B1);
@@ -721,7 +818,22 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       float gap_units = 0.f;   // fp16 filter: second best - best in key units
       float gap3_units = 0.f;  // (lower bound of the) third best - best
       int i2 = -1;             // index of the second best
-      {
+      // TB_GRID, per epilogue warp h: values of the three smallest M-class minima (gv1 = the warp's best score) and
+      // of the second / third smallest A-class minima; first centres of the two best M-classes; the two best A-classes
+      int gv1[2], gm2[2], gm3[2], ga2[2], ga3[2], gb1[2], gb2[2], gc1[2], gc2[2];
+      if (H16 && TB_GRID) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int B1 = __float_as_int(sm->p_b1[ab][h][row_in_tile]), B2 = __float_as_int(sm->p_b2[ab][h][row_in_tile]);
+          const int B3 = sm->p_b3[ab][h][row_in_tile], a2 = sm->p_i2[ab][h][row_in_tile], a3 = sm->p_a3[ab][h][row_in_tile];
+          const uint32_t i12 = (uint32_t)sm->p_i1[ab][h][row_in_tile];
+          gv1[h] = B1 >> 3; gm2[h] = B2 >> 3; gm3[h] = B3 >> 3;  // (INT_MAX stays far above every real value)
+          ga2[h] = a2 >> 4; ga3[h] = a3 >> 4;
+          gb1[h] = (int)(i12 & 0xffffu); gb2[h] = (int)(i12 >> 16);
+          gc1[h] = a3 & 15; gc2[h] = a2 & 15;
+        }
+        mbar_arrive(&sm->a_empty[ab]);
+      } else {
         const float ob1 = sm->p_b1[ab][1][row_in_tile], ob2 = sm->p_b2[ab][1][row_in_tile];
         const int oi1 = sm->p_i1[ab][1][row_in_tile];
         int B3 = 0x7fffffff, O3 = 0x7fffffff, mi2 = -1, oi2 = -1;
@@ -764,6 +876,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       const bool live = row < n;
       bool certain = (b2 - b1) > tau2;  // false for NaN as well
       bool pair_ok = false;  // uncertain, but every centre other than the best two is out of reach
+      int quad_lo = 0, quad_hi = 0;  // TB_GRID: the candidates of such a row
       if (H16) {
         // key units per score unit, and what the keys themselves may be off by: per-row scale: one rounding each
         // (2.5 units for a difference); global scale: the tensor core TRUNCATES when it adds -- 8 accumulations at up
@@ -775,6 +888,47 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         const bool usable = arow > 0.f && arow < INFINITY && xn < INFINITY;
         certain = gap_units > thr && usable;
         pair_ok = !certain && usable && pairs != nullptr && gap3_units > thr && i2 >= 0 && i2 < k && i2 != i1;
+        if (TB_GRID) {
+          // candidates = centres that may be within thr of the best: (M-classes within thr) x (A-classes within
+          // thr), per epilogue warp; a third class of either kind within thr = too many to enumerate
+          const int S1 = min(gv1[0], gv1[1]);
+          const int m = (gv1[1] < gv1[0]) ? 1 : 0;  // the warp that holds the best
+          int nM[2], nA[2];
+          bool many = false;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int n1 = !((float)(gv1[h] - S1) > thr);
+            const int m2 = !((float)(gm2[h] - S1) > thr), m3 = !((float)(gm3[h] - S1) > thr);
+            const int a2 = !((float)(ga2[h] - S1) > thr), a3 = !((float)(ga3[h] - S1) > thr);
+            nM[h] = n1 + m2;
+            nA[h] = n1 + a2;
+            many |= (m3 | a3) != 0;
+          }
+          const int tot = nM[0] * nA[0] + nM[1] * nA[1];
+          i1 = gb1[m] + gc1[m];
+          certain = usable && !many && tot == 1;
+          pair_ok = !certain && usable && pairs != nullptr && !many && tot <= 4;
+          if (pair_ok) {  // up to four candidate centres, the best first, 16 bits each
+            unsigned long long pk = 0;
+            int nc = 0;
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+              const int h = hh ^ m;
+#pragma unroll
+              for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                for (int ai = 0; ai < 2; ++ai)
+                  if (mi < nM[h] && ai < nA[h]) {
+                    const int idx = (mi ? gb2[h] : gb1[h]) + (ai ? gc2[h] : gc1[h]);
+                    pk |= (unsigned long long)(uint32_t)idx << (16 * nc);
+                    ++nc;
+                  }
+            }
+            quad_lo = (int)(uint32_t)pk;
+            quad_hi = (int)(uint32_t)(pk >> 32);
+            i2 = tot;  // number of candidates
+          }
+        }
       }
       if (live) labels[row] = i1;             // provisional for uncertain rows (rewritten by the re-check)
       const int my_lab = (live && certain) ? i1 : -1;
@@ -807,20 +961,28 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       bool to_list = live && !certain && !pair_ok;
       if (H16) {
         const bool to_pair = live && pair_ok;
-        const unsigned pm = __ballot_sync(0xffffffffu, to_pair);
+        unsigned pm = __ballot_sync(0xffffffffu, to_pair);
+#ifdef TB_EXP_NOLIST  // timing experiment: uncertain rows are dropped
+        pm = 0;
+#endif
         if (pm) {
           int base = 0;
           if (lane == (__ffs(pm) - 1)) base = atomicAdd(&ws->pcount, __popc(pm));
           base = __shfl_sync(0xffffffffu, base, __ffs(pm) - 1);
           if (to_pair) {
             const int slot = base + __popc(pm & ((1u << lane) - 1));
-            if (slot < pcap) pairs[slot] = make_int4((int)(row & 0x7fffffff), i1, i2, 0);
+            if (slot < pcap)
+              pairs[slot] = TB_GRID ? make_int4((int)(row & 0x7fffffff), quad_lo, quad_hi, i2)
+                                    : make_int4((int)(row & 0x7fffffff), i1, i2, 0);
             else to_list = true;
           }
         }
       }
       // append the other uncertain rows to the re-check list (one atomic per warp)
-      const unsigned m = __ballot_sync(0xffffffffu, to_list);
+      unsigned m = __ballot_sync(0xffffffffu, to_list);
+#ifdef TB_EXP_NOLIST
+      m = 0;
+#endif
       if (m) {
         int base = 0;
         if (lane == (__ffs(m) - 1)) base = atomicAdd(&ws->count, __popc(m));
@@ -957,41 +1119,57 @@ __global__ void __launch_bounds__(256) km_pair_exact_kernel(const float* __restr
   for (int e = warp; e < used; e += nwarps) {
     const int4 pr = pairs[e];
     const int64_t row = pr.x;
-    const int i1 = pr.y, i2 = pr.z;
+    // candidates of the row: TB_GRID: up to four, 16 bits each in (y, z), their number in w; else the best two
+    int cand[4];
+    int nc;
+    if (TB_GRID) {
+      cand[0] = pr.y & 0xffff; cand[1] = (int)((uint32_t)pr.y >> 16);
+      cand[2] = pr.z & 0xffff; cand[3] = (int)((uint32_t)pr.z >> 16);
+      nc = min(max(pr.w, 1), 4);
+    } else {
+      cand[0] = pr.y; cand[1] = pr.z; cand[2] = pr.y; cand[3] = pr.y;
+      nc = 2;
+    }
     float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-    double a1[4] = {0, 0, 0, 0}, a2[4] = {0, 0, 0, 0};
     if (on) {
       x = *reinterpret_cast<const float4*>(X + row * ld + c);
       if (colscale) {
         const float4 sc = *reinterpret_cast<const float4*>(colscale + c);
         x.x = __fmul_rn(x.x, sc.x); x.y = __fmul_rn(x.y, sc.y); x.z = __fmul_rn(x.z, sc.z); x.w = __fmul_rn(x.w, sc.w);
       }
-      const double2* p1 = reinterpret_cast<const double2*>(C64 + (size_t)i1 * d + c);
-      const double2* p2 = reinterpret_cast<const double2*>(C64 + (size_t)i2 * d + c);
-      const double2 u0 = p1[0], u1 = p1[1], v0 = p2[0], v1 = p2[1];
-      a1[0] = u0.x; a1[1] = u0.y; a1[2] = u1.x; a1[3] = u1.y;
-      a2[0] = v0.x; a2[1] = v0.y; a2[2] = v1.x; a2[3] = v1.y;
     }
     const double xd[4] = {(double)x.x, (double)x.y, (double)x.z, (double)x.w};
-    double xn = 0.0, s1 = 0.0, s2 = 0.0;
+    double xn = 0.0, sdot[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      xn = fma(xd[j], xd[j], xn);
-      s1 = fma(xd[j], a1[j], s1);
-      s2 = fma(xd[j], a2[j], s2);
+    for (int j = 0; j < 4; ++j) xn = fma(xd[j], xd[j], xn);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (q < nc && on) {  // (nc is the same for the whole warp)
+        const double2* pc = reinterpret_cast<const double2*>(C64 + (size_t)cand[q] * d + c);
+        const double2 u0 = pc[0], u1 = pc[1];
+        sdot[q] = fma(xd[0], u0.x, fma(xd[1], u0.y, fma(xd[2], u1.x, xd[3] * u1.y)));
+      }
     }
     xn = warp_sum(xn);
-    s1 = warp_sum(s1);
-    s2 = warp_sum(s2);
-    const double v1 = fmax(xn + CN64[i1] - 2.0 * s1, 0.0), v2 = fmax(xn + CN64[i2] - 2.0 * s2, 0.0);
-    const bool second = (v2 < v1) || (v2 == v1 && i2 < i1);
-    const int pick = second ? i2 : i1;
+    int pick = cand[0];
+    double vbest = 0.0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (q < nc) {
+        const double sq = warp_sum(sdot[q]);
+        const double vq = fmax(xn + CN64[cand[q]] - 2.0 * sq, 0.0);
+        if (q == 0 || vq < vbest || (vq == vbest && cand[q] < pick)) {
+          vbest = vq;
+          pick = cand[q];
+        }
+      }
+    }
     if (lane == 0) labels[row] = pick;
     if (accumulate) {
       if (on) red_add_v4(myrep + (size_t)pick * d + c, x);
       if (lane == 0) {
         atomicAdd(cnt + pick, 1ull);
-        cost += second ? v2 : v1;
+        cost += vbest;
         ++rows;
       }
     }
@@ -1094,7 +1272,7 @@ static int km_tcb_stages(int k, int d, int filter) {
 
 bool km_tcb_supported(int k, int d, int64_t ld) {
   if (d != 64 && d != 128) return false;  // whole 64-k atoms, X hi/lo pairs fit the tensor memory budget
-  if (k % TN != 0 || k < TN) return false;
+  if (k % TN != 0 || k < TN || k > 65536) return false;  // (the filter hands centre indices over in 16 bits)
   if (ld % 4 != 0) return false;
   return km_tcb_stages(k, d, KM_FILTER_BF16X3) >= 2 && km_tcb_stages(k, d, KM_FILTER_FP16) >= 2 &&
          km_tc_supported(k, d, ld);
