@@ -187,9 +187,13 @@ constexpr int TB_CN_BYTES = 128 * 32;  // the ||c||^2 k-block of a centre tile: 
 // what the epilogue warpgroups gain, (EPI - 96) * 256, must be given back first by the others:
 // (96 - CTRL) * 128 + (96 - FIN) * 128  (the pool is per CTA)
 // (the pool is what the CTA was LAUNCHED with -- 640 threads x 96 -- not the SM's register file)
-#define TB_REG_CTRL 48
+// Measured with the class-minima epilogue (20M x 128, k = 1024, whole step): (CTRL, FIN, EPI) = (48, 80, 128) 7.9-8.2 ms;
+// (64, 80, 120), (80, 80, 112), (88, 88, 104), (72, 88, 112) all 7.5: at 48 registers the producer and MMA-issuer
+// loops reload spilled loop state from local memory every iteration, and that sits on the critical path; the
+// epilogue no longer needs 128.
+#define TB_REG_CTRL 80
 #define TB_REG_FIN 80
-#define TB_REG_EPI 128
+#define TB_REG_EPI 112
 #define TB_FIN_ROWS 8
 #define TB_FX_ROWS 8
 #endif
@@ -464,6 +468,16 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         for (int nt = 0; nt < NT; ++nt) {
           if (!bres) mbar_wait_ns(&sm->b_empty[s], ph ^ 1, 64);
           if (nt < 8) TR(11, nt);
+#ifdef TB_EXP_FAKEB  // timing experiment: centre stages are loaded for the first row tile only (results invalid)
+          if (it > 0) {
+            mbar_arrive(&sm->b_full[s]);
+            if (++s == (uint32_t)nstages) {
+              s = 0;
+              ph ^= 1;
+            }
+            continue;
+          }
+#endif
           mbar_expect_tx(&sm->b_full[s], (uint32_t)(KA * TB_STAGE_BYTES + (H16 ? TB_CN_BYTES : 0)));
           for (int a = 0; a < KA; ++a) {
             uint8_t* dst = stages + (size_t)s * TB_TILE_BYTES + (size_t)a * TB_STAGE_BYTES;
@@ -905,7 +919,8 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             many |= (m3 | a3) != 0;
           }
           const int tot = nM[0] * nA[0] + nM[1] * nA[1];
-          i1 = gb1[m] + gc1[m];
+          // (selects, not indexing by m: a dynamically indexed array would live in local memory)
+          i1 = m ? gb1[1] + gc1[1] : gb1[0] + gc1[0];
           certain = usable && !many && tot == 1;
           pair_ok = !certain && usable && pairs != nullptr && !many && tot <= 4;
           if (pair_ok) {  // up to four candidate centres, the best first, 16 bits each
@@ -913,13 +928,16 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
             int nc = 0;
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
-              const int h = hh ^ m;
+              const bool o = (hh ^ m) != 0;  // warp whose candidates come now: the one holding the best first
+              const int cM = o ? nM[1] : nM[0], cA = o ? nA[1] : nA[0];
+              const int b1c = o ? gb1[1] : gb1[0], b2c = o ? gb2[1] : gb2[0];
+              const int c1c = o ? gc1[1] : gc1[0], c2c = o ? gc2[1] : gc2[0];
 #pragma unroll
               for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
                 for (int ai = 0; ai < 2; ++ai)
-                  if (mi < nM[h] && ai < nA[h]) {
-                    const int idx = (mi ? gb2[h] : gb1[h]) + (ai ? gc2[h] : gc1[h]);
+                  if (mi < cM && ai < cA) {
+                    const int idx = (mi ? b2c : b1c) + (ai ? c2c : c1c);
                     pk |= (unsigned long long)(uint32_t)idx << (16 * nc);
                     ++nc;
                   }
