@@ -822,6 +822,43 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     unsigned long long nrows = 0;
     float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
     uint32_t it = 0, fxc = 0;  // fxc: batches this warp has pushed through its row buffers
+    // list appends of the previous tile whose slots are reserved but whose entries are not written yet
+    unsigned pend_pm = 0, pend_lm = 0;       // lanes with a pair / re-check entry
+    int pend_pbase = 0, pend_lbase = 0;      // (leader lane) first reserved slot
+    bool pend_pair = false, pend_list = false;
+    int4 pend_ent = make_int4(0, 0, 0, 0);
+    int32_t pend_lrow = 0;
+    auto flush_pending = [&]() {
+      const unsigned lt = (1u << lane) - 1;
+      bool over = false;  // pair list full: the row goes to the re-check list after all (rare: own atomic, waited for)
+      if (pend_pm) {
+        const int base = __shfl_sync(0xffffffffu, pend_pbase, __ffs(pend_pm) - 1);
+        if (pend_pair) {
+          const int slot = base + __popc(pend_pm & lt);
+          if (slot < pcap) pairs[slot] = pend_ent;
+          else over = true;
+        }
+        const unsigned om = __ballot_sync(0xffffffffu, over);
+        if (om) {
+          int ob = 0;
+          if (lane == (__ffs(om) - 1)) ob = atomicAdd(&ws->count, __popc(om));
+          ob = __shfl_sync(0xffffffffu, ob, __ffs(om) - 1);
+          if (over) {
+            const int slot = ob + __popc(om & lt);
+            if (slot < cap) amb_idx[slot] = pend_ent.x;
+          }
+        }
+      }
+      if (pend_lm) {
+        const int base = __shfl_sync(0xffffffffu, pend_lbase, __ffs(pend_lm) - 1);
+        if (pend_list) {
+          const int slot = base + __popc(pend_lm & lt);
+          if (slot < cap) amb_idx[slot] = pend_lrow;
+        }
+      }
+      pend_pm = 0;
+      pend_lm = 0;
+    };
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t ab = it & 1;
       if (w4 == 0) TR(10, 0);
@@ -974,42 +1011,30 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         acc_rows.fx_full = sm->fx_full[w4];
         acc_rows.begin(fxc, my_lab);
       }
-      // uncertain rows with exactly two candidates: pair list (row, best, second best), decided by two fp64
-      // distances; a full pair list sends the row to the re-check list instead
+      // Uncertain rows with at most four (two) candidates: pair list, decided by fp64 distances; a full pair list sends
+      // the row to the re-check list instead.  The other uncertain rows: re-check list.  One atomic per warp and list
+      // reserves the slots -- and its return value is an L2 round trip, which used to sit in this loop for ~94 % of
+      // the warp-tiles (cfg 2).  So the entries are WRITTEN one tile later (flush_pending), when the reservation has
+      // long arrived, and the atomics of this tile are only issued here.
+      flush_pending();
       bool to_list = live && !certain && !pair_ok;
       if (H16) {
-        const bool to_pair = live && pair_ok;
-        unsigned pm = __ballot_sync(0xffffffffu, to_pair);
+        pend_pair = live && pair_ok;
+        pend_pm = __ballot_sync(0xffffffffu, pend_pair);
 #ifdef TB_EXP_NOLIST  // timing experiment: uncertain rows are dropped
-        pm = 0;
+        pend_pm = 0;
 #endif
-        if (pm) {
-          int base = 0;
-          if (lane == (__ffs(pm) - 1)) base = atomicAdd(&ws->pcount, __popc(pm));
-          base = __shfl_sync(0xffffffffu, base, __ffs(pm) - 1);
-          if (to_pair) {
-            const int slot = base + __popc(pm & ((1u << lane) - 1));
-            if (slot < pcap)
-              pairs[slot] = TB_GRID ? make_int4((int)(row & 0x7fffffff), quad_lo, quad_hi, i2)
-                                    : make_int4((int)(row & 0x7fffffff), i1, i2, 0);
-            else to_list = true;
-          }
-        }
+        pend_ent = TB_GRID ? make_int4((int)(row & 0x7fffffff), quad_lo, quad_hi, i2)
+                           : make_int4((int)(row & 0x7fffffff), i1, i2, 0);
+        if (pend_pm && lane == (__ffs(pend_pm) - 1)) pend_pbase = atomicAdd(&ws->pcount, __popc(pend_pm));
       }
-      // append the other uncertain rows to the re-check list (one atomic per warp)
-      unsigned m = __ballot_sync(0xffffffffu, to_list);
+      pend_list = to_list;
+      pend_lrow = (int32_t)(row & 0x7fffffff);
+      pend_lm = __ballot_sync(0xffffffffu, to_list);
 #ifdef TB_EXP_NOLIST
-      m = 0;
+      pend_lm = 0;
 #endif
-      if (m) {
-        int base = 0;
-        if (lane == (__ffs(m) - 1)) base = atomicAdd(&ws->count, __popc(m));
-        base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-        if (to_list) {
-          const int slot = base + __popc(m & ((1u << lane) - 1));
-          if (slot < cap) amb_idx[slot] = (int32_t)(row & 0x7fffffff);
-        }
-      }
+      if (pend_lm && lane == (__ffs(pend_lm) - 1)) pend_lbase = atomicAdd(&ws->count, __popc(pend_lm));
       if (w4 == 0) TR(10, 2);
       if (RFS) {
         bulk_wait_read<0>();
@@ -1049,6 +1074,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       }
       if (w4 == 0) TR(10, 3);
     }
+    flush_pending();
     if (H16) bulk_wait_all();  // the reductions read this CTA's shared memory
     if (accumulate) {
       cost = warp_sum(cost);
