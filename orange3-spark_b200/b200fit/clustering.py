@@ -48,7 +48,7 @@ class CudaLloydEngine:
         # needs a labels buffer and a workspace.  Decided from the SHAPE only (never from this rank's row count):
         # every rank must take the same branches between collectives, also one whose shard is empty.
         self.use_ws = (algo in (N.KM_AUTO, N.KM_TCB, N.KM_TCH) and w is None and self.d in (64, 128)
-                       and self.k % 128 == 0 and X.ld % 4 == 0)
+                       and self.k % 128 == 0 and self.k <= 65536 and X.ld % 4 == 0)
         if algo in (N.KM_TCB, N.KM_TCH) and not self.use_ws:
             raise ValueError("B2F_KM_TCB / B2F_KM_TCH need d in {64, 128}, k % 128 == 0 and no row weights")
         self.col_scale = getattr(X, "col_scale", None)
@@ -209,7 +209,7 @@ def predict_labels(X, centers, want_dist=False, algo=N.KM_AUTO, info=None):
     N.check(L.b2f_kmeans_prepare(N.ptr(cdev), k, d, N.ptr(prep), N.stream_ptr()), "b2f_kmeans_prepare")
     labels = torch.empty(X.n, dtype=torch.int32, device=dev)
     dist = torch.empty(X.n, dtype=torch.float32, device=dev) if want_dist else None
-    tc_shape = d % 32 == 0 and 32 <= d <= 128 and k % 128 == 0 and X.ld % 4 == 0
+    tc_shape = d % 32 == 0 and 32 <= d <= 128 and k % 128 == 0 and k <= 65536 and X.ld % 4 == 0
     scale = getattr(X, "col_scale", None)
     if scale is not None and not (tc_shape and d in (64, 128) and algo in (N.KM_AUTO, N.KM_TCH)):
         X, scale = X.materialized(), None

@@ -468,16 +468,6 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         for (int nt = 0; nt < NT; ++nt) {
           if (!bres) mbar_wait_ns(&sm->b_empty[s], ph ^ 1, 64);
           if (nt < 8) TR(11, nt);
-#ifdef TB_EXP_FAKEB  // timing experiment: centre stages are loaded for the first row tile only (results invalid)
-          if (it > 0) {
-            mbar_arrive(&sm->b_full[s]);
-            if (++s == (uint32_t)nstages) {
-              s = 0;
-              ph ^= 1;
-            }
-            continue;
-          }
-#endif
           mbar_expect_tx(&sm->b_full[s], (uint32_t)(KA * TB_STAGE_BYTES + (H16 ? TB_CN_BYTES : 0)));
           for (int a = 0; a < KA; ++a) {
             uint8_t* dst = stages + (size_t)s * TB_TILE_BYTES + (size_t)a * TB_STAGE_BYTES;
@@ -1021,9 +1011,6 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       if (H16) {
         pend_pair = live && pair_ok;
         pend_pm = __ballot_sync(0xffffffffu, pend_pair);
-#ifdef TB_EXP_NOLIST  // timing experiment: uncertain rows are dropped
-        pend_pm = 0;
-#endif
         pend_ent = TB_GRID ? make_int4((int)(row & 0x7fffffff), quad_lo, quad_hi, i2)
                            : make_int4((int)(row & 0x7fffffff), i1, i2, 0);
         if (pend_pm && lane == (__ffs(pend_pm) - 1)) pend_pbase = atomicAdd(&ws->pcount, __popc(pend_pm));
@@ -1031,9 +1018,6 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       pend_list = to_list;
       pend_lrow = (int32_t)(row & 0x7fffffff);
       pend_lm = __ballot_sync(0xffffffffu, to_list);
-#ifdef TB_EXP_NOLIST
-      pend_lm = 0;
-#endif
       if (pend_lm && lane == (__ffs(pend_lm) - 1)) pend_lbase = atomicAdd(&ws->count, __popc(pend_lm));
       if (w4 == 0) TR(10, 2);
       if (RFS) {
@@ -1146,7 +1130,8 @@ __global__ void tcb_set_cap_kernel(TcbWs* __restrict__ ws, int cap) { ws->cap = 
 __global__ void __launch_bounds__(256) km_pair_exact_kernel(const float* __restrict__ X, int64_t ld, int d,
                                                             const float* __restrict__ colscale,
                                                             const double* __restrict__ C64,
-                                                            const double* __restrict__ CN64, int k,
+                                                            const double* __restrict__ CN64,
+                                                            const float* __restrict__ C32, int k,
                                                             double* __restrict__ payload, float* __restrict__ rep,
                                                             unsigned long long* __restrict__ cnt,
                                                             int32_t* __restrict__ labels,
@@ -1180,6 +1165,67 @@ __global__ void __launch_bounds__(256) km_pair_exact_kernel(const float* __restr
       if (colscale) {
         const float4 sc = *reinterpret_cast<const float4*>(colscale + c);
         x.x = __fmul_rn(x.x, sc.x); x.y = __fmul_rn(x.y, sc.y); x.z = __fmul_rn(x.z, sc.z); x.w = __fmul_rn(x.w, sc.w);
+      }
+    }
+    // First in fp32, sum (x - c32)^2 on the fp32 centres (half the bytes of the fp64 table, and this kernel is bound
+    // by those L2 reads): relative error <= 12 * 2^-24 from the arithmetic (positive terms) and, from c32 = fl32(c),
+    // 2 sqrt(dist2) 2^-24 ||c||; twice that is allowed for.  If the smallest distance beats every other by more than
+    // both bounds the fp64 order is the same; else (about one entry in a few hundred: these rows were uncertain at
+    // fp16 precision, not fp32) the fp64 evaluation below decides.
+    if (C32 != nullptr) {
+      float dq[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (q < nc) {
+          float a = 0.f;
+          if (on) {
+            const float4 cv = *reinterpret_cast<const float4*>(C32 + (size_t)cand[q] * d + c);
+            const float t0 = x.x - cv.x, t1 = x.y - cv.y, t2 = x.z - cv.z, t3 = x.w - cv.w;
+            a = fmaf(t0, t0, fmaf(t1, t1, fmaf(t2, t2, t3 * t3)));
+          }
+          dq[q] = warp_sum(a);
+        }
+      }
+      int qb = 0;
+      float dbest = dq[0];
+#pragma unroll
+      for (int q = 1; q < 4; ++q)
+        if (q < nc && dq[q] < dbest) {
+          qb = q;
+          dbest = dq[q];
+        }
+      bool sure = true;
+      float hi_best = 0.f;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (q < nc) {
+          const float cnq = (float)CN64[cand[q]];
+          const float err = fmaf(2.0e-6f, dq[q], 3.0e-7f * sqrtf(dq[q] * cnq)) + 1e-30f;
+          if (q == qb) hi_best = dq[q] + err;
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (q < nc && q != qb) {
+          const float cnq = (float)CN64[cand[q]];
+          const float err = fmaf(2.0e-6f, dq[q], 3.0e-7f * sqrtf(dq[q] * cnq)) + 1e-30f;
+          sure = sure && (dq[q] - err > hi_best);
+        }
+      }
+      if (sure) {
+        int pick32 = cand[0];
+#pragma unroll
+        for (int q = 1; q < 4; ++q) pick32 = (qb == q) ? cand[q] : pick32;
+        if (lane == 0) labels[row] = pick32;
+        if (accumulate) {
+          if (on) red_add_v4(myrep + (size_t)pick32 * d + c, x);
+          if (lane == 0) {
+            atomicAdd(cnt + pick32, 1ull);
+            cost += (double)dbest;
+            ++rows;
+          }
+        }
+        continue;
       }
     }
     const double xd[4] = {(double)x.x, (double)x.y, (double)x.z, (double)x.w};
@@ -1466,6 +1512,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
   if (h16) {
     const double* c64 = reinterpret_cast<const double*>(pp + P.off_c64);
     const double* cn64 = reinterpret_cast<const double*>(pp + P.off_cn64);
+    const float* c32 = TB_GRID ? reinterpret_cast<const float*>(pp + P.off_c32) : nullptr;
     const int cgrid = (k + 7) / 8;
     // scaled pass: this kernel adds RAW rows to the replicas; whatever they hold on entry is folded away first and
     // the raw sums are folded through the scale right after the kernel, so everything downstream sees scaled sums
@@ -1482,7 +1529,7 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
     if (acc_main && colscale && (rc = km_fold_scaled(acc, k, d, colscale, stream)) != B2F_OK) return rc;
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, 1.0);
     // rows with exactly two candidate centres: two fp64 distances each
-    km_pair_exact_kernel<<<b2f_sm_count() * 8, 256, 0, stream>>>(X, ld, d, colscale, c64, cn64, k, payload, rep, cnt,
+    km_pair_exact_kernel<<<b2f_sm_count() * 8, 256, 0, stream>>>(X, ld, d, colscale, c64, cn64, c32, k, payload, rep, cnt,
                                                                  labels, hdr, pairs, cap, accumulate ? 1 : 0);
     B2F_LAUNCH_CHECK();
   } else {
