@@ -1145,8 +1145,21 @@ __global__ void __launch_bounds__(256) km_pair_exact_kernel(const float* __restr
   float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
   double cost = 0.0;
   unsigned long long rows = 0;
-  for (int e = warp; e < used; e += nwarps) {
-    const int4 pr = pairs[e];
+  // One warp per entry, ~110 entries per warp, and each is a chain of dependent round trips (entry -> row from HBM
+  // -> centres from L2): the entry after next and the next entry's row are fetched while the current one is worked on.
+  const int4 none = make_int4(0, 0, 0, 0);
+  auto load_row = [&](int64_t r) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (on) v = ldg_stream(reinterpret_cast<const float4*>(X + r * ld + c));
+    return v;
+  };
+  int4 pr = warp < used ? pairs[warp] : none;
+  int4 pr1 = warp + nwarps < used ? pairs[warp + nwarps] : none;
+  float4 xraw = load_row(pr.x), xraw1 = make_float4(0.f, 0.f, 0.f, 0.f);
+  int4 pr2 = none;
+  for (int e = warp; e < used; e += nwarps, pr = pr1, pr1 = pr2, xraw = xraw1) {
+    pr2 = (int64_t)e + 2 * (int64_t)nwarps < used ? pairs[e + 2 * nwarps] : none;
+    xraw1 = load_row(pr1.x);  // (row 0 when there is no next entry: a harmless read)
     const int64_t row = pr.x;
     // candidates of the row: TB_GRID: up to four, 16 bits each in (y, z), their number in w; else the best two
     int cand[4];
@@ -1159,9 +1172,8 @@ __global__ void __launch_bounds__(256) km_pair_exact_kernel(const float* __restr
       cand[0] = pr.y; cand[1] = pr.z; cand[2] = pr.y; cand[3] = pr.y;
       nc = 2;
     }
-    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 x = xraw;
     if (on) {
-      x = *reinterpret_cast<const float4*>(X + row * ld + c);
       if (colscale) {
         const float4 sc = *reinterpret_cast<const float4*>(colscale + c);
         x.x = __fmul_rn(x.x, sc.x); x.y = __fmul_rn(x.y, sc.y); x.z = __fmul_rn(x.z, sc.z); x.w = __fmul_rn(x.w, sc.w);
