@@ -114,7 +114,10 @@ def test_tc_rejects_unsupported_shapes():
 # (k / 128 odd: the two MMA issuers, the two epilogue warps per quarter and the three accumulators then fall out of
 # step with the row tiles; 45000 rows = 352 row tiles: several per CTA)
 TCB_SHAPES = [(128, 64, 128), (1000, 64, 128), (5000, 128, 256), (4099, 128, 1024), (20000, 128, 128),
-              (30000, 64, 256), (3000, 64, 384), (45000, 128, 640), (40000, 64, 128)]
+              (30000, 64, 256), (3000, 64, 384), (45000, 128, 640), (40000, 64, 128),
+              # k > 1024: row counts through global atomics instead of the per-CTA shared-memory counters; at d = 64
+              # more centre tiles than stages (no resident tiles)
+              (9000, 64, 2048), (6000, 128, 1536)]
 
 
 FILTERS = ["TCB", "TCH"]  # bf16x3 filter (three MMAs per product) / fp16 filter (one MMA, scaled operands)

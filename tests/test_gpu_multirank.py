@@ -168,8 +168,10 @@ def test_two_rank_fits_equal_the_one_rank_fits():
             # exposed the staging-slot race of the multinomial tensor-core kernel in round 2: with it the two runs
             # parted by 1e-3 after one iteration; with the fix the histories agree to 1e-9.)
             close(pre + "multinomial objective", two["m_hist"], one["m_hist"], 1e-7)
+            # (coefficients: 1e-5 relative, floor 1e-6 of the largest -- entries the L1 term holds near zero move by
+            # more than their own 1e-5 when the pass sums differ in the last bits: 1.1e-5 on one box with a 1e-7 floor)
             close(pre + "multinomial coefficients", two["m_coef"], one["m_coef"], 1e-5,
-                  1e-7 * np.abs(one["m_coef"]).max())
+                  1e-6 * np.abs(one["m_coef"]).max())
     print("\n" + "\n".join(report))
     assert not failures, "\n".join(failures)
     # ranks of one run hold identical models (no root, no broadcast: every rank ran the same finalize)
