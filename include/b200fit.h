@@ -47,7 +47,7 @@ extern "C" {
 #define B2F_KM_TC3 2     /* tcgen05 3xTF32 (fp32-accurate) contraction, d % 32 == 0, k % 128 == 0 */
 #define B2F_KM_TC1 3     /* tcgen05 1xTF32 contraction (filter pass; labels need refine) */
 #define B2F_KM_TCB 4     /* tcgen05 bf16x3 filter pass + 3xTF32 re-check of uncertain rows; d in {64,128},
-                            k % 128 == 0; only through b2f_kmeans_step_ws (needs labels + workspace)    */
+                            k % 128 == 0, k <= 65536; only through b2f_kmeans_step_ws (labels + workspace) */
 #define B2F_KM_TCH 5     /* same pipeline with a single-MMA fp16 filter pass (a third of the tensor work, a
                             wider uncertainty band); same shapes and entry point as B2F_KM_TCB           */
 
@@ -167,7 +167,7 @@ int b2f_kmeans_finalize(const double* payload, int k, int d, double tol, double*
 int b2f_kmeans_predict(const float* X, int64_t n, int d, int64_t ld, const void* prep, int k, int32_t* labels,
                        float* dist2, int algo, b2f_stream_t stream);
 /* The same with a workspace (b2f_kmeans_ws_bytes): labels then come from the certainty pipeline of
- * b2f_kmeans_step_ws (filter pass, pair check, 3xTF32 re-check, fp64 tail) wherever the shape allows it, i.e. they
+ * b2f_kmeans_step_ws (filter pass, candidate check, 3xTF32 re-check, fp64 tail) wherever the shape allows it, i.e. they
  * equal the fp64 assignment except for fp64-level ties; dist2 is the fp32 direct-form distance to the labelled
  * centre.  col_scale (may be NULL) as in b2f_kmeans_step_scaled.  Same reference call site.            */
 int b2f_kmeans_predict_ws(const float* X, int64_t n, int d, int64_t ld, const float* col_scale, const void* prep,

@@ -658,7 +658,7 @@ static int km_step_ws_impl(const char* who, const float* X, int64_t n, int d, in
   }
   B2F_REQUIRE(!w, "%s: the tensor-core path does not take row weights", who);
   B2F_REQUIRE(have_ws, "%s: the filter pipeline needs labels and a workspace", who);
-  B2F_REQUIRE(tc3_checked || km_tcb_supported(k, d, ld), "%s: B2F_KM_TCB / B2F_KM_TCH need d in {64, 128} and k %% 128 == 0",
+  B2F_REQUIRE(tc3_checked || km_tcb_supported(k, d, ld), "%s: B2F_KM_TCB / B2F_KM_TCH need d in {64, 128}, k %% 128 == 0 and k <= 65536",
               who);
   B2F_REQUIRE(!colscale || algo == B2F_KM_TCH, "%s: a column scale is only taken by B2F_KM_TCH / B2F_KM_AUTO", who);
   B2F_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "%s: X must be 16-byte aligned", who);
