@@ -98,6 +98,18 @@ __device__ __forceinline__ float tb_row_scale(float xn, float cmax) {
 #ifndef TB_GRID
 #define TB_GRID 1
 #endif
+// ---- skewed row-tile pairs (TB_SKEW, fp16 filter with the class-minima epilogue) ---------------------------------
+// Every CTA streams ALL centre tiles from L2 for each of its row tiles: 45 of the 62 GB of L2 -> SM reads per 20M x 128,
+// k = 1024 launch, at 80 % of what this L2 delivers.  Here a centre-tile stage serves TWO row tiles: the CTA's even row
+// tiles (slot A: MMA issuer 0, epilogue warps 0-3, operand buffer 0) and its odd ones (slot B: issuer 1, epilogue warps
+// 4-7, buffer 1) run NT/2 centre tiles out of phase, slot A taking the centre tiles in the order 0 .. NT-1 and slot B
+// in the order NT/2 .. NT-1, 0 .. NT/2-1 -- so at every STEP both work on the same centre tile, while their row tiles
+// begin and end half a period apart and the operand of one is rebuilt under the MMAs of the other.  Step s loads
+// centre tile s % NT once; batches are issued A(s), B(s) in token order; accumulators are handed out along that
+// global order.  An epilogue warp now sees every centre tile of its row tile (no merge of two halves afterwards).
+#ifndef TB_SKEW
+#define TB_SKEW 1
+#endif
 constexpr int TB_QBASE = 0x4B000000;  // bit pattern of 2^23: quantised scores are TB_QBASE + [0, 2^23)
 __device__ __forceinline__ int tb_min3(int a, int b, int c) { return min(min(a, b), c); }
 // smallest of 16 consecutive entries of a chunk (8 operations)
@@ -376,6 +388,15 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
   // k <= 128 * nstages: every centre tile has a stage of its own -- loaded once, never released, instead of once per
   // row tile (at k = 256, d = 64 that was 40 KB of L2 reads per 32 KB row tile)
   const bool bres = NT <= nstages;
+  // TB_SKEW schedule: slot A = this CTA's row tiles 0, 2, 4, ..., slot B = 1, 3, 5, ...; steps [0, endA) and [begB, endB)
+  constexpr bool SKEW = H16 && TB_GRID && TB_SKEW;
+  const int my_tiles = (int64_t)blockIdx.x < ntiles ? (int)((ntiles - 1 - blockIdx.x) / gridDim.x) + 1 : 0;
+  const int nA = (my_tiles + 1) >> 1, nB = my_tiles >> 1;
+  const int begB = NT >> 1, endA = nA * NT, endB = begB + nB * NT;
+  const int nsteps = nB ? max(endA, endB) : endA;
+  // position of a batch in the global issue order A(0), [B(0)], A(1), [B(1)], ...
+  auto skew_gA = [&](int s) { return s + min(max(s - begB, 0), nB * NT); };
+  auto skew_gB = [&](int s) { return min(s + 1, endA) + (s - begB); };
 
   if (threadIdx.x == 0) {
     for (int c = 0; c < 4; ++c) {
@@ -396,7 +417,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       mbar_init(&sm->tok[c], 1);
       mbar_init(&sm->xa_full[c], EPI_THREADS);
       mbar_init(&sm->xa_empty[c], 1);
-      mbar_init(&sm->a_full[c], 2 * EPI_THREADS);
+      mbar_init(&sm->a_full[c], SKEW ? EPI_THREADS : 2 * EPI_THREADS);  // (TB_SKEW: one epilogue warpgroup per row tile)
       mbar_init(&sm->a_empty[c], EPI_THREADS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -461,7 +482,21 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     }
   } else if (warp == W_BPROD) {
     // ===================== B producer =====================
-    if (lane == 0) {
+    if (SKEW && lane == 0) {
+      const uint32_t it = 0;  // (tracer slot)
+      (void)it;
+      const int nload = bres ? min(nsteps, NT) : nsteps;  // resident centre tiles: one load each for the whole kernel
+      for (int st = 0; st < nload; ++st) {
+        const int nt = st % NT;
+        const uint32_t s = bres ? (uint32_t)nt : (uint32_t)(st % nstages);
+        if (!bres) mbar_wait_ns(&sm->b_empty[s], (((uint32_t)st / (uint32_t)nstages) & 1u) ^ 1u, 64);
+        mbar_expect_tx(&sm->b_full[s], (uint32_t)(KA * TB_STAGE_BYTES + TB_CN_BYTES));
+        for (int a = 0; a < KA; ++a)
+          tma_load_2d(stages + (size_t)s * TB_TILE_BYTES + (size_t)a * TB_STAGE_BYTES, &map_c1, a * 64, nt * TN,
+                      &sm->b_full[s]);
+        tma_load_2d(stages + (size_t)s * TB_TILE_BYTES + KA * TB_STAGE_BYTES, &map_c2, 0, nt * TN, &sm->b_full[s]);
+      }
+    } else if (lane == 0) {
       uint32_t s = 0, ph = 0, it = 0;
       for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         if (bres && it > 0) break;  // resident centre tiles: one load each for the whole kernel
@@ -495,9 +530,65 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     const uint64_t desc_sw32 = (1ull << 16) | (16ull << 32) | (1ull << 46) | (6ull << 61);
     const uint32_t st_a = smem_u32(stages) >> 4;
     const uint32_t chunk16 = CHUNK_BYTES >> 4, stage16 = (uint32_t)TB_STAGE_BYTES >> 4;
+    if (SKEW) {
+      // Issuer mp owns slot mp: its r-th row tile is the CTA's row tile 2r + mp, operand buffer mp, steps
+      // off + r*NT .. off + (r+1)*NT - 1 with off = 0 (A) or NT/2 (B); step s works on centre tile s % NT.
+      const int nMine = mp ? nB : nA, off = mp ? begB : 0;
+      const uint32_t xb = mp;
+      const uint32_t a1 = tmem_base + TB_A1 + xb * TB_ABUF;
+      // slot B's first batch comes after A(0) .. A(begB): phases of the token this warp has to see one by one
+      if (mp == 1 && nMine > 0)
+        for (int ph = 0; ph < begB; ++ph) mbar_wait_ns(&sm->tok[0], (uint32_t)ph & 1u, 20);
+      for (int r = 0; r < nMine; ++r) {
+        const uint32_t it = (uint32_t)(2 * r) + mp;  // (tracer slot)
+        (void)it;
+        for (int j = 0; j < NT; ++j) {
+          const int st = off + r * NT + j;
+          const int nt = st % NT;
+          const uint32_t g = (uint32_t)(mp ? skew_gB(st) : skew_gA(st));
+          const uint32_t cbuf = g % NBUF, cround = (g / NBUF) & 1u;
+          const uint32_t cstage = bres ? (uint32_t)nt : (uint32_t)(st % nstages);
+          const uint32_t cbphase = bres ? 0u : (((uint32_t)st / (uint32_t)nstages) & 1u);
+          mbar_wait_ns(&sm->b_full[cstage], cbphase, 20);
+          mbar_wait_ns(&sm->t_empty[cbuf], cround ^ 1u, 20);
+          // the batch before this one in the global order, if it is the other slot's: A(s) before B(s), B(s-1) before A(s)
+          if (mp == 1) {
+            if (st < endA) mbar_wait_ns(&sm->tok[0], (uint32_t)st & 1u, 20);
+          } else {
+            if (st - 1 >= begB && st - 1 < endB) mbar_wait_ns(&sm->tok[1], (uint32_t)(st - 1 - begB) & 1u, 20);
+          }
+          if (j == 0) mbar_wait_ns(&sm->xa_full[xb], (uint32_t)r & 1u, 20);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t tmem_d = tmem_base + tb_acc_col(cbuf);
+            const uint64_t bd = desc_fixed | (uint64_t)(st_a + cstage * ((uint32_t)TB_TILE_BYTES >> 4));
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+              if (a < KA) {
+                const uint64_t b1 = bd + a * stage16;
+#pragma unroll
+                for (int s4 = 0; s4 < 4; ++s4)
+                  tc_mma_f16_ts(tmem_d, a1 + a * 32 + 8 * s4, b1 + 2 * s4, IDESC_FP16, (a | s4) ? 1u : 0u);
+              }
+            }
+            tc_mma_f16_ss(tmem_d, desc_sw32 | (uint64_t)(smem_u32(aconst) >> 4),
+                          desc_sw32 | (uint64_t)(st_a + cstage * ((uint32_t)TB_TILE_BYTES >> 4) + KA * stage16),
+                          IDESC_FP16, 1u);
+            mbar_arrive(&sm->tok[mp]);
+            // the stage goes back after its LAST user of this step: B(s) when slot B is active at s, else A(s)
+            // (the tensor pipe runs in issue order: B's commit covers A's batch)
+            const bool b_active = st >= begB && st < endB;
+            if (!bres && (mp == 1 || !b_active)) tc_commit(&sm->b_empty[cstage]);
+            if (j == NT - 1) tc_commit(&sm->xa_empty[xb]);
+            tc_commit(&sm->t_full[cbuf]);
+          }
+          __syncwarp();
+        }
+      }
+    }
     uint32_t it = 0, buf = 0, round = 0, stage = 0, bphase = 0, gpar = 0;
     uint32_t mine_n = 0;  // centre tiles this warp has issued
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    for (int64_t tile = blockIdx.x; !SKEW && tile < ntiles; tile += gridDim.x, ++it) {
       const uint32_t xb = it % XBUFS;  // row-tile buffer of the TMEM operand
       const uint32_t a1 = tmem_base + TB_A1 + xb * TB_ABUF;  // 32 columns = 64 halves of k per atom
       const uint32_t a2 = tmem_base + TB_A2 + xb * TB_ABUF;
@@ -580,8 +671,11 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
     const float inv = H16 ? misc[KM_MISC_INV_SCALE2] : 1.f;
     const float cmax_e = misc[KM_MISC_CMAX];
     const bool gs = H16 && misc[KM_MISC_SC] > 0.f;  // global key scale: keys come straight out of the accumulator
-    uint32_t it = 0, buf = 0, round = 0, par = 0;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    uint32_t buf = 0, round = 0, par = 0;
+    // TB_SKEW: this warp takes EVERY centre tile of the row tiles of its slot (slot = half), in its slot's order
+    const uint32_t nrt = SKEW ? (uint32_t)(half ? nB : nA) : (uint32_t)my_tiles;
+    for (uint32_t rr = 0; rr < nrt; ++rr) {
+      const uint32_t it = SKEW ? 2 * rr + half : rr;
       float b1a = INFINITY, b2a = INFINITY, b1b = INFINITY, b2b = INFINITY;
       int i1a = 0, i1b = 1;
       // integer-key path (fp16 filter): running best / second best keys and the centre tile of the best
@@ -597,9 +691,22 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
         mbar_wait_ns(&sm->n_full[it & 3], (it >> 2) & 1, 32);
         arow = inv * tb_row_scale(sm->xnorm2[it & 3][row_in_tile], cmax_e);
       }
-      for (int nt = 0; nt < NT; ++nt) {
-        const uint32_t cbuf = buf, cround = round;
-        const bool mine = par == half;
+      for (int jt = 0; jt < NT; ++jt) {
+        int nt = jt;
+        uint32_t cbuf = buf, cround = round;
+        bool mine = par == half;
+        if (SKEW) {
+          const int st = (half ? begB : 0) + (int)rr * NT + jt;
+          const uint32_t g = (uint32_t)(half ? skew_gB(st) : skew_gA(st));
+          nt = st % NT;
+          cbuf = g % NBUF;
+          cround = (g / NBUF) & 1u;
+          mine = true;
+          // Slot B's first accumulator is not the first use of its buffer, and a parity wait only means something one
+          // phase ahead of what the waiter has seen: watch the earlier uses (slot A's) go by first.
+          if (half == 1 && rr == 0 && jt == 0)
+            for (uint32_t u = 0; u < g / NBUF; ++u) mbar_wait_ns(&sm->t_full[cbuf], u & 1u, 20);
+        }
         par ^= 1;
         if (++buf == NBUF) {
           buf = 0;
@@ -702,14 +809,15 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
           tb_top3_of8(A + 8, y1, y2, y3);
           tb_merge3(a1, a2, a3, y1, y2, y3);
         }
-        sm->p_b1[ab][half][row_in_tile] = __int_as_float(B1);
-        sm->p_b2[ab][half][row_in_tile] = __int_as_float(B2);
-        sm->p_b3[ab][half][row_in_tile] = B3;
+        const uint32_t hs = SKEW ? 0u : half;  // (TB_SKEW: the only hand-off of this row tile)
+        sm->p_b1[ab][hs][row_in_tile] = __int_as_float(B1);
+        sm->p_b2[ab][hs][row_in_tile] = __int_as_float(B2);
+        sm->p_b3[ab][hs][row_in_tile] = B3;
         // first centres of the best and the second best M-class (k <= 65536)
-        sm->p_i1[ab][half][row_in_tile] =
+        sm->p_i1[ab][hs][row_in_tile] =
             (int)((uint32_t)(T1 * TN + (B1 & 7) * 16) | ((uint32_t)(T2 * TN + (B2 & 7) * 16) << 16));
-        sm->p_i2[ab][half][row_in_tile] = a2;
-        sm->p_a3[ab][half][row_in_tile] = (a3 & ~15) | (a1 & 15);
+        sm->p_i2[ab][hs][row_in_tile] = a2;
+        sm->p_a3[ab][hs][row_in_tile] = (a3 & ~15) | (a1 & 15);
       } else if (H16) {
         sm->p_b1[ab][half][row_in_tile] = __int_as_float(B1);
         sm->p_b2[ab][half][row_in_tile] = __int_as_float(B2);
@@ -865,9 +973,16 @@ __global__ void __launch_bounds__(TB_THREADS, 1)
       if (H16 && TB_GRID) {
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          const int B1 = __float_as_int(sm->p_b1[ab][h][row_in_tile]), B2 = __float_as_int(sm->p_b2[ab][h][row_in_tile]);
-          const int B3 = sm->p_b3[ab][h][row_in_tile], a2 = sm->p_i2[ab][h][row_in_tile], a3 = sm->p_a3[ab][h][row_in_tile];
-          const uint32_t i12 = (uint32_t)sm->p_i1[ab][h][row_in_tile];
+          int B1 = 0x7fffffff, B2 = 0x7fffffff, B3 = 0x7fffffff, a2 = 0x7fffffff, a3 = 0x7fffffff;
+          uint32_t i12 = 0;
+          if (!SKEW || h == 0) {  // (TB_SKEW: the row tile has ONE hand-off; the other stays at "no centre tile")
+            B1 = __float_as_int(sm->p_b1[ab][h][row_in_tile]);
+            B2 = __float_as_int(sm->p_b2[ab][h][row_in_tile]);
+            B3 = sm->p_b3[ab][h][row_in_tile];
+            a2 = sm->p_i2[ab][h][row_in_tile];
+            a3 = sm->p_a3[ab][h][row_in_tile];
+            i12 = (uint32_t)sm->p_i1[ab][h][row_in_tile];
+          }
           gv1[h] = B1 >> 3; gm2[h] = B2 >> 3; gm3[h] = B3 >> 3;  // (INT_MAX stays far above every real value)
           ga2[h] = a2 >> 4; ga3[h] = a3 >> 4;
           gb1[h] = (int)(i12 & 0xffffu); gb2[h] = (int)(i12 >> 16);
