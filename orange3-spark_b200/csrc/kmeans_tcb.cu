@@ -10,9 +10,9 @@
 // A row whose best and second-best scores are more than 2 tau apart has a CERTAIN label and is accumulated here;
 // every other row goes to a list, is gathered into a compact matrix and re-assigned by the 3xTF32 kernel (which has
 // its own certainty test) and, failing that, by the fp64 kernel.  Labels, sums and counts therefore equal the exact
-// path's.  (fp16 filter: an uncertain row whose THIRD best score is clear of the best by more than 2 tau can only
-// belong to its best or second-best centre; such rows go to a pair list and are decided by two fp64 distances
-// (km_pair_exact_kernel) instead of a pass over all k centres.)  Cost: bf16x3 adds its (zero-mean) score error per certain row; the fp16 variant adds sum ||x||^2 only and
+// path's.  (fp16 filter: the epilogue keeps class minima instead of a running top two (TB_GRID below); an uncertain
+// row with at most four candidate centres within 2 tau of the best goes to a candidate list and is decided by
+// fp32 / fp64 distances to those (km_pair_exact_kernel) instead of a pass over all k centres.)  Cost: bf16x3 adds its (zero-mean) score error per certain row; the fp16 variant adds sum ||x||^2 only and
 // the centre-dependent remainder sum_j (n_j ||c_j||^2 - 2 c_j . S_j) exactly from the sums (tcb_cost_terms_kernel).
 //
 // Replaces MLlib's findClosest + axpy loop behind KMeans.fit;
@@ -20,11 +20,13 @@
 //
 // CTA = 640 threads, persistent, one per SM.  The scheduler prefers the higher warp ids, so latency-critical roles
 // sit at the top:
-//   warps 0-7   epilogue: two per TMEM lane quarter, each takes every other centre tile whole; tcgen05.ld, running
-//               best / second best (fp16: on integer keys, min/max only), partial results to shared memory
+//   warps 0-7   epilogue: two per TMEM lane quarter; bf16x3: each takes every other centre tile whole, running best /
+//               second best; fp16: each takes every centre tile of every other ROW tile (TB_SKEW below), integer
+//               class minima with 3-input min only; results to shared memory
 //   warps 8-11  split: fp32 row -> fp16 (or bf16 pair) operand -> tcgen05.st into tensor memory; row norms
-//   warps 12-15 finish (thread == row): merge the two epilogue partials, certainty test, labels, re-check list,
-//               accumulation of certain rows (16-byte vector reductions into 4 fp32 replicas), cost, counts
+//   warps 12-15 finish (thread == row): (merge the two epilogue partials,) certainty test, labels, candidate and
+//               re-check lists, accumulation of certain rows on the copy engine (bulk / tensor reductions into 4 fp32
+//               replicas), cost, counts
 //   warp 16     X producer (TMA, fp32 staging chunks of 128 rows x 32 floats)
 //   warps 17,19 MMA issuers, alternate centre tiles in token order (one batch of 4*KA + 1 or 12*KA tcgen05.mma per
 //               centre tile, A operand from tensor memory); warp 19 also allocates the tensor memory
