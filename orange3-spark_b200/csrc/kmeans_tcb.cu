@@ -1399,6 +1399,148 @@ __global__ void __launch_bounds__(256) km_pair_exact_kernel(const float* __restr
   }
 }
 
+// The same check with HALF a warp per entry (TB_GRID entries, d = 64 * NV): one warp per entry is a chain of dependent
+// round trips (entry -> row from HBM -> centres from L2) with 32 lanes waiting on it, and at d = 64 half of them had no
+// column at all.  Two entries per warp double the loads in flight and shorten the reductions to four shuffles.
+// (ncu launch list at cfg 2: 2.9 ms per iteration for 5-8M entries with the warp-per-entry kernel.)
+template <int NV>
+__global__ void __launch_bounds__(256) km_cand_kernel(const float* __restrict__ X, int64_t ld, int d,
+                                                      const float* __restrict__ colscale,
+                                                      const double* __restrict__ C64, const double* __restrict__ CN64,
+                                                      const float* __restrict__ C32, int k,
+                                                      double* __restrict__ payload, float* __restrict__ rep,
+                                                      unsigned long long* __restrict__ cnt, int32_t* __restrict__ labels,
+                                                      const TcbWs* __restrict__ ws, const int4* __restrict__ pairs,
+                                                      int pcap, int accumulate) {
+  const int lane = threadIdx.x & 31, hl = lane & 15;
+  const int hw = (blockIdx.x * blockDim.x + threadIdx.x) >> 4, nhw = (gridDim.x * blockDim.x) >> 4;
+  const int used = min(ws->pcount, pcap);
+  const int c0 = hl * 4;  // this lane's columns: c0 .. c0 + 3 (and 64 further on when NV == 2)
+  float* myrep = rep ? rep + (size_t)(blockIdx.x % KM_REPLICAS) * k * d : nullptr;
+  double cost = 0.0;
+  unsigned long long rows = 0;
+  const int4 none = make_int4(0, 0, 0, 0);
+  float4 xr[NV], xr1[NV];
+  int4 pr = hw < used ? pairs[hw] : none;
+  int4 pr1 = hw + nhw < used ? pairs[hw + nhw] : none;
+#pragma unroll
+  for (int v = 0; v < NV; ++v) xr[v] = ldg_stream(reinterpret_cast<const float4*>(X + (int64_t)pr.x * ld + c0 + 64 * v));
+  for (int e = hw; __any_sync(0xffffffffu, e < used); e += nhw) {
+    const bool valid = e < used;
+    const int4 pr2 = (int64_t)e + 2 * (int64_t)nhw < used ? pairs[e + 2 * nhw] : none;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)  // (row 0 when there is no next entry: a harmless read)
+      xr1[v] = ldg_stream(reinterpret_cast<const float4*>(X + (int64_t)pr1.x * ld + c0 + 64 * v));
+    const int64_t row = pr.x;
+    const int cand[4] = {pr.y & 0xffff, (int)((uint32_t)pr.y >> 16), pr.z & 0xffff, (int)((uint32_t)pr.z >> 16)};
+    const int nc = valid ? min(max(pr.w, 1), 4) : 0;
+    float4 x[NV];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      x[v] = xr[v];
+      if (colscale) {
+        const float4 sc = *reinterpret_cast<const float4*>(colscale + c0 + 64 * v);
+        x[v].x = __fmul_rn(x[v].x, sc.x); x[v].y = __fmul_rn(x[v].y, sc.y);
+        x[v].z = __fmul_rn(x[v].z, sc.z); x[v].w = __fmul_rn(x[v].w, sc.w);
+      }
+    }
+    // fp32 first (see km_pair_exact_kernel for the bounds)
+    float dq[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float a = 0.f;
+      if (q < nc) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+          const float4 cv = *reinterpret_cast<const float4*>(C32 + (size_t)cand[q] * d + c0 + 64 * v);
+          const float t0 = x[v].x - cv.x, t1 = x[v].y - cv.y, t2 = x[v].z - cv.z, t3 = x[v].w - cv.w;
+          a = fmaf(t0, t0, fmaf(t1, t1, fmaf(t2, t2, fmaf(t3, t3, a))));
+        }
+      }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+      dq[q] = a;
+    }
+    int pick = cand[0];
+    float dbest = dq[0], ebest = 0.f;
+    bool sure = true;
+#pragma unroll
+    for (int q = 1; q < 4; ++q)
+      if (q < nc && dq[q] < dbest) {
+        dbest = dq[q];
+        pick = cand[q];
+      }
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (q < nc && cand[q] == pick)
+        ebest = fmaf(2.0e-6f, dq[q], 3.0e-7f * sqrtf(dq[q] * (float)CN64[cand[q]])) + 1e-30f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (q < nc && cand[q] != pick) {
+        const float err = fmaf(2.0e-6f, dq[q], 3.0e-7f * sqrtf(dq[q] * (float)CN64[cand[q]])) + 1e-30f;
+        sure = sure && (dq[q] - err > dbest + ebest);
+      }
+    double vbest = (double)dbest;
+    const bool need64 = valid && !sure;
+    if (__any_sync(0xffffffffu, need64)) {  // fp64 on the master centres, same form as km_exact_kernel
+      double xn = 0.0;
+#pragma unroll
+      for (int v = 0; v < NV; ++v)
+        xn = fma((double)x[v].x, (double)x[v].x, fma((double)x[v].y, (double)x[v].y,
+                 fma((double)x[v].z, (double)x[v].z, fma((double)x[v].w, (double)x[v].w, xn))));
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) xn += __shfl_xor_sync(0xffffffffu, xn, o);
+      int pick64 = cand[0];
+      double v64 = 0.0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        double sdot = 0.0;
+        if (need64 && q < nc) {
+#pragma unroll
+          for (int v = 0; v < NV; ++v) {
+            const double2* pc = reinterpret_cast<const double2*>(C64 + (size_t)cand[q] * d + c0 + 64 * v);
+            const double2 u0 = pc[0], u1 = pc[1];
+            sdot = fma((double)x[v].x, u0.x, fma((double)x[v].y, u0.y, fma((double)x[v].z, u1.x, fma((double)x[v].w, u1.y, sdot))));
+          }
+        }
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) sdot += __shfl_xor_sync(0xffffffffu, sdot, o);
+        if (need64 && q < nc) {
+          const double vq = fmax(xn + CN64[cand[q]] - 2.0 * sdot, 0.0);
+          if (q == 0 || vq < v64 || (vq == v64 && cand[q] < pick64)) {  // lower index wins ties
+            v64 = vq;
+            pick64 = cand[q];
+          }
+        }
+      }
+      if (need64) {
+        pick = pick64;
+        vbest = v64;
+      }
+    }
+    if (valid) {
+      if (hl == 0) labels[row] = pick;
+      if (accumulate) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) red_add_v4(myrep + (size_t)pick * d + c0 + 64 * v, x[v]);
+        if (hl == 0) {
+          atomicAdd(cnt + pick, 1ull);
+          cost += vbest;
+          ++rows;
+        }
+      }
+    }
+    pr = pr1;
+    pr1 = pr2;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) xr[v] = xr1[v];
+  }
+  if (accumulate && hl == 0 && rows) {
+    atomicAdd(payload + (size_t)k * d + k, cost);
+    atomicAdd(payload + (size_t)k * d + k + 1, (double)rows);
+  }
+}
+
 // Centre-dependent part of the cost of everything accumulated so far:
 //   F = sum_j ( n_j ||c_j||^2 - 2 c_j . S_j ),   S_j / n_j = fp64 payload + fp32 replicas / integer counts.
 // The fp16 filter kernel adds only sum ||x||^2 of its certain rows to the cost; the exact remainder of their cost is
@@ -1658,8 +1800,15 @@ int km_tcb_step(const float* X, int64_t n, int d, int64_t ld, const float* colsc
     if (acc_main && colscale && (rc = km_fold_scaled(acc, k, d, colscale, stream)) != B2F_OK) return rc;
     if (acc_main) tcb_cost_terms_kernel<<<cgrid, 256, 0, stream>>>(payload, rep, cnt, c64, k, d, 1.0);
     // rows with exactly two candidate centres: two fp64 distances each
-    km_pair_exact_kernel<<<b2f_sm_count() * 8, 256, 0, stream>>>(X, ld, d, colscale, c64, cn64, c32, k, payload, rep, cnt,
-                                                                 labels, hdr, pairs, cap, accumulate ? 1 : 0);
+    if (TB_GRID && d == 64)
+      km_cand_kernel<1><<<b2f_sm_count() * 8, 256, 0, stream>>>(X, ld, d, colscale, c64, cn64, c32, k, payload, rep, cnt,
+                                                                labels, hdr, pairs, cap, accumulate ? 1 : 0);
+    else if (TB_GRID && d == 128)
+      km_cand_kernel<2><<<b2f_sm_count() * 8, 256, 0, stream>>>(X, ld, d, colscale, c64, cn64, c32, k, payload, rep, cnt,
+                                                                labels, hdr, pairs, cap, accumulate ? 1 : 0);
+    else
+      km_pair_exact_kernel<<<b2f_sm_count() * 8, 256, 0, stream>>>(X, ld, d, colscale, c64, cn64, c32, k, payload, rep,
+                                                                   cnt, labels, hdr, pairs, cap, accumulate ? 1 : 0);
     B2F_LAUNCH_CHECK();
   } else {
     rc = tcb_launch_filter<KM_FILTER_BF16X3, false, false>(grid, smem, stream, mx, m1, m2, mr, X, n, d, ld, nullptr, cn, misc, kappa2,
