@@ -255,7 +255,7 @@ def b200_arm(args):
     rows_after = eng.rows_counted(eng.payload)
     hdr = eng.ws[:20].view(torch.int32).cpu().numpy() if eng.use_ws else [0] * 5
     uncertain, pair_rows = int(hdr[0]), min(int(hdr[4]), int(hdr[3]))
-    algo_name = ("fp16 filter + pair check + 3xTF32 re-check + fp64 tail (B2F_KM_TCH)" if eng.use_ws and args.algo in (0, 5) else "bf16x3 filter + 3xTF32 re-check (B2F_KM_TCB)" if eng.use_ws else "algo %d" % args.algo)
+    algo_name = ("fp16 filter + candidate check + 3xTF32 re-check + fp64 tail (B2F_KM_TCH)" if eng.use_ws and args.algo in (0, 5) else "bf16x3 filter + 3xTF32 re-check (B2F_KM_TCB)" if eng.use_ws else "algo %d" % args.algo)
     value = 1e3 / ms_step
     flops = 2.0 * n * k * d
     achieved = flops / (kern_ms * 1e-3) / 1e12

@@ -44,7 +44,7 @@ class CudaLloydEngine:
         self.launches = 0
         self.fallbacks = 0
         self._xmax = None
-        # low-precision filter pass + pair check + 3xTF32 re-check (B2F_KM_TCH fp16 / B2F_KM_TCB bf16x3; AUTO = TCH)
+        # low-precision filter pass + candidate check (at most four centres, fp32 / fp64) + 3xTF32 re-check (B2F_KM_TCH fp16 / B2F_KM_TCB bf16x3; AUTO = TCH)
         # needs a labels buffer and a workspace.  Decided from the SHAPE only (never from this rank's row count):
         # every rank must take the same branches between collectives, also one whose shard is empty.
         self.use_ws = (algo in (N.KM_AUTO, N.KM_TCB, N.KM_TCH) and w is None and self.d in (64, 128)
@@ -115,7 +115,7 @@ class CudaLloydEngine:
                 N.check(self.L.b2f_kmeans_step_ws(N.ptr(X.data), X.n, X.d, X.ld, None, N.ptr(self.prep), self.k,
                                                   N.ptr(self.acc), N.ptr(lab), N.ptr(self.ws), self.ws_bytes, algo,
                                                   s), "b2f_kmeans_step_ws")
-                # TCH: 2 cost-term kernels + filter + pair check + gather + 3xTF32 re-check + scatter + exact tail;
+                # TCH: 2 cost-term kernels + filter + candidate check + gather + 3xTF32 re-check + scatter + exact tail;
                 # TCB: filter + gather + re-check + scatter + exact tail; exact: set-cap + 3xTF32 + exact tail
                 self.launches += 3 if exact else (5 if self.algo == N.KM_TCB else 8)
         else:
@@ -194,7 +194,7 @@ def ws_dropped(ws):
 
 def predict_labels(X, centers, want_dist=False, algo=N.KM_AUTO, info=None):
     """Assignment only (KMeansModel.transform / computeCost / initialisers).  Where the shape allows it the labels
-    come from the same certainty pipeline as the fit (filter pass, pair check, 3xTF32 re-check, fp64 tail), so they
+    come from the same certainty pipeline as the fit (filter pass, candidate check, 3xTF32 re-check, fp64 tail), so they
     equal the fp64 assignment except for fp64-level ties; distances are those to the labelled centre."""
     N.require_cuda()
     torch = _torch()

@@ -65,7 +65,7 @@ def kmeans_step_raw(X, n, d, ld, C, algo, w=None, want_labels=True, ws_bytes=Non
                                          N.ptr(ws), wsb, algo, stream()), "step_ws")
         if info is not None:
             # workspace header (include/b200fit.h): [0] rows listed for the 3xTF32 re-check, [1] rows re-checked,
-            # [2] rows listed for the fp64 kernel, [3] capacity of each list, [4] rows offered to the pair check
+            # [2] rows listed for the fp64 kernel, [3] capacity of each list, [4] rows offered to the candidate check (the pair check of earlier versions)
             hdr = ws[:20].view(torch.int32).cpu().numpy()
             info["listed"], info["rechecked"], info["exact"], info["cap"] = (int(v) for v in hdr[:4])
             info["pairs"] = min(int(hdr[4]), int(hdr[3]))
